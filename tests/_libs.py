@@ -1,0 +1,194 @@
+"""ctypes loaders used by the tests (checker side only):
+
+  oracle()   -> oracle/liboracle.so   the plain-C restatement (built on demand with gcc)
+  ref()      -> oracle/_ref/libsmcref.so  the UNMODIFIED reference compiled from /root/reference (None if not built
+                and /root/reference is absent, e.g. never on the GPU box unless it travelled with the snapshot)
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+MAXN, MAXE = 64, 64
+MAXNODES = 2 * MAXN - 1
+
+c_dp = ctypes.POINTER(ctypes.c_double)
+c_ip = ctypes.POINTER(ctypes.c_int)
+
+
+def P(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class OrcModel(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int), ("E", ctypes.c_int), ("mu", ctypes.c_double), ("rho", ctypes.c_double),
+                ("seqlen", ctypes.c_double), ("t_start", ctypes.c_double * MAXE), ("inv2N", ctypes.c_double * MAXE),
+                ("vb_logfac", ctypes.c_double * MAXE), ("rec_mask", ctypes.c_uint8 * MAXE)]
+
+
+class OrcParticle(ctypes.Structure):
+    _fields_ = [("parent", ctypes.c_int * MAXNODES), ("height", ctypes.c_double * MAXNODES),
+                ("logw", ctypes.c_double), ("updated_to", ctypes.c_double), ("cur_base", ctypes.c_double),
+                ("next_base", ctypes.c_double)]
+
+
+class OrcRng(ctypes.Structure):
+    _fields_ = [("key", ctypes.c_uint32 * 2), ("ctr", ctypes.c_uint32 * 4), ("buf", ctypes.c_double * 2),
+                ("have", ctypes.c_int)]
+
+
+class OrcEvent(ctypes.Structure):
+    _fields_ = [("type", ctypes.c_int), ("epoch", ctypes.c_int), ("cnt", ctypes.c_int),
+                ("x0", ctypes.c_double), ("x1", ctypes.c_double), ("opp", ctypes.c_double)]
+
+
+class OrcEvents(ctypes.Structure):
+    _fields_ = [("ev", ctypes.POINTER(OrcEvent)), ("count", ctypes.c_int), ("cap", ctypes.c_int),
+                ("overflow", ctypes.c_int)]
+
+
+class OrcRecEvent(ctypes.Structure):
+    _fields_ = [("row", ctypes.c_int), ("slot", ctypes.c_int), ("ev", OrcEvent)]
+
+
+_oracle = None
+_ref = None
+
+
+def build_oracle():
+    so = os.path.join(ORACLE_DIR, "liboracle.so")
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("smc_oracle.c", "smc_tally_oracle.c", "smc_oracle.h")]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        L = ctypes.CDLL(build_oracle())
+        for name in ("orc_fastexp", "orc_exp_digamma", "orc_prune_likelihood", "orc_site_likelihood",
+                     "orc_tree_length", "orc_branch_length_with_data", "orc_normalize", "orc_ess_partial_sums",
+                     "orc_normalize_log", "orc_rng_uniform"):
+            getattr(L, name).restype = ctypes.c_double
+        L.orc_fastexp.argtypes = [ctypes.c_double]
+        L.orc_exp_digamma.argtypes = [ctypes.c_double]
+        L.orc_prune_likelihood.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_double, ctypes.c_int]
+        L.orc_site_likelihood.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                          ctypes.c_double, ctypes.c_int, ctypes.c_int]
+        L.orc_tree_length.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_branch_length_with_data.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_systematic_resampling.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                                ctypes.c_void_p]
+        L.orc_normalize.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.orc_normalize_log.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.orc_ess_partial_sums.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        L.orc_rng_init.argtypes = [ctypes.POINTER(OrcRng), ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32,
+                                   ctypes.c_uint32, ctypes.c_uint32]
+        L.orc_rng_uniform.argtypes = [ctypes.POINTER(OrcRng)]
+        L.orc_init_particle.argtypes = [ctypes.POINTER(OrcModel), ctypes.POINTER(OrcParticle), ctypes.POINTER(OrcRng),
+                                        ctypes.c_double]
+        L.orc_smc_move.argtypes = [ctypes.POINTER(OrcModel), ctypes.POINTER(OrcParticle), ctypes.POINTER(OrcRng),
+                                   ctypes.c_int, ctypes.POINTER(OrcEvents), c_dp]
+        L.orc_extend_row.argtypes = [ctypes.POINTER(OrcModel), ctypes.POINTER(OrcParticle), ctypes.POINTER(OrcRng),
+                                     ctypes.c_double, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                     ctypes.POINTER(OrcEvents)]
+        L.orc_redraw_next_base.argtypes = [ctypes.POINTER(OrcModel), ctypes.POINTER(OrcParticle),
+                                           ctypes.POINTER(OrcRng)]
+        L.orc_update_schedule.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double,
+                                          ctypes.c_int, ctypes.c_void_p]
+        L.orc_max_epoch_to_record.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_double]
+        L.orc_lagged_tallies.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double,
+                                         ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
+        _oracle = L
+    return _oracle
+
+
+def make_model(n, t_start, inv2N, mu, rho, seqlen, vb_logfac=None, rec_mask=None):
+    m = OrcModel()
+    m.n, m.E, m.mu, m.rho, m.seqlen = n, len(t_start), mu, rho, seqlen
+    for e, (t, v) in enumerate(zip(t_start, inv2N)):
+        m.t_start[e] = t
+        m.inv2N[e] = v
+        m.vb_logfac[e] = 0.0 if vb_logfac is None else vb_logfac[e]
+        m.rec_mask[e] = 3 if rec_mask is None else rec_mask[e]
+    return m
+
+
+def ref():
+    """The compiled reference (or None).  Built from /root/reference when that is present."""
+    global _ref
+    if _ref is None:
+        so = os.path.join(ORACLE_DIR, "_ref", "libsmcref.so")
+        if not os.path.exists(so) and os.path.isdir("/root/reference/src"):
+            subprocess.check_call([os.path.join(ORACLE_DIR, "build_ref.sh")], stdout=subprocess.DEVNULL,
+                                  stderr=subprocess.DEVNULL)
+        if not os.path.exists(so):
+            return None
+        L = ctypes.CDLL(so)
+        L.ref_open.restype = ctypes.c_void_p
+        L.ref_last_error.restype = ctypes.c_char_p
+        L.ref_mutation_rate.restype = ctypes.c_double
+        L.ref_recombination_rate.restype = ctypes.c_double
+        L.ref_max_seg_len.restype = ctypes.c_double
+        for name in ("ref_close", "ref_num_epochs", "ref_mutation_rate", "ref_recombination_rate", "ref_max_seg_len"):
+            getattr(L, name).argtypes = [ctypes.c_void_p]
+        L.ref_epoch_table.argtypes = [ctypes.c_void_p] * 3
+        L.ref_prune.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                ctypes.c_void_p, ctypes.c_int, c_dp]
+        L.ref_site_likelihood.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, c_dp]
+        L.ref_branch_lengths.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                         ctypes.c_void_p, ctypes.c_void_p, c_dp, c_dp]
+        L.ref_extend_nomut.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_void_p, ctypes.c_double, ctypes.c_double, c_dp]
+        L.ref_systematic.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                     ctypes.c_void_p]
+        L.ref_weights_path.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_double, c_dp, c_ip, ctypes.c_void_p, ctypes.c_void_p]
+        L.ref_prior_trees.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                      ctypes.c_void_p]
+        L.ref_smc_moves.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                    ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.ref_arg_walk.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 4
+        L.ref_tally_script.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_long, ctypes.c_void_p]
+        _ref = L
+    return _ref
+
+
+def ref_open(cmdline):
+    """Open a reference handle from an smcsmc command line string (quiet)."""
+    L = ref()
+    args = cmdline.split()
+    av = (ctypes.c_char_p * len(args))(*[a.encode() for a in args])
+    # the reference prints its command line on stdout while parsing; silence fd 1 around the call
+    import sys
+    sys.stdout.flush()
+    saved = os.dup(1)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 1)
+    try:
+        h = L.ref_open(len(args), av)
+    finally:
+        os.dup2(saved, 1)
+        os.close(devnull)
+        os.close(saved)
+    if not h:
+        raise RuntimeError("ref_open failed: %s" % L.ref_last_error())
+    return ctypes.c_void_p(h)
+
+
+def ref_model(h, n, seqlen):
+    """orc model taken from the reference's own parsed Model (single population)."""
+    L = ref()
+    E = L.ref_num_epochs(h)
+    t = np.zeros(E)
+    inv = np.zeros(E)
+    L.ref_epoch_table(h, P(t), P(inv))
+    return make_model(n, list(t), list(inv), L.ref_mutation_rate(h), L.ref_recombination_rate(h), seqlen)
