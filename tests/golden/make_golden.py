@@ -1,0 +1,206 @@
+#!/usr/bin/env python
+"""Regenerate tests/golden/*.npz from the UNMODIFIED reference compiled into oracle/_ref/libsmcref.so
+(oracle/build_ref.sh, needs /root/reference).  Test tooling only.  Run:  python tests/golden/make_golden.py
+
+Every fixture stores the seeded inputs next to the reference's outputs, so the tests need neither the reference nor
+this script at run time.  Reference entry points: see oracle/ref_harness.cpp.
+"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import _libs  # noqa: E402
+import _cases  # noqa: E402
+from _libs import P  # noqa: E402
+
+CMD = "smcsmc -nsam {n} -Np 10 -N0 10000 -t {t} -r {r} {L} -seed 1 {extra}"
+
+
+def open_ref(n, extra="", L=1000000, mu=2.5e-8, rho=1e-8):
+    return _libs.ref_open(CMD.format(n=n, t=4e4 * mu * L, r=4e4 * rho * L, L=L, extra=extra))
+
+
+def golden_prune():
+    R = _libs.ref()
+    out = {}
+    for n in (2, 3, 4, 8, 16):
+        h = open_ref(n)
+        mu = R.ref_mutation_rate(h)
+        count = 64
+        parent, height = _cases.random_trees(n, count, seed=100 + n)
+        # stretch some trees so that branch*mu crosses the fastexp switch-over (x^2 >= 0.516)
+        height[count // 2:] *= np.logspace(0, 4.5, count - count // 2)[:, None]
+        data = _cases.random_alleles(n, count, seed=200 + n, p_unphased=0.3 if n >= 4 else 0.0)
+        phased = _cases.random_alleles(n, count, seed=300 + n)
+        nn = 2 * n - 1
+        lik = np.zeros(count); lik_aa = np.zeros(count); site = np.zeros(count); site_aa = np.zeros(count)
+        bl = np.zeros(count); tl = np.zeros(count); nomut = np.zeros(count)
+        for t in range(count):
+            v = ctypes.c_double()
+            par, hei = np.ascontiguousarray(parent[t]), np.ascontiguousarray(height[t])
+            assert R.ref_prune(h, n, nn, P(par), P(hei), P(phased[t]), 0, ctypes.byref(v)) == 0
+            lik[t] = v.value
+            assert R.ref_prune(h, n, nn, P(par), P(hei), P(phased[t]), 1, ctypes.byref(v)) == 0
+            lik_aa[t] = v.value
+            assert R.ref_site_likelihood(h, n, nn, P(par), P(hei), P(data[t]), 0, 0, ctypes.byref(v)) == 0
+            site[t] = v.value
+            assert R.ref_site_likelihood(h, n, nn, P(par), P(hei), P(data[t]), 1, 0, ctypes.byref(v)) == 0
+            site_aa[t] = v.value
+            a, b = ctypes.c_double(), ctypes.c_double()
+            assert R.ref_branch_lengths(h, n, nn, P(par), P(hei), P(phased[t]), ctypes.byref(a), ctypes.byref(b)) == 0
+            bl[t], tl[t] = a.value, b.value
+            assert R.ref_extend_nomut(h, n, nn, P(par), P(hei), P(phased[t]), 10.0, 10.0 + 37.0 * (t + 1),
+                                      ctypes.byref(v)) == 0
+            nomut[t] = v.value
+        out.update({f"n{n}_parent": parent, f"n{n}_height": height, f"n{n}_data": data, f"n{n}_phased": phased,
+                    f"n{n}_lik": lik, f"n{n}_lik_aa": lik_aa, f"n{n}_site": site, f"n{n}_site_aa": site_aa,
+                    f"n{n}_bl": bl, f"n{n}_tl": tl, f"n{n}_nomut": nomut, f"n{n}_mu": np.array(mu)})
+        R.ref_close(h)
+    # the reference's own example tree (scrm/src/forest-debug.cc:57-121) and the allele patterns of
+    # test/old/unittest/test_FroestState.cpp:135-199
+    h = open_ref(4)
+    par = np.array([4, 4, 5, 5, 6, 6, -1], dtype=np.int32)
+    hei = np.array([0, 0, 0, 0, 1, 3, 10], dtype=np.float64)
+    pats = np.array([[1, 1, 1, 1], [0, 1, 1, 1], [-1, 1, 1, 1], [0, 1, 0, 1], [0, 1, -1, 1], [0, 1, -1, -1],
+                     [-1, -1, 0, 1], [-1, -1, 0, -1], [-1, 1, 0, -1], [-1, -1, -1, -1], [1, -1, -1, 0]], dtype=np.int32)
+    ex_bl = np.zeros(len(pats)); ex_tl = np.zeros(len(pats)); ex_lik = np.zeros(len(pats))
+    for i, d in enumerate(pats):
+        a, b, v = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+        d = np.ascontiguousarray(d)
+        assert R.ref_branch_lengths(h, 4, 7, P(par), P(hei), P(d), ctypes.byref(a), ctypes.byref(b)) == 0
+        assert R.ref_prune(h, 4, 7, P(par), P(hei * 1e4), P(d), 0, ctypes.byref(v)) == 0
+        ex_bl[i], ex_tl[i], ex_lik[i] = a.value, b.value, v.value
+    out.update({"ex_parent": par, "ex_height": hei, "ex_pats": pats, "ex_bl": ex_bl, "ex_tl": ex_tl,
+                "ex_lik_scaled1e4": ex_lik, "ex_mu": np.array(R.ref_mutation_rate(h))})
+    R.ref_close(h)
+    np.savez_compressed(os.path.join(HERE, "prune.npz"), **out)
+
+
+def golden_resampling():
+    R = _libs.ref()
+    h = open_ref(4, "-ESS 0.5")
+    out = {}
+    k = 0
+    for N in (1, 2, 7, 100, 1000, 4096):
+        for kind in ("uniform", "mild", "lognormal", "degenerate", "zeros"):
+            w = _cases.skewed_weights(N, seed=1000 + k, kind=kind)
+            ps = _cases.sequential_partial_sums(w)
+            for u in (1e-300, 0.25, 0.5, 0.9999999999, float(np.random.default_rng(k).random())):
+                counts = np.zeros(N, dtype=np.int32)
+                assert R.ref_systematic(h, P(ps), N, N, ctypes.c_double(u), P(counts)) == 0
+                assert counts.sum() == N
+                out[f"c{k}_ps"] = ps; out[f"c{k}_u"] = np.array(u); out[f"c{k}_counts"] = counts
+                k += 1
+    out["ncases"] = np.array(k)
+    # full weight path: normalise -> ESS test -> systematic resampling -> multiplicities and child weights
+    j = 0
+    for N in (10, 333, 2000):
+        for kind in ("uniform", "mild", "lognormal"):
+            rng = np.random.default_rng(5000 + j)
+            w = _cases.skewed_weights(N, seed=2000 + j, kind=kind) * 0.37     # un-normalised on purpose
+            u = float(rng.random())
+            lnZ, res = ctypes.c_double(), ctypes.c_int()
+            mult = np.zeros(N, dtype=np.int32); wout = np.zeros(N)
+            assert R.ref_weights_path(h, N, P(w), P(w), ctypes.c_double(u), ctypes.byref(lnZ), ctypes.byref(res),
+                                      P(mult), P(wout)) == 0
+            out[f"p{j}_w"] = w; out[f"p{j}_u"] = np.array(u); out[f"p{j}_lnZ"] = np.array(lnZ.value)
+            out[f"p{j}_resampled"] = np.array(res.value); out[f"p{j}_mult"] = mult; out[f"p{j}_wout"] = wout
+            j += 1
+    out["npaths"] = np.array(j)
+    R.ref_close(h)
+    np.savez_compressed(os.path.join(HERE, "resampling.npz"), **out)
+
+
+def golden_tallies():
+    R = _libs.ref()
+    out = {}
+    k = 0
+    for (N, E, Rows, seed) in ((4, 1, 30, 1), (6, 3, 60, 2), (16, 5, 80, 3)):
+        times = " ".join("-eN {} 1".format(0.1 * e) for e in range(1, E))
+        h = open_ref(4, times)
+        assert R.ref_num_epochs(h) == E
+        seqlen = 1e6
+        lags = np.array([2e5 / (e + 1) for e in range(E)])
+        ts, inv = np.zeros(E), np.zeros(E)
+        R.ref_epoch_table(h, P(ts), P(inv))
+        script, row_end, weights, anc, w_final, evs = _cases.tally_script(N, E, Rows, seed, lags, seqlen, ts)
+        res = np.zeros(6 * E)
+        assert R.ref_tally_script(h, N, P(lags), P(script), len(script), P(res)) == 0, R.ref_last_error()
+        out[f"t{k}_N"] = np.array(N); out[f"t{k}_E"] = np.array(E); out[f"t{k}_lags"] = lags
+        out[f"t{k}_row_end"] = row_end; out[f"t{k}_weights"] = weights; out[f"t{k}_anc"] = anc
+        out[f"t{k}_w_final"] = w_final; out[f"t{k}_seqlen"] = np.array(seqlen)
+        out[f"t{k}_evs"] = np.array(evs, dtype=np.float64)
+        out[f"t{k}_tallies"] = res.reshape(6, E)
+        R.ref_close(h)
+        k += 1
+    out["ncases"] = np.array(k)
+    np.savez_compressed(os.path.join(HERE, "tallies.npz"), **out)
+
+
+MOMENT_MODELS = {
+    # name: (n, scrm demography flags)
+    "const4": (4, ""),
+    "bottleneck8": (8, "-eN 0.05 0.2 -eN 0.2 2"),
+    "zigzag8": (8, "-eN 0.0025 0.2 -eN 0.005 1 -eN 0.01 0.2 -eN 0.02 1 -eN 0.04 0.2 -eN 0.08 1 -eN 0.16 0.2 "
+                   "-eN 0.32 1 -eN 0.64 0.2 -eN 1.28 1"),
+}
+
+
+def golden_moments(count=40000, reps=40000):
+    """Sample moments of the reference's stochastic pieces (its own mt19937_64 stream): prior trees
+    (Forest::buildInitialTree), one SMC' move from a fixed start tree (Forest::sampleNextGenealogy) and the prior ARG
+    walk (sampleNextGenealogy + sampleRecSeqPosition).  Stored as mean / standard error for z-tests."""
+    R = _libs.ref()
+    out = {}
+    for name, (n, dem) in MOMENT_MODELS.items():
+        h = open_ref(n, dem, L=100000000)
+        E = R.ref_num_epochs(h)
+        ts, inv = np.zeros(E), np.zeros(E)
+        R.ref_epoch_table(h, P(ts), P(inv))
+        nn = 2 * n - 1
+        parent = np.zeros((count, nn), dtype=np.int32); height = np.zeros((count, nn)); tl = np.zeros(count)
+        assert R.ref_prior_trees(h, count, P(parent), P(height), P(tl)) == 0, R.ref_last_error()
+        tm = height.max(axis=1)
+        first = height[:, n]
+        out[f"{name}_n"] = np.array(n); out[f"{name}_t_start"] = ts; out[f"{name}_inv2N"] = inv
+        out[f"{name}_prior"] = np.array([[x.mean(), x.std(ddof=1) / np.sqrt(count)] for x in (tm, tl, first, tm ** 2)])
+        # one SMC' move from a fixed start tree (the first prior tree)
+        p0, h0 = np.ascontiguousarray(parent[0]), np.ascontiguousarray(height[0])
+        mp = np.zeros((reps, nn), dtype=np.int32); mh = np.zeros((reps, nn)); rh = np.zeros(reps)
+        assert R.ref_smc_moves(h, n, P(p0), P(h0), reps, P(mp), P(mh), P(rh)) == 0, R.ref_last_error()
+        mtl = np.array([(mh[i][mp[i][mp[i] >= 0]] - mh[i][mp[i] >= 0]).sum() for i in range(reps)])
+        mtm = mh.max(axis=1)
+        unchanged = (np.abs(mh - h0[None, :]).max(axis=1) < 1e-9 * h0.max()).astype(float)
+        newroot = (mtm > h0.max() * (1 + 1e-12)).astype(float)
+        out[f"{name}_move_start_parent"] = p0; out[f"{name}_move_start_height"] = h0
+        out[f"{name}_move"] = np.array([[x.mean(), x.std(ddof=1) / np.sqrt(reps)] for x in (rh, mtl, mtm, unchanged, newroot)])
+        # ARG walk along the sequence
+        cnt = 20000
+        pos = np.zeros(cnt); rech = np.zeros(cnt); tmr = np.zeros(cnt); tln = np.zeros(cnt)
+        got = R.ref_arg_walk(h, cnt, P(pos), P(rech), P(tmr), P(tln))
+        assert got > 1000, got
+        pos, rech, tmr, tln = pos[:got], rech[:got], tmr[:got], tln[:got]
+        gaps = np.diff(pos)
+        # autocorrelated along the sequence: use batch means (50 batches) for the standard errors
+        def bm(x):
+            b = np.array_split(x, 50)
+            m = np.array([c.mean() for c in b])
+            return [x.mean(), m.std(ddof=1) / np.sqrt(len(m))]
+        out[f"{name}_walk"] = np.array([bm(gaps), bm(rech), bm(tmr[1:]), bm(tln[1:])])
+        out[f"{name}_rho"] = np.array(R.ref_recombination_rate(h)); out[f"{name}_mu"] = np.array(R.ref_mutation_rate(h))
+        R.ref_close(h)
+    np.savez_compressed(os.path.join(HERE, "moments.npz"), **out)
+
+
+if __name__ == "__main__":
+    if _libs.ref() is None:
+        sys.exit("oracle/_ref/libsmcref.so not available (needs /root/reference)")
+    golden_prune()
+    golden_resampling()
+    golden_tallies()
+    golden_moments()
+    print("wrote", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))

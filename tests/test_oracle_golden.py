@@ -1,0 +1,126 @@
+"""CPU tests: the C restatement (oracle/liboracle.so) against the committed golden vectors produced by the UNMODIFIED
+reference (tests/golden/make_golden.py <- oracle/_ref/libsmcref.so).  This is what pins the oracle."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+import _libs
+import _cases
+from _libs import P
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def L():
+    return _libs.oracle()
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 8, 16])
+def test_prune_and_branch_lengths(L, n):
+    g = np.load(os.path.join(G, "prune.npz"))
+    mu = float(g[f"n{n}_mu"])
+    parent, height = g[f"n{n}_parent"], g[f"n{n}_height"]
+    for t in range(parent.shape[0]):
+        par, hei = np.ascontiguousarray(parent[t]), np.ascontiguousarray(height[t])
+        ph, da = np.ascontiguousarray(g[f"n{n}_phased"][t]), np.ascontiguousarray(g[f"n{n}_data"][t])
+        # bit-exact: same operations in the same order as particle.cpp:625-680
+        assert L.orc_prune_likelihood(n, P(par), P(hei), P(ph), mu, 0) == g[f"n{n}_lik"][t]
+        assert L.orc_prune_likelihood(n, P(par), P(hei), P(ph), mu, 1) == g[f"n{n}_lik_aa"][t]
+        assert L.orc_site_likelihood(n, P(par), P(hei), P(da), mu, 0, 0) == g[f"n{n}_site"][t]
+        assert L.orc_site_likelihood(n, P(par), P(hei), P(da), mu, 1, 0) == g[f"n{n}_site_aa"][t]
+        bl = L.orc_branch_length_with_data(n, P(par), P(hei), P(ph))
+        tl = L.orc_tree_length(n, P(par), P(hei))
+        # the reference maintains length_below incrementally (updateAbove), so summation order differs: 1e-12 relative
+        assert bl == pytest.approx(g[f"n{n}_bl"][t], rel=1e-12, abs=0)
+        assert tl == pytest.approx(g[f"n{n}_tl"][t], rel=1e-12, abs=0)
+        nmiss = int((ph == -1).sum())
+        lobs = 0.0 if nmiss == n else (tl if nmiss == 0 else bl)
+        nomut = L.orc_fastexp(-mu * lobs * (37.0 * (t + 1)))
+        assert nomut == pytest.approx(g[f"n{n}_nomut"][t], rel=1e-12, abs=0)
+
+
+def test_reference_example_tree(L):
+    """createExampleTree (forest-debug.cc:57): 7 local nodes, tree length 24; allele patterns of
+    test/old/unittest/test_FroestState.cpp:135-199 (that test is stale and commented out in the reference; the values
+    asserted here are what the CURRENT reference code returns, stored in the fixture)."""
+    g = np.load(os.path.join(G, "prune.npz"))
+    par, hei = g["ex_parent"], g["ex_height"]
+    assert L.orc_tree_length(4, P(par), P(hei)) == 24.0
+    assert list(g["ex_tl"]) == [24.0] * len(g["ex_tl"])
+    for d, want in zip(g["ex_pats"], g["ex_bl"]):
+        d = np.ascontiguousarray(d)
+        assert L.orc_branch_length_with_data(4, P(par), P(hei), P(d)) == want
+    # Known answers of the reference's (stale, commented-out) cppunit test: 24,24,21,24,23,6,2,0,20,0,20.  That test
+    # numbered the tips in the opposite order (include_haplotypes_at_tips), so they hold for the reversed patterns.
+    stale = [24.0, 24.0, 21.0, 24.0, 23.0, 6.0, 2.0, 0.0, 20.0, 0.0, 20.0]
+    for d, want in zip(g["ex_pats"], stale):
+        d = np.ascontiguousarray(d[::-1])
+        assert L.orc_branch_length_with_data(4, P(par), P(hei), P(d)) == want
+    hs = np.ascontiguousarray(hei * 1e4)
+    for d, want in zip(g["ex_pats"], g["ex_lik_scaled1e4"]):
+        d = np.ascontiguousarray(d)
+        assert L.orc_prune_likelihood(4, P(par), P(hs), P(d), float(g["ex_mu"]), 0) == want
+
+
+def test_systematic_resampling_bit_exact(L):
+    g = np.load(os.path.join(G, "resampling.npz"))
+    for k in range(int(g["ncases"])):
+        ps, u, want = g[f"c{k}_ps"], float(g[f"c{k}_u"]), g[f"c{k}_counts"]
+        N = len(want)
+        got = np.zeros(N, dtype=np.int32)
+        L.orc_systematic_resampling(P(ps), N, N, u, P(got))
+        assert np.array_equal(got, want), k
+
+
+def test_weights_path(L):
+    """normalize_probability + resample (ESS test, systematic resampling, child weights) on the same weights/uniform."""
+    g = np.load(os.path.join(G, "resampling.npz"))
+    for j in range(int(g["npaths"])):
+        w = g[f"p{j}_w"].copy()
+        N = len(w)
+        lnZ = L.orc_normalize(P(w), N)
+        assert lnZ == pytest.approx(float(g[f"p{j}_lnZ"]), rel=1e-13)
+        ps = np.zeros(N + 1)
+        ess = L.orc_ess_partial_sums(P(w), N, P(ps))
+        resampled = ess < 0.5 * N - 1e-6
+        assert int(resampled) == int(g[f"p{j}_resampled"])
+        if resampled:
+            counts = np.zeros(N, dtype=np.int32)
+            L.orc_systematic_resampling(P(ps), N, N, float(g[f"p{j}_u"]), P(counts))
+            assert np.array_equal(counts, g[f"p{j}_mult"])
+            # child weight = w_i * sum / (N * w_i) (particleContainer.cpp:350-351)
+            alive = counts > 0
+            wout = np.where(alive, w * (ps[N] / (N * np.where(alive, w, 1.0))), 0.0)
+            np.testing.assert_allclose(wout, g[f"p{j}_wout"], rtol=1e-13, atol=0)
+        else:
+            np.testing.assert_allclose(w, g[f"p{j}_wout"], rtol=1e-13, atol=0)
+
+
+def test_lagged_tallies(L):
+    g = np.load(os.path.join(G, "tallies.npz"))
+    for k in range(int(g["ncases"])):
+        N, E = int(g[f"t{k}_N"]), int(g[f"t{k}_E"])
+        evs = [(int(r), int(s), int(ty), int(e), int(c), x0, x1, opp) for (r, s, ty, e, c, x0, x1, opp) in g[f"t{k}_evs"]]
+        arr = _cases.rec_events_array(evs)
+        row_end, weights, anc = g[f"t{k}_row_end"], g[f"t{k}_weights"], g[f"t{k}_anc"]
+        out = np.zeros(6 * E)
+        L.orc_lagged_tallies(E, P(g[f"t{k}_lags"]), len(row_end), N, P(row_end), P(np.ascontiguousarray(weights)),
+                             P(np.ascontiguousarray(anc)), P(g[f"t{k}_w_final"]), float(g[f"t{k}_seqlen"]), arr,
+                             len(evs), P(out))
+        want = g[f"t{k}_tallies"].reshape(-1)
+        assert np.abs(want).sum() > 0
+        np.testing.assert_allclose(out, want, rtol=1e-12, atol=1e-300)
+
+
+def test_fastexp_branches(L):
+    # rational branch vs libm branch (particle.cpp:30-40)
+    for x in (-1e-9, -0.1, -0.7, -0.7184, -0.72, -5.0):
+        v = L.orc_fastexp(x)
+        if x * x < 0.516167859:
+            assert v == 1 + 2 * x / (2 - x + x * x / (6 + x * x * 0.1))
+            assert v == pytest.approx(np.exp(x), rel=2e-6)
+        else:
+            assert v == np.exp(x)
