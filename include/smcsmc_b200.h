@@ -1,0 +1,130 @@
+/* smcsmc_b200 -- C ABI of the B200-native SMCSMC particle-filter engine (libsmcgpu.so).
+ *
+ * The reference (luntergroup/smcsmc) has no in-process plugin API: its hot path is reached through the C++ classes
+ * ParticleContainer / ForestState / CountModel driven by pfARG_core (src/smcsmc.cpp:278-400).  This header is the
+ * boundary a maintainer binds instead of those classes; every entry point cites the reference call it replaces
+ * (paths relative to /root/reference/src).  INTEGRATION.md shows the replacement of pfARG_core's loop body.
+ *
+ * Conventions: plain C, no C++ types, no exceptions across the boundary.  All pointers are HOST memory; the library
+ * owns every device allocation and does the host<->device copies itself.  Functions return 0 on success and a
+ * non-zero smc_status otherwise; smc_last_error() returns the message of the last failure on the calling thread.
+ * One engine per chunk; an engine is not thread-safe (the reference is single-threaded as well).  Times are in
+ * generations, positions in bp, rates per bp per generation -- the units of scrm's Model (scrm/src/model.h:175-188).
+ * There is NO CPU fallback: every compute entry point fails with SMC_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef SMCSMC_B200_H
+#define SMCSMC_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SMC_MAX_HAPLOTYPES 32   /* n: local trees are flat arrays of 2n-1 nodes */
+#define SMC_MAX_EPOCHS 64
+
+typedef enum {
+  SMC_OK = 0,
+  SMC_ERR_ARG = 1,       /* invalid argument (message says which) */
+  SMC_ERR_CUDA = 2,      /* CUDA runtime / no usable device */
+  SMC_ERR_STATE = 3,     /* call out of order (e.g. sweep before rows were uploaded) */
+  SMC_ERR_NUMERIC = 4    /* zero or non-finite total weight (ParticleContainer::normalize_probability throws,
+                            particleContainer.cpp:428-429) */
+} smc_status;
+
+typedef struct smc_engine smc_engine;
+
+/* Flattened Model + PfParam of one sweep (single population; migration is a later row).
+ * Replaces: Model (scrm/src/model.h:55), PfParam (pfparam.hpp), CountModel::lags (count.hpp). */
+typedef struct {
+  int32_t n;                /* -nsam: haplotypes, 2..SMC_MAX_HAPLOTYPES */
+  int32_t N;                /* -Np: particles held by THIS engine (a shard when particles are split over GPUs) */
+  int32_t E;                /* number of epochs (Model::change_times_.size()) */
+  int32_t device;           /* CUDA device ordinal */
+  uint64_t seed;            /* -seed; Philox key */
+  uint32_t chunk;           /* RNG sub-stream id of this chunk (24 bits) */
+  uint32_t slot_offset;     /* global index of this engine's first particle (RNG slot = slot_offset + local index) */
+  double mu;                /* Model::mutation_rate() */
+  double rho;               /* Model::recombination_rate() */
+  double seqlen;            /* Model::loci_length() */
+  double start_pos;         /* initial_position of ParticleContainer (particleContainer.cpp:37) */
+  double ess_fraction;      /* -ESS (pfparam.cpp:323: ESSthreshold = N * ESS_fraction) */
+  int32_t ancestral_aware;  /* -ancestral_aware */
+  int32_t parity_scan;      /* 1: order-faithful sequential partial sums (particleContainer.cpp:256-262) so that
+                               offspring counts are bit-exact given the weights; 0: blocked parallel scan */
+  const double* t_start;    /* [E] epoch start times, t_start[0] = 0 */
+  const double* inv2N;      /* [E] 1/(2 N_e)  (Model::inv_double_pop_size) */
+  const double* vb_logfac;  /* [E] log(exp_digamma(c)/c) per epoch or NULL  (particle.cpp:65-74,266-272) */
+  const uint8_t* rec_mask;  /* [E] bit0 record recombination, bit1 record coalescence (pfparam.cpp:82-99) or NULL=3 */
+  const double* lags;       /* [E] CountModel::lags (count.cpp:230-264) */
+} smc_config;
+
+/* ---- engine life cycle -------------------------------------------------------------------------------------- */
+int smc_create(const smc_config* cfg, smc_engine** out);   /* ParticleContainer ctor minus the trees */
+void smc_destroy(smc_engine* e);
+const char* smc_last_error(void);
+const char* smc_version(void);
+
+/* Upload the rows of the .seg chunk (Segment, segdata.cpp:55-223) and derive the lagged-tally schedule
+ * (CountModel::extract_and_update_count's per-epoch update positions, count.cpp:363-385).
+ *   x_end[R]            segment_end() of each row, already clipped to seqlen (particleContainer.cpp:452)
+ *   alleles[R*n]        allelic_state_at_Segment_end: 0, 1, -1 missing, 2 unphased het (pairs)
+ *   is_site[R]          1 when segment_state == SEGMENT_INVARIANT (the row ends in a typed site)
+ *   max_rec_epoch[R]    max_epoch_to_update (smcsmc.cpp:266-275) or NULL (= E-1 everywhere) */
+int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, const uint8_t* is_site,
+                    const int32_t* max_rec_epoch, int64_t R);
+
+/* N prior trees at start_pos + first recombination positions + weights 1/N
+ * (ParticleContainer ctor particleContainer.cpp:33-65 -> Forest::buildInitialTree forest.cc:299-347). */
+int smc_init_particles(smc_engine* e);
+
+/* The hot loop of pfARG_core (smcsmc.cpp:328-361) for rows [row_begin, row_end): per row
+ *   extend_ARGs + update_weight_at_site + normalize_probability   (particleContainer.cpp:441-466)
+ *   CountModel::extract_and_update_count                          (count.cpp:355-415)
+ *   ParticleContainer::resample                                   (particleContainer.cpp:247-311)
+ * Asynchronous: returns after enqueueing; any getter synchronises. */
+int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end);
+
+/* End of data: final normalisation and flush of all pending tallies with lag 0 (smcsmc.cpp:371-373). */
+int smc_finish(smc_engine* e);
+
+/* ---- results ------------------------------------------------------------------------------------------------ */
+/* out[6*E]: coal_count, coal_opportunity, coal_weight, recomb_count, recomb_opportunity, recomb_weight per epoch,
+ * WITHOUT CountModel's initial pseudo-counts (count.cpp:161-193).  *_weight is sum(w^2 * opportunity). */
+int smc_get_tallies(smc_engine* e, double* out);
+int smc_get_lnZ(smc_engine* e, double* lnZ);                       /* ParticleContainer::ln_normalization_factor */
+/* counters[0] rows swept, [1] resampling events, [2] recombinations sampled, [3] numeric-error flag */
+int smc_get_counters(smc_engine* e, int64_t counters[4]);
+/* (position, ESS) of resampling events as PfParam::append_resample_file (pfparam.cpp:530-538); returns count via *n */
+int smc_get_resample_log(smc_engine* e, double* position, double* ess, int64_t cap, int64_t* n);
+/* particle state, AoS on the host side: parent[N*(2n-1)], height[N*(2n-1)], logw[N] (normalised), next_base[N] */
+int smc_get_particles(smc_engine* e, int32_t* parent, double* height, double* logw, double* next_base);
+int smc_set_particles(smc_engine* e, const int32_t* parent, const double* height, const double* logw,
+                      const double* next_base);
+/* ancestry of the last resampling event: anc[j] = slot (before) that slot j (after) was copied from; -1 if none yet */
+int smc_get_last_ancestry(smc_engine* e, int32_t* anc);
+/* device time spent in the engine's kernels since creation (CUDA events on the engine's stream), and launches */
+int smc_get_timing(smc_engine* e, double* kernel_ms, int64_t* launches);
+
+/* ---- stand-alone entry points (function-level parity; host buffers in, host buffers out) ---------------------- */
+/* ForestState::calculate_likelihood over phasings as ParticleContainer::update_weight_at_site
+ * (particle.cpp:625-680, particleContainer.cpp:138-224): lik[count], linear domain like the reference. */
+int smc_site_likelihood(int device, int32_t n, int64_t count, const int32_t* parent, const double* height,
+                        const int8_t* alleles, double mu, int32_t ancestral_aware, double* lik);
+/* ForestState::trackLocalTreeBranchLength and Forest::getLocalTreeLength (particle.cpp:699-730, forest.h:188) */
+int smc_branch_lengths(int device, int32_t n, int64_t count, const int32_t* parent, const double* height,
+                       const int8_t* alleles, double* with_data, double* total);
+/* ParticleContainer::systematic_resampling (particleContainer.cpp:474-504): counts[N] from partial_sum[N+1] and the
+ * uniform u; bit-exact with the reference. */
+int smc_systematic_offspring(int device, const double* partial_sum, int64_t N, double u, int32_t* counts);
+/* resample (particleContainer.cpp:247-311) from weights: partial sums (sequential when parity_scan) + ESS + counts */
+int smc_resample_counts(int device, const double* w, int64_t N, double u, int32_t parity_scan, double* ess,
+                        int32_t* counts);
+/* normalize_probability in log space (particleContainer.cpp:420-438): logw -= log(sum exp(logw)); returns lnZ, ESS */
+int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* ess);
+/* fastexp (particle.cpp:30-40) evaluated on the device, for the 1e-12 no-mutation-factor parity test */
+int smc_fastexp(int device, const double* x, int64_t count, double* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

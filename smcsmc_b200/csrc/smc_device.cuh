@@ -1,0 +1,403 @@
+// Device functions of the SMCSMC particle filter for sm_100a: one thread per particle, the particle's local tree
+// staged in shared memory ([node][thread] so that a warp touches consecutive banks).  Compiled with -fmad=false: the
+// arithmetic is operation-for-operation the reference's (an x86-64 build has no FMA contraction), which is what lets
+// the pruning likelihood and the no-mutation factor meet 1e-12 against the reference (they are in fact bit-identical).
+//
+// Reference behaviour restated here (paths under /root/reference/src):
+//   fastexp                         particle.cpp:30-40
+//   calculate_likelihood            particle.cpp:625-680   + phasing enumeration particleContainer.cpp:138-224
+//   trackLocalTreeBranchLength      particle.cpp:699-730
+//   extend_ARG                      particle.cpp:743-918
+//   sampleNextGenealogy (SMC')      scrm/src/forest.cc:423-598, time_interval.cc:84-134, forest.cc:601-756
+//   sampleNextBase                  particle.cpp:1195-1254
+//   record_all_event / record_recomb_extension / record_recomb_event   particle.cpp:193-390
+#pragma once
+#include <cstdint>
+#include <cfloat>
+#include <cmath>
+
+namespace smc {
+
+// ------------------------------------------------------------------------------------------------------------------
+// Philox4x32-10, counter = (block, slot, step, chunk | purpose << 24), key = seed.  Replaces the reference's single
+// global mt19937_64 (scrm/src/random/mersenne_twister.cc): streams differ by design, every (particle, row) has its own.
+// ------------------------------------------------------------------------------------------------------------------
+enum { RNG_INIT = 1, RNG_EXTEND = 2, RNG_RESAMPLE = 3, RNG_REDRAW = 4 };
+
+struct Rng {
+  uint32_t k0, k1, c0, c1, c2, c3;
+  double spare;
+  int have;
+};
+
+__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int round = 0; round < 10; round++) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0;
+    uint32_t hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__host__ __device__ inline double u53(uint32_t a, uint32_t b) {
+  // 53 random bits + half an ulp: strictly inside (0,1)
+  return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6) + 0.5) * (1.0 / 9007199254740992.0);
+}
+
+__host__ __device__ inline void rng_init(Rng& r, uint64_t seed, uint32_t slot, uint32_t step, uint32_t chunk,
+                                         uint32_t purpose) {
+  r.k0 = (uint32_t)seed; r.k1 = (uint32_t)(seed >> 32);
+  r.c0 = 0; r.c1 = slot; r.c2 = step; r.c3 = (chunk & 0xFFFFFFu) | (purpose << 24);
+  r.have = 0; r.spare = 0.0;
+}
+
+__host__ __device__ inline double rng_uniform(Rng& r) {
+  if (r.have) { r.have = 0; return r.spare; }
+  uint32_t o[4];
+  philox4x32_10(r.c0, r.c1, r.c2, r.c3, r.k0, r.k1, o);
+  r.c0++;
+  r.spare = u53(o[2], o[3]);
+  r.have = 1;
+  return u53(o[0], o[1]);
+}
+
+// particle.cpp:30-40 -- continued-fraction exp; same rational expression, no contraction
+__host__ __device__ inline double fastexp(double x) {
+  double xx = x * x;
+  if (xx < 0.516167859) return 1 + 2 * x / (2 - x + xx / (6 + xx * 0.1));
+  return exp(x);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Model constants shared by all threads (kernel parameter block; lives in the constant bank)
+// ------------------------------------------------------------------------------------------------------------------
+struct ModelDev {
+  int n, nn, E;
+  int ancestral_aware;
+  double mu, rho, seqlen;
+  double t_start[64];
+  double inv2N[64];
+  double vb_logfac[64];
+  unsigned char rec_mask[64];
+};
+
+// Per-thread view of the particle's tree in shared memory.
+struct TreeView {
+  double* H;          // [nn][BS]
+  signed char* PAR;   // [nn][BS]
+  double* L0;         // [nn][BS] scratch
+  double* L1;         // [nn][BS] scratch
+  double* LEN;        // [E][BS]  local branch length inside each epoch
+  int BS, t;
+  __device__ __forceinline__ double& h(int v) const { return H[v * BS + t]; }
+  __device__ __forceinline__ signed char& par(int v) const { return PAR[v * BS + t]; }
+  __device__ __forceinline__ double& l0(int v) const { return L0[v * BS + t]; }
+  __device__ __forceinline__ double& l1(int v) const { return L1[v * BS + t]; }
+  __device__ __forceinline__ double& len(int e) const { return LEN[e * BS + t]; }
+};
+
+// forest.h:188 getLocalTreeLength: sum of branch lengths in slot order (the order the parity tests assume)
+__device__ inline double tree_length(const ModelDev& m, const TreeView& T) {
+  double len = 0.0;
+  for (int v = 0; v < m.nn; v++) {
+    int p = T.par(v);
+    if (p >= 0) len += T.h(p) - T.h(v);
+  }
+  return len;
+}
+
+// particle.cpp:699-730 trackLocalTreeBranchLength: length of the subtree spanning the leaves that carry data.
+// Iterative form of the reference's recursion: nodes are visited children-first (leaves, then internal slots in
+// increasing height), each node hands its value to its parent; the lower-numbered child arrives first, which is the
+// reference's left/right order.
+__device__ inline double branch_length_with_data(const ModelDev& m, const TreeView& T, const signed char* data) {
+  const int n = m.n, nn = m.nn;
+  for (int v = n; v < nn; v++) { T.l0(v) = -2.0; T.l1(v) = -2.0; }   // -2 = child value not yet delivered
+  double total = 0.0;
+  for (int v = 0; v < nn; v++) {
+    double s;
+    if (v < n) {
+      s = data[v] >= 0 ? 0.0 : -1.0;
+    } else {
+      double sl = T.l0(v), sr = T.l1(v);
+      if (sl >= 0.0 && sr >= 0.0) { total = sl + sr; s = total; }
+      else if (sl >= 0.0) s = sl;
+      else s = sr;
+    }
+    int p = T.par(v);
+    if (p >= 0) {
+      double up = s;
+      if (up >= 0.0) up += T.h(p) - T.h(v);
+      if (T.l0(p) == -2.0) T.l0(p) = up; else T.l1(p) = up;
+    }
+  }
+  return total;
+}
+
+// particle.cpp:625-680: two-state Felsenstein pruning for one fully specified haplotype (0 / 1 / -1 missing).
+__device__ inline double prune_likelihood(const ModelDev& m, const TreeView& T, const signed char* hap) {
+  const int n = m.n, nn = m.nn;
+  for (int v = n; v < nn; v++) { T.l0(v) = 1.0; T.l1(v) = 1.0; }
+  double r0 = 1.0, r1 = 1.0;
+  for (int v = 0; v < nn; v++) {
+    double a0, a1;
+    if (v < n) {
+      int s = hap[v];
+      a0 = s == 1 ? 0.0 : 1.0;
+      a1 = s == 0 ? 0.0 : 1.0;
+    } else {
+      a0 = T.l0(v); a1 = T.l1(v);
+    }
+    int p = T.par(v);
+    if (p < 0) { r0 = a0; r1 = a1; continue; }
+    double t = T.h(p) - T.h(v);
+    double pr = fastexp(-t * m.mu);
+    double q = 1 - pr;
+    // 1.0 * x == x exactly, so the first child's factor is stored as is and the second multiplies it: (left)*(right)
+    T.l0(p) = T.l0(p) * (a0 * pr + a1 * q);
+    T.l1(p) = T.l1(p) * (a1 * pr + a0 * q);
+  }
+  double prior0 = m.ancestral_aware ? 1.0 : 0.5, prior1 = m.ancestral_aware ? 0.0 : 0.5;
+  return r0 * prior0 + r1 * prior1;
+}
+
+// particleContainer.cpp:138-181,204-221: mean likelihood over the 2^k phasings of the unphased het pairs (code 2).
+__device__ inline double site_likelihood(const ModelDev& m, const TreeView& T, const signed char* data) {
+  signed char hap[32];
+  const int n = m.n;
+  int ncfg = 1;
+  for (int i = 0; i < n; i++) hap[i] = data[i];
+  for (int i = 0; i + 1 < n; i += 2)
+    if (data[i] == 2) { ncfg *= 2; hap[i] = 0; hap[i + 1] = 1; }
+  double norm = 1.0 / ncfg, acc = 0.0;
+  for (;;) {
+    acc += prune_likelihood(m, T, hap);
+    if (ncfg <= 1) break;
+    bool advanced = false;
+    for (int i = 0; i + 1 < n; i += 2) {
+      if (data[i] != 2) continue;
+      if (hap[i] == 0) { hap[i] = 1; hap[i + 1] = 0; advanced = true; break; }
+      hap[i] = 0; hap[i + 1] = 1;
+    }
+    if (!advanced) break;
+  }
+  return acc * norm;
+}
+
+// Local branch length inside each epoch = recombination opportunity per bp (record_recomb_extension,
+// particle.cpp:305-357: sum over time slices of #lineages * slice length).  Internal slots are sorted by height and all
+// leaves sit at height 0, so the slice between consecutive internal nodes carries n, n-1, ... lineages.
+__device__ inline void epoch_tree_length(const ModelDev& m, const TreeView& T) {
+  const int n = m.n, E = m.E;
+  for (int e = 0; e < E; e++) T.len(e) = 0.0;
+  int e = 0;
+  double lo = 0.0;
+  int k = n;
+  for (int j = n; j < m.nn; j++) {
+    double hi = T.h(j);
+    while (e + 1 < E && m.t_start[e + 1] < hi) {
+      double b = m.t_start[e + 1];
+      if (b > lo) { T.len(e) += k * (b - lo); lo = b; }
+      e++;
+    }
+    if (hi > lo) T.len(e) += k * (hi - lo);
+    lo = hi;
+    k--;
+  }
+}
+
+__device__ inline int epoch_of(const ModelDev& m, double t) {
+  int e = 0;
+  while (e + 1 < m.E && m.t_start[e + 1] <= t) e++;
+  return e;
+}
+
+__device__ inline void swap_slots(const ModelDev& m, const TreeView& T, int a, int b) {
+  double th = T.h(a); T.h(a) = T.h(b); T.h(b) = th;
+  signed char tp = T.par(a); T.par(a) = T.par(b); T.par(b) = tp;
+  for (int v = 0; v < m.nn; v++) {
+    int p = T.par(v);
+    if (p == a) T.par(v) = (signed char)b;
+    else if (p == b) T.par(v) = (signed char)a;
+  }
+}
+
+// Sink for the tally records a move / a stretch produces (the content of the reference's EvolutionaryEvent records).
+// Implemented by the engine (lag-bucket ring in HBM) and by a null sink for the stand-alone kernels.
+struct NullSink {
+  __device__ void coal(int, double, int, double) const {}
+  __device__ void rec_event(int, double) const {}
+  __device__ void rec_opp(int, double, double, double) const {}
+};
+
+// One SMC' transition at position x (Forest::sampleNextGenealogy with exact window 0).  The test-side CPU restatement
+// consumes the same Philox draws in the same order, so the two can be compared draw for draw.
+template <class Sink>
+__device__ inline void smc_move(const ModelDev& m, const TreeView& T, Rng& r, double x, int max_rec_epoch, Sink& sink,
+                                double& logw) {
+  const int n = m.n, nn = m.nn;
+  // 1. recombination point, uniform on the local tree (forest.cc:370-412)
+  double tl = tree_length(m, T);
+  double target = rng_uniform(r) * tl;
+  int b = -1;
+  double hh = 0.0, cum = 0.0;
+  for (int v = 0; v < nn; v++) {
+    int p = T.par(v);
+    if (p < 0) continue;
+    double hv = T.h(v);
+    double bl = T.h(p) - hv;
+    b = v; hh = hv + (target - cum);
+    if (target < cum + bl) break;
+    cum += bl;
+  }
+  int Pn = T.par(b);
+  if (hh > T.h(Pn)) hh = T.h(Pn);
+  int e = epoch_of(m, hh);
+  if ((m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_event(e, x);
+  // 2. the cut lineage floats upwards (time_interval.cc:84-134, forest.cc:601-696)
+  const int root = nn - 1;                 // internal slots are height-sorted
+  const double hroot = T.h(root);
+  int c = n;                               // next internal slot above tt
+  while (c < nn && T.h(c) <= hh) c++;
+  double tt = hh, tc = 0.0;
+  int k = 0;
+  bool above_root = false;
+  for (;;) {
+    double tnode = DBL_MAX;
+    above_root = !(tt < hroot);
+    if (!above_root) { tnode = T.h(c); k = n - (c - n); }
+    else k = 1;
+    double tep = e + 1 < m.E ? m.t_start[e + 1] : DBL_MAX;
+    double tend = tnode < tep ? tnode : tep;
+    double rate = k * m.inv2N[e];
+    double w = -log(rng_uniform(r)) / rate;
+    tc = tt + w;
+    bool coal = tc < tend;
+    double dt = (coal ? tc : tend) - tt;
+    if ((m.rec_mask[e] & 2) && e <= max_rec_epoch) sink.coal(e, x, coal ? 1 : 0, k * dt);
+    if (coal) break;
+    tt = tend;
+    if (tend == tep) e++;
+    if (!above_root && tend == tnode) c++;
+  }
+  logw += m.vb_logfac[e];
+  // 3. target among the k contemporaries (contemporaries_container.h:343-365) and 4. surgery; the unary node left at
+  // the cut is pruned (forest.cc:1245-1257): the parent slot of the cut branch becomes the new coalescence node.
+  int S = -1;
+  for (int v = 0; v < nn; v++) if (T.par(v) == Pn && v != b) S = v;
+  if (above_root) {
+    if (Pn != root) {
+      T.par(S) = T.par(Pn);
+      T.par(root) = (signed char)Pn;
+      T.par(Pn) = -1;
+    }
+    T.h(Pn) = tc;
+  } else {
+    int idx = (int)(rng_uniform(r) * k);
+    if (idx >= k) idx = k - 1;
+    int Tg = -1;
+    for (int v = 0; v < nn; v++) {
+      int p = T.par(v);
+      if (p >= 0 && T.h(v) <= tt && tt < T.h(p)) { if (idx == 0) { Tg = v; break; } idx--; }
+    }
+    if (Tg == b) {
+      // back-coalescence into the stub: tree unchanged (SMC')
+    } else if (Tg == S || Tg == Pn) {
+      T.h(Pn) = tc;
+    } else {
+      T.par(S) = T.par(Pn);
+      T.par(Pn) = T.par(Tg);
+      T.par(Tg) = (signed char)Pn;
+      T.h(Pn) = tc;
+    }
+  }
+  int s = Pn;
+  while (s + 1 < nn && T.h(s + 1) < T.h(s)) { swap_slots(m, T, s, s + 1); s++; }
+  while (s - 1 >= n && T.h(s - 1) > T.h(s)) { swap_slots(m, T, s, s - 1); s--; }
+}
+
+// particle.cpp:1195-1254 with multiplicity 1 and one rho segment; forest.h:140-151 for the re-draw after resampling
+__device__ inline double draw_next_base(const ModelDev& m, double tree_len, Rng& r, double from) {
+  double rate = m.rho * tree_len;
+  double len = -log(rng_uniform(r)) / rate;
+  double next = from + len;
+  if (next == from) next = nextafter(from, from * 2);
+  if (!(next < m.seqlen)) next = m.seqlen;
+  return next;
+}
+
+// ForestState::extend_ARG for one row (x0, x1] with alleles data[n], followed by update_weight_at_site when is_site.
+// Returns the number of recombinations sampled.
+template <class Sink>
+__device__ inline int extend_row(const ModelDev& m, const TreeView& T, Rng& r, double x0, double x1,
+                                 const signed char* data, int is_site, int max_rec_epoch, Sink& sink, double& logw,
+                                 double& next_base) {
+  const int n = m.n;
+  int nmiss = 0;
+  for (int i = 0; i < n; i++) nmiss += data[i] == -1;
+  const int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);   // particleContainer.cpp:103-111
+  double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tree_length(m, T) : branch_length_with_data(m, T, data);
+  epoch_tree_length(m, T);
+  double updated_to = x0;
+  int nrec = 0;
+  while (updated_to < x1) {
+    double new_to = x1 < next_base ? x1 : next_base;
+    logw += log(fastexp(-m.mu * L_obs * (new_to - updated_to)));     // particle.cpp:770
+    for (int e = 0; e < m.E; e++) {
+      double le = T.len(e);
+      if (le > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, updated_to, new_to, le);
+    }
+    updated_to = new_to;
+    if (updated_to < x1) {
+      smc_move(m, T, r, updated_to, max_rec_epoch, sink, logw);
+      nrec++;
+      if (leaf_status == 0) L_obs = branch_length_with_data(m, T, data);
+      if (leaf_status == 1) L_obs = tree_length(m, T);
+      epoch_tree_length(m, T);
+      next_base = draw_next_base(m, tree_length(m, T), r, updated_to);
+    }
+  }
+  if (is_site) logw += log(site_likelihood(m, T, data));
+  return nrec;
+}
+
+// Prior tree at the left end (forest.cc:299-347): Kingman coalescent under piecewise-constant epochs; mirrors
+// the test-side CPU restatement draw for draw.
+__device__ inline void init_tree(const ModelDev& m, const TreeView& T, Rng& r) {
+  const int n = m.n, nn = m.nn;
+  signed char active[32];
+  for (int i = 0; i < n; i++) { active[i] = (signed char)i; T.h(i) = 0.0; }
+  for (int v = 0; v < nn; v++) T.par(v) = -1;
+  int k = n, e = 0, next_slot = n;
+  double t = 0.0;
+  while (k > 1) {
+    double pairs = 0.5 * k * (k - 1);
+    double rate = pairs * m.inv2N[e];
+    double w = -log(rng_uniform(r)) / rate;
+    double tend = e + 1 < m.E ? m.t_start[e + 1] : DBL_MAX;
+    if (t + w < tend) {
+      t += w;
+      int idx = (int)(rng_uniform(r) * pairs);
+      if (idx >= (int)pairs) idx = (int)pairs - 1;
+      int i = 0;
+      while (idx >= k - 1 - i) { idx -= k - 1 - i; i++; }
+      int j = i + 1 + idx;
+      T.h(next_slot) = t;
+      T.par(active[i]) = (signed char)next_slot;
+      T.par(active[j]) = (signed char)next_slot;
+      active[i] = (signed char)next_slot;
+      active[j] = active[k - 1];
+      next_slot++; k--;
+    } else {
+      t = tend; e++;
+    }
+  }
+}
+
+}  // namespace smc

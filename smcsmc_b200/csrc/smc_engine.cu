@@ -1,0 +1,1202 @@
+// libsmcgpu.so -- B200-native SMCSMC particle-filter engine: kernels + the C ABI of include/smcsmc_b200.h.
+//
+// One kernel launch per .seg row does everything the reference's pfARG_core loop body does (smcsmc.cpp:328-361):
+//   phase 0  lagged tallies due after the previous row (CountModel::extract_and_update_count, count.cpp:355-415)
+//   phase 1  if the previous row triggered resampling: systematic offspring assignment + gather of the parent's state
+//            (ParticleContainer::resample / systematic_resampling / implement_resampling, particleContainer.cpp:247-392)
+//   phase 2  extend_ARG over the row, no-mutation factor, SMC' moves, tally records, pruning likelihood at the site
+//            (particle.cpp:743-918, forest.cc:423-598, particle.cpp:625-680)
+//   phase 3  log-sum-exp partials per block; the LAST block to arrive combines them: ln normaliser, ESS, resampling
+//            decision, the exact u_j chain of the systematic sampler (normalize_probability :420-438, resample :256-270)
+// Nothing returns to the host inside the sweep: the resampling decision, the buffer flip and the row counter live in a
+// device-side control block, so the R launches of a chunk are identical and queue back to back on one stream.
+//
+// HBM layout (structure of arrays, particle index fastest => every warp access is coalesced):
+//   height  [n-1][N] f64   internal-node heights (leaves sit at 0), slots height-sorted
+//   parent  [2n-1][N] i8
+//   logw[N], next_base[N] f64
+//   ring    [E][B][4][N] f64   lag buckets of pending tallies: coal count, coal opp, recomb count, recomb opp
+// all of it twice (ping-pong: resampling gathers from one copy into the other).
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/smcsmc_b200.h"
+#include "smc_device.cuh"
+
+using namespace smc;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CUDA_TRY(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return fail(SMC_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(_e)); } while (0)
+
+constexpr int MAXSEG = 160;
+
+struct USeg { long long j0; double u0; double step; };   // u_j = u0 + (j - j0) * step for j in [j0, next j0)
+
+struct Ctrl {
+  long long row;            // next row to process
+  int cur;                  // which copy of the state is current
+  int resampled;            // the row just finished asked for resampling: the next launch pulls offspring
+  double lse;               // ln normaliser of the last row; stored log-weights are un-normalised by this
+  double lnZ;
+  double norm;              // last partial sum (== total normalised weight)
+  double child_logw;        // log(norm / N): weight of every offspring (particleContainer.cpp:350-351)
+  double resample_pos;      // row end at which the resampling was decided (offspring re-draw from here)
+  long long resample_row;
+  long long cons_done;      // row whose leading tally consumption has already been done (by a materialise pass)
+  unsigned int ticket;
+  int err;
+  long long n_resample, n_recomb;
+  int nseg;
+  USeg seg[MAXSEG];
+};
+
+struct StateBuf {
+  double* height;       // [n-1][N]
+  signed char* parent;  // [nn][N]
+  double* logw;
+  double* next_base;
+  double* ring;         // [E*B*4][N]
+};
+
+struct Params {
+  ModelDev m;
+  int N, B, parity_scan, nblocks;
+  uint64_t seed;
+  uint32_t chunk, slot_offset;
+  double ess_fraction, start_pos;
+  StateBuf buf[2];
+  Ctrl* ctrl;
+  // rows
+  long long R;
+  const double* x_end;
+  const signed char* alleles;
+  const unsigned char* is_site;
+  const int* max_rec;
+  const int* kstart;       // [R][E] bucket index at the row's left end
+  const int* ub_off;       // [E+1]
+  const double* ub;        // bucket upper bounds per epoch (last = +inf: the end-of-data bucket)
+  const int* cons_off;     // [R+1]
+  const int2* cons;        // (epoch, bucket) pairs due after each row
+  // per-row weight partials, double-buffered by row parity
+  double* local_cum[2];    // [N] inclusive prefix of exp(logw - bmax) inside the block
+  double* bmax[2];
+  double* bsum[2];
+  double* bsq[2];
+  double* boff[2];         // [nblocks+1] exclusive prefix of normalised block totals
+  double* bscale[2];
+  double* psum;            // [N+1] parity-mode sequential partial sums
+  double* tallies;         // [6][E]
+  int* anc;                // [N] ancestry of the last resampling
+  double* rs_pos; double* rs_ess; long long rs_cap;
+};
+
+// Tally sink writing into the particle's lag-bucket ring.
+struct RingSink {
+  const Params* P;
+  double* ring;    // destination copy
+  int i;           // particle index
+  const int* ks;   // kstart of this row [E]
+  __device__ __forceinline__ int bucket(int e, double x) const {
+    int k = ks[e];
+    const double* ub = P->ub + P->ub_off[e];
+    while (ub[k] <= x) k++;          // last bound is +inf
+    return k;
+  }
+  __device__ __forceinline__ double* cell(int e, int k, int q) const {
+    return ring + ((size_t)((e * P->B + (k % P->B)) * 4 + q)) * P->N + i;
+  }
+  __device__ void coal(int e, double x, int cnt, double opp) const {
+    int k = bucket(e, x);
+    if (cnt) *cell(e, k, 0) += 1.0;
+    *cell(e, k, 1) += opp;
+  }
+  __device__ void rec_event(int e, double x) const { *cell(e, bucket(e, x), 2) += 1.0; }
+  __device__ void rec_opp(int e, double xa, double xb, double rate) const {
+    int k = bucket(e, xa);
+    const double* ub = P->ub + P->ub_off[e];
+    while (xa < xb) {
+      double bend = ub[k] < xb ? ub[k] : xb;
+      *cell(e, k, 3) += rate * (bend - xa);
+      xa = bend;
+      k++;
+    }
+  }
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// normalised cumulative weight c_i = P_{i+1} (un-divided) of particle i after row parity p
+__device__ __forceinline__ double cum_at(const Params& P, int p, long long i, int bs) {
+  if (P.parity_scan) return P.psum[i + 1];
+  int b = (int)(i / bs);
+  double v = P.boff[p][b] + __ldcg(P.local_cum[p] + i) * P.bscale[p][b];
+  double cap = P.boff[p][b + 1];
+  return v < cap ? v : cap;
+}
+
+__device__ __forceinline__ double u_at(const Ctrl* c, long long j) {
+  int lo = 0, hi = c->nseg - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (c->seg[mid].j0 <= j) lo = mid; else hi = mid - 1;
+  }
+  return c->seg[lo].u0 + (double)(j - c->seg[lo].j0) * c->seg[lo].step;
+}
+
+// parent of offspring j: the first interval i with c_i / norm > u_j (particleContainer.cpp:474-504)
+__device__ __forceinline__ long long parent_of(const Params& P, int p, double uj, double norm, int bs) {
+  long long lo = 0, hi = P.N;   // count of i with c_i/norm <= uj
+  while (lo < hi) {
+    long long mid = (lo + hi) >> 1;
+    if (cum_at(P, p, mid, bs) / norm > uj) hi = mid; else lo = mid + 1;
+  }
+  return lo < P.N ? lo : P.N - 1;
+}
+
+// The exact chain u_0 = U/N, u_{j+1} = fl(u_j + 1/N) (particleContainer.cpp:479,494) in closed form: inside a binade
+// repeated addition of d advances by a constant multiple of the ulp (after at most one tie-resolving step), so the
+// chain is piecewise an exact arithmetic progression.  One thread builds the <= 2*log2(N)+O(1) pieces.
+__device__ void build_u_chain(Ctrl* c, double U, long long N) {
+  const double d = 1.0 / (double)N;
+  double u = U / (double)N;
+  long long j = 0;
+  int ns = 0;
+  while (j < N && ns < MAXSEG - 2) {
+    c->seg[ns].j0 = j; c->seg[ns].u0 = u; c->seg[ns].step = 0.0; ns++;    // element j on its own
+    double u1 = u + d;
+    if (j + 1 >= N) { j++; break; }
+    int e0, e1, e2;
+    frexp(u, &e0); frexp(u1, &e1);
+    double u2 = u1 + d;
+    frexp(u2, &e2);
+    if (e0 != e1 || e1 != e2 || u <= 0.0) { j++; u = u1; continue; }
+    double s = u2 - u1;                 // exact: same binade
+    double ulp = ldexp(1.0, e1 - 53);   // u1 in [2^(e1-1), 2^e1)
+    double top = ldexp(1.0, e1);
+    // number of elements u1 + i*s (i >= 0) below the top of the binade; all quantities are integer multiples of ulp
+    unsigned long long room = (unsigned long long)((top - u1) / ulp);
+    unsigned long long si = (unsigned long long)(s / ulp);
+    if (si == 0) { j++; u = u1; continue; }
+    long long cnt = (long long)((room + si - 1) / si);
+    if (cnt > N - (j + 1)) cnt = N - (j + 1);
+    if (cnt < 1) { j++; u = u1; continue; }
+    c->seg[ns].j0 = j + 1; c->seg[ns].u0 = u1; c->seg[ns].step = s; ns++;
+    double ulast = u1 + (double)(cnt - 1) * s;
+    j = j + 1 + cnt;
+    u = ulast + d;
+  }
+  // (cannot happen for N < 2^52) fall back to explicit steps being cut short: extend the last piece
+  c->nseg = ns;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// the row kernel
+// ---------------------------------------------------------------------------------------------------------------
+// mode 0: one row; mode 1: materialise only (apply pending normalisation / resampling, no extension, no finalise)
+__global__ void __launch_bounds__(128)
+smc_row_kernel(const __grid_constant__ Params P, int mode) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int BS = blockDim.x, t = threadIdx.x;
+  const ModelDev& m = P.m;
+  const int n = m.n, nn = m.nn, E = m.E;
+  TreeView T;
+  T.BS = BS; T.t = t;
+  T.H = reinterpret_cast<double*>(smem_raw);
+  T.L0 = T.H + (size_t)nn * BS;
+  T.L1 = T.L0 + (size_t)nn * BS;
+  T.LEN = T.L1 + (size_t)nn * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.LEN + (size_t)E * BS);
+  __shared__ double red[3][4];
+  __shared__ double tal[6][4];
+  __shared__ bool is_last;
+
+  Ctrl* c = P.ctrl;
+  const long long row = c->row;
+  if (mode == 0 && row >= P.R) return;
+  const int cur = c->cur;
+  const int resampled = c->resampled;
+  const double lse = c->lse;
+  const int pprev = (int)((row + 1) & 1);     // parity of the previous row's partials
+  const int pnow = (int)(row & 1);
+  const long long i = (long long)blockIdx.x * BS + t;
+  const bool live = i < P.N;
+  const StateBuf& src = P.buf[cur];
+  const StateBuf& dst = P.buf[resampled ? cur ^ 1 : cur];
+  const int warp = t >> 5, lane = t & 31, nwarp = BS >> 5;
+
+  // ---- phase 0: tallies due after the previous row, weighted with the previous row's normalised weights ----------
+  int c0 = 0, c1 = 0;
+  if (row > 0 && c->cons_done != row) { c0 = P.cons_off[row - 1]; c1 = P.cons_off[row]; }
+  for (int q = c0; q < c1; q++) {
+    int2 ek = P.cons[q];
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    if (live) {
+      double w = exp(src.logw[i] - lse);
+      const double* cell = src.ring + ((size_t)((ek.x * P.B + (ek.y % P.B)) * 4)) * P.N + i;
+      double cc = cell[0], co = cell[(size_t)P.N], rc = cell[(size_t)2 * P.N], ro = cell[(size_t)3 * P.N];
+      v[0] = w * cc; v[1] = w * co; v[2] = w * w * co; v[3] = w * rc; v[4] = w * ro; v[5] = w * w * ro;
+    }
+    for (int a = 0; a < 6; a++) { v[a] = warp_sum(v[a]); if (lane == 0) tal[a][warp] = v[a]; }
+    __syncthreads();
+    if (t < 6) {
+      double s = 0;
+      for (int w = 0; w < nwarp; w++) s += tal[t][w];
+      if (s != 0.0) atomicAdd(P.tallies + t * E + ek.x, s);
+    }
+    __syncthreads();
+  }
+
+  // ---- phase 1: load own state, or pull the parent's after a resampling ---------------------------------------
+  double logw = 0.0, next_base = 0.0;
+  long long a = i;
+  bool redraw = false;
+  if (live) {
+    if (resampled) {
+      const double norm = c->norm;
+      double uj = u_at(c, i);
+      a = parent_of(P, pprev, uj, norm, BS);
+      // did the parent get more than one offspring?  (then every copy re-draws its next recombination position,
+      // particleContainer.cpp:357-367 / forest.h:140-151)
+      if (i > 0) {
+        double up = u_at(c, i - 1);
+        if (a == 0 || !(cum_at(P, pprev, a - 1, BS) / norm > up)) redraw = true;
+      }
+      if (!redraw && i + 1 < P.N) {
+        double un = u_at(c, i + 1);
+        if (a == P.N - 1 || cum_at(P, pprev, a, BS) / norm > un) redraw = true;
+      }
+      P.anc[i] = (int)a;
+      logw = c->child_logw;
+    } else {
+      logw = src.logw[i] - lse;
+    }
+    next_base = src.next_base[a];
+    for (int v = 0; v < n; v++) T.h(v) = 0.0;
+    for (int v = n; v < nn; v++) T.h(v) = src.height[(size_t)(v - n) * P.N + a];
+    for (int v = 0; v < nn; v++) T.par(v) = src.parent[(size_t)v * P.N + a];
+    // ring: gather everything on a pull; consumed buckets are cleared either way
+    if (resampled) {
+      const int cells = E * P.B * 4;
+      for (int q = 0; q < cells; q++) dst.ring[(size_t)q * P.N + i] = src.ring[(size_t)q * P.N + a];
+    }
+    for (int q = c0; q < c1; q++) {
+      int2 ek = P.cons[q];
+      double* cell = dst.ring + ((size_t)((ek.x * P.B + (ek.y % P.B)) * 4)) * P.N + i;
+      cell[0] = 0.0; cell[(size_t)P.N] = 0.0; cell[(size_t)2 * P.N] = 0.0; cell[(size_t)3 * P.N] = 0.0;
+    }
+    if (redraw) {
+      Rng rr;
+      rng_init(rr, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)c->resample_row, P.chunk, RNG_REDRAW);
+      next_base = draw_next_base(m, tree_length(m, T), rr, c->resample_pos);
+    }
+  }
+
+  // ---- phase 2: the row ----------------------------------------------------------------------------------------
+  int nrec = 0;
+  if (live && mode == 0) {
+    const double x0 = row > 0 ? P.x_end[row - 1] : P.start_pos;
+    const double x1 = P.x_end[row];
+    signed char data[32];
+    for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
+    Rng r;
+    rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
+    RingSink sink{&P, dst.ring, (int)i, P.kstart + row * E};
+    nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
+  }
+
+  // ---- phase 3: store, weight partials, last block finalises ----------------------------------------------------
+  if (live) {
+    dst.logw[i] = logw;
+    dst.next_base[i] = next_base;
+    if (resampled || mode == 0) {
+      for (int v = n; v < nn; v++) dst.height[(size_t)(v - n) * P.N + i] = T.h(v);
+      for (int v = 0; v < nn; v++) dst.parent[(size_t)v * P.N + i] = T.par(v);
+    }
+  }
+  if (mode != 0) return;
+
+  // block max, then inclusive scan of exp(logw - max) and the sum of squares
+  double mx = warp_max(live ? logw : -DBL_MAX);
+  if (lane == 0) red[0][warp] = mx;
+  __syncthreads();
+  mx = red[0][0];
+  for (int w = 1; w < nwarp; w++) mx = fmax(mx, red[0][w]);
+  double ex = live ? exp(logw - mx) : 0.0;
+  double incl = ex;
+  for (int o = 1; o < 32; o <<= 1) {
+    double y = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += y;
+  }
+  double sq = warp_sum(ex * ex);
+  __syncthreads();
+  if (lane == 31) red[1][warp] = incl;
+  if (lane == 0) red[2][warp] = sq;
+  __syncthreads();
+  double woff = 0.0, btot = 0.0, bsq = 0.0;
+  for (int w = 0; w < nwarp; w++) {
+    if (w < warp) woff += red[1][w];
+    btot += red[1][w];
+    bsq += red[2][w];
+  }
+  if (live) P.local_cum[pnow][i] = woff + incl;
+  int nr = warp_sum((double)nrec) + 0.5;
+  if (lane == 0 && nr > 0) atomicAdd((unsigned long long*)&c->n_recomb, (unsigned long long)nr);
+  if (t == 0) {
+    P.bmax[pnow][blockIdx.x] = mx;
+    P.bsum[pnow][blockIdx.x] = btot;
+    P.bsq[pnow][blockIdx.x] = bsq;
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) {
+    unsigned int tk = atomicAdd(&c->ticket, 1u);
+    is_last = (tk == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+
+  // ---- finalise (one block): ln normaliser, ESS, block offsets, resampling decision -----------------------------
+  const int nb = gridDim.x;
+  double* sh = reinterpret_cast<double*>(smem_raw);   // tree staging is dead now: reuse it
+  double gm = -DBL_MAX;
+  for (int b = t; b < nb; b += BS) gm = fmax(gm, __ldcg(P.bmax[pnow] + b));
+  gm = warp_max(gm);
+  if (lane == 0) red[0][warp] = gm;
+  __syncthreads();
+  gm = red[0][0];
+  for (int w = 1; w < nwarp; w++) gm = fmax(gm, red[0][w]);
+  double S = 0.0, Q = 0.0;
+  for (int b = t; b < nb; b += BS) {
+    double f = exp(__ldcg(P.bmax[pnow] + b) - gm);
+    S += __ldcg(P.bsum[pnow] + b) * f;
+    Q += __ldcg(P.bsq[pnow] + b) * f * f;
+  }
+  S = warp_sum(S); Q = warp_sum(Q);
+  __syncthreads();
+  if (lane == 0) { red[1][warp] = S; red[2][warp] = Q; }
+  __syncthreads();
+  S = 0.0; Q = 0.0;
+  for (int w = 0; w < nwarp; w++) { S += red[1][w]; Q += red[2][w]; }
+  const double new_lse = gm + log(S);
+  const double ess = S * S / Q;
+  // exclusive prefix over blocks of the normalised block totals: each thread owns a contiguous run of blocks
+  const int per = (nb + BS - 1) / BS;
+  const int b0 = t * per, b1 = min(nb, b0 + per);
+  double run = 0.0;
+  for (int b = b0; b < b1; b++) {
+    double sc = exp(__ldcg(P.bmax[pnow] + b) - new_lse);
+    P.bscale[pnow][b] = sc;
+    run += __ldcg(P.bsum[pnow] + b) * sc;
+  }
+  sh[t] = run;
+  __syncthreads();
+  if (t == 0) {
+    double accu = 0.0;
+    for (int k = 0; k < BS; k++) { double v = sh[k]; sh[k] = accu; accu += v; }
+    sh[BS] = accu;
+  }
+  __syncthreads();
+  run = sh[t];
+  for (int b = b0; b < b1; b++) {
+    P.boff[pnow][b] = run;
+    run += __ldcg(P.bsum[pnow] + b) * P.bscale[pnow][b];
+  }
+  if (t == 0) P.boff[pnow][nb] = sh[BS];
+  __syncthreads();
+  if (t == 0) {
+    double norm = sh[BS];
+    const StateBuf& now = dst;
+    if (P.parity_scan) {
+      // order-faithful partial sums (particleContainer.cpp:256-262): left to right, one thread
+      double acc = 0.0;
+      for (long long k = 0; k < P.N; k++) { P.psum[k] = acc; acc += exp(__ldcg(now.logw + k) - new_lse); }
+      P.psum[P.N] = acc;
+      norm = acc;
+    }
+    if (!(S > 0.0) || !isfinite(new_lse)) c->err = 1;
+    c->lnZ += new_lse;
+    c->lse = new_lse;
+    const bool rs = ess < (double)P.N * P.ess_fraction - 1e-6;    // particleContainer.cpp:281
+    if (resampled) c->cur = cur ^ 1;
+    c->resampled = rs ? 1 : 0;
+    if (rs) {
+      Rng rr;
+      rng_init(rr, P.seed, 0, (uint32_t)row, P.chunk, RNG_RESAMPLE);
+      double U = rng_uniform(rr);
+      build_u_chain(c, U, P.N);
+      c->norm = norm;
+      c->child_logw = log(norm / (double)P.N);
+      c->resample_pos = P.x_end[row];
+      c->resample_row = row;
+      if (c->n_resample < P.rs_cap) { P.rs_pos[c->n_resample] = P.x_end[row]; P.rs_ess[c->n_resample] = ess; }
+      c->n_resample++;
+    }
+    c->ticket = 0;
+    c->row = row + 1;
+  }
+}
+
+// commit of a materialise-only pass
+__global__ void smc_commit_kernel(Ctrl* c) {
+  c->cons_done = c->row;
+  if (c->resampled) c->cur ^= 1;
+  c->resampled = 0;
+  c->lse = 0.0;
+}
+
+// end of data: every pending bucket is weighted with the final normalised weights (smcsmc.cpp:371-373, lag 0)
+__global__ void __launch_bounds__(128) smc_flush_kernel(const __grid_constant__ Params P, const int* first_pending) {
+  __shared__ double tal[6][4];
+  Ctrl* c = P.ctrl;
+  const int BS = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarp = BS >> 5;
+  const long long i = (long long)blockIdx.x * BS + t;
+  const bool live = i < P.N;
+  const StateBuf& src = P.buf[c->cur];
+  const int E = P.m.E;
+  double w = live ? exp(src.logw[i] - c->lse) : 0.0;
+  for (int e = 0; e < E; e++) {
+    int nbk = P.ub_off[e + 1] - P.ub_off[e];
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = first_pending[e]; k < nbk; k++) {
+      if (live) {
+        double* cell = src.ring + ((size_t)((e * P.B + (k % P.B)) * 4)) * P.N + i;
+        double cc = cell[0], co = cell[(size_t)P.N], rc = cell[(size_t)2 * P.N], ro = cell[(size_t)3 * P.N];
+        v[0] += w * cc; v[1] += w * co; v[2] += w * w * co; v[3] += w * rc; v[4] += w * ro; v[5] += w * w * ro;
+        cell[0] = 0.0; cell[(size_t)P.N] = 0.0; cell[(size_t)2 * P.N] = 0.0; cell[(size_t)3 * P.N] = 0.0;
+      }
+    }
+    for (int a = 0; a < 6; a++) { v[a] = warp_sum(v[a]); if (lane == 0) tal[a][warp] = v[a]; }
+    __syncthreads();
+    if (t < 6) {
+      double s = 0;
+      for (int ww = 0; ww < nwarp; ww++) s += tal[t][ww];
+      if (s != 0.0) atomicAdd(P.tallies + t * E + e, s);
+    }
+    __syncthreads();
+  }
+}
+
+// prior trees + first recombination position + weight 1/N (particleContainer.cpp:33-65)
+__global__ void __launch_bounds__(128) smc_init_kernel(const __grid_constant__ Params P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int BS = blockDim.x, t = threadIdx.x;
+  const ModelDev& m = P.m;
+  const int n = m.n, nn = m.nn;
+  TreeView T;
+  T.BS = BS; T.t = t;
+  T.H = reinterpret_cast<double*>(smem_raw);
+  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.LEN + (size_t)m.E * BS);
+  const long long i = (long long)blockIdx.x * BS + t;
+  if (i >= P.N) return;
+  Rng r;
+  rng_init(r, P.seed, P.slot_offset + (uint32_t)i, 0, P.chunk, RNG_INIT);
+  init_tree(m, T, r);
+  double nb = draw_next_base(m, tree_length(m, T), r, P.start_pos);
+  const StateBuf& d = P.buf[0];
+  for (int v = n; v < nn; v++) d.height[(size_t)(v - n) * P.N + i] = T.h(v);
+  for (int v = 0; v < nn; v++) d.parent[(size_t)v * P.N + i] = T.par(v);
+  d.logw[i] = -log((double)P.N);
+  d.next_base[i] = nb;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// stand-alone kernels (function-level parity entry points)
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long count, const int* parent,
+                                                        const double* height, const signed char* alleles, int what,
+                                                        double* out0, double* out1) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int BS = blockDim.x, t = threadIdx.x;
+  const int n = m.n, nn = m.nn;
+  TreeView T;
+  T.BS = BS; T.t = t;
+  T.H = reinterpret_cast<double*>(smem_raw);
+  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.LEN + (size_t)m.E * BS);
+  const long long i = (long long)blockIdx.x * BS + t;
+  if (i >= count) return;
+  for (int v = 0; v < nn; v++) { T.h(v) = height[i * nn + v]; T.par(v) = (signed char)parent[i * nn + v]; }
+  signed char data[32];
+  for (int k = 0; k < n; k++) data[k] = alleles[i * n + k];
+  if (what == 0) {
+    out0[i] = site_likelihood(m, T, data);
+  } else {
+    out0[i] = branch_length_with_data(m, T, data);
+    out1[i] = tree_length(m, T);
+  }
+}
+
+__global__ void k_fastexp(const double* x, long long count, double* out) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) out[i] = fastexp(x[i]);
+}
+
+__global__ void k_build_chain(Ctrl* c, double U, long long N) { build_u_chain(c, U, N); }
+
+// sequential partial sums + ESS on one thread (parity mode), or taken as given
+__global__ void k_seq_partial_sums(const double* w, long long N, double* psum, double* ess) {
+  double acc = 0.0;
+  for (long long k = 0; k < N; k++) { psum[k] = acc; acc += w[k]; }
+  psum[N] = acc;
+  double scaling = 1.0 / acc, sq = 0.0;
+  for (long long k = 0; k < N; k++) sq += (w[k] * scaling) * (w[k] * scaling);
+  *ess = 1.0 / sq;
+}
+
+// blocked scan variant of the above (three tiny kernels folded into one single-block kernel; test sizes only)
+__global__ void __launch_bounds__(1024) k_par_partial_sums(const double* w, long long N, double* psum, double* ess) {
+  __shared__ double part[1024];
+  __shared__ double sqp[1024];
+  const int t = threadIdx.x, BS = blockDim.x;
+  const long long per = (N + BS - 1) / BS, b0 = t * per, b1 = min(N, b0 + per);
+  double run = 0.0, sq = 0.0;
+  for (long long k = b0; k < b1; k++) { run += w[k]; sq += w[k] * w[k]; }
+  part[t] = run; sqp[t] = sq;
+  __syncthreads();
+  if (t == 0) {
+    double acc = 0.0, q = 0.0;
+    for (int k = 0; k < BS; k++) { double v = part[k]; part[k] = acc; acc += v; q += sqp[k]; }
+    psum[N] = acc;
+    *ess = acc * acc / q;
+  }
+  __syncthreads();
+  run = part[t];
+  for (long long k = b0; k < b1; k++) { psum[k] = run; run += w[k]; }
+}
+
+// offspring counts from partial sums: count_i = #{ j : parent(j) == i }, by two binary searches over the exact u chain
+__global__ void k_offspring_counts(const Ctrl* c, const double* psum, long long N, int* counts) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const double norm = psum[N];
+  // first j with u_j >= c_{i-1}/norm ... offspring of i are the j with c_{i-1}/norm <= u_j < c_i/norm, where
+  // "c_i/norm > u_j" is the reference's comparison
+  auto first_not_below = [&](double bound, bool last) -> long long {   // #{ j : !(bound > u_j) } complement count
+    // returns number of j with bound > u_j  (u_j increasing)
+    if (last) return N;   // the reference's loop assigns every remaining sample to the last interval reached
+    long long lo = 0, hi = N;
+    while (lo < hi) {
+      long long mid = (lo + hi) >> 1;
+      if (bound > u_at(c, mid)) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+  };
+  long long hi_cnt = first_not_below(psum[i + 1] / norm, false);
+  long long lo_cnt = i == 0 ? 0 : first_not_below(psum[i] / norm, false);
+  counts[i] = (int)(hi_cnt - lo_cnt);
+}
+
+__global__ void __launch_bounds__(1024) k_normalize_log(double* logw, long long N, double* out) {
+  __shared__ double red[32];
+  const int t = threadIdx.x, BS = blockDim.x, lane = t & 31, warp = t >> 5, nwarp = BS >> 5;
+  double mx = -DBL_MAX;
+  for (long long k = t; k < N; k += BS) mx = fmax(mx, logw[k]);
+  mx = warp_max(mx);
+  if (lane == 0) red[warp] = mx;
+  __syncthreads();
+  mx = red[0];
+  for (int w = 1; w < nwarp; w++) mx = fmax(mx, red[w]);
+  __syncthreads();
+  double s = 0.0, q = 0.0;
+  for (long long k = t; k < N; k += BS) { double e = exp(logw[k] - mx); s += e; q += e * e; }
+  s = warp_sum(s); q = warp_sum(q);
+  if (lane == 0) red[warp] = s;
+  __syncthreads();
+  double S = 0.0;
+  for (int w = 0; w < nwarp; w++) S += red[w];
+  __syncthreads();
+  if (lane == 0) red[warp] = q;
+  __syncthreads();
+  double Q = 0.0;
+  for (int w = 0; w < nwarp; w++) Q += red[w];
+  double lz = mx + log(S);
+  for (long long k = t; k < N; k += BS) logw[k] -= lz;
+  if (t == 0) { out[0] = lz; out[1] = S * S / Q; }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------
+struct smc_engine {
+  smc_config cfg;
+  Params P;
+  int BS = 128;
+  size_t smem = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double kernel_ms = 0.0;
+  long long launches = 0;
+  std::vector<void*> allocs;
+  bool rows_ready = false, inited = false, finished = false;
+  long long swept = 0;
+  std::vector<int> first_pending_h;     // per epoch: number of buckets the regular schedule consumes
+  int* first_pending_d = nullptr;
+};
+
+namespace {
+
+template <class Tp>
+int dev_alloc(smc_engine* e, Tp** p, size_t count, bool zero = true) {
+  void* q = nullptr;
+  size_t bytes = std::max<size_t>(count, 1) * sizeof(Tp);
+  CUDA_TRY(cudaMalloc(&q, bytes));
+  if (zero) CUDA_TRY(cudaMemsetAsync(q, 0, bytes, e->stream));
+  e->allocs.push_back(q);
+  *p = (Tp*)q;
+  return 0;
+}
+
+int use_device(int device) {
+  int count = 0;
+  cudaError_t err = cudaGetDeviceCount(&count);
+  if (err != cudaSuccess || count == 0)
+    return fail(SMC_ERR_CUDA, std::string("no CUDA device available: ") + cudaGetErrorString(err) +
+                                  " (libsmcgpu has no CPU fallback)");
+  if (device < 0 || device >= count) return fail(SMC_ERR_ARG, "device ordinal out of range");
+  CUDA_TRY(cudaSetDevice(device));
+  return 0;
+}
+
+size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * ((size_t)nn * 25 + (size_t)E * 8) + 16; }
+
+int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, int aa, const double* t_start,
+               const double* inv2N, const double* vb, const uint8_t* mask) {
+  if (n < 2 || n > SMC_MAX_HAPLOTYPES) return fail(SMC_ERR_ARG, "n must be in 2..32");
+  if (E < 1 || E > SMC_MAX_EPOCHS) return fail(SMC_ERR_ARG, "E must be in 1..64");
+  memset(&m, 0, sizeof(m));
+  m.n = n; m.nn = 2 * n - 1; m.E = E; m.ancestral_aware = aa; m.mu = mu; m.rho = rho; m.seqlen = seqlen;
+  for (int e = 0; e < E; e++) {
+    m.t_start[e] = t_start ? t_start[e] : 0.0;
+    m.inv2N[e] = inv2N ? inv2N[e] : 1.0;
+    m.vb_logfac[e] = vb ? vb[e] : 0.0;
+    m.rec_mask[e] = mask ? mask[e] : 3;
+    if (e > 0 && !(m.t_start[e] > m.t_start[e - 1])) return fail(SMC_ERR_ARG, "t_start must be strictly increasing");
+    if (!(m.inv2N[e] > 0)) return fail(SMC_ERR_ARG, "inv2N must be positive");
+  }
+  if (m.t_start[0] != 0.0) return fail(SMC_ERR_ARG, "t_start[0] must be 0");
+  return 0;
+}
+
+int launch_row(smc_engine* e, int mode) {
+  int nb = e->P.nblocks;
+  smc_row_kernel<<<nb, e->BS, e->smem, e->stream>>>(e->P, mode);
+  e->launches++;
+  return 0;
+}
+
+int materialise(smc_engine* e) {
+  launch_row(e, 1);
+  smc_commit_kernel<<<1, 1, 0, e->stream>>>(e->P.ctrl);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* smc_last_error(void) { return g_err.c_str(); }
+const char* smc_version(void) { return "smcsmc_b200 0.1 (sm_100a)"; }
+
+int smc_create(const smc_config* cfg, smc_engine** out) {
+  if (!cfg || !out) return fail(SMC_ERR_ARG, "null argument");
+  *out = nullptr;
+  if (cfg->N < 1) return fail(SMC_ERR_ARG, "N must be >= 1");
+  if (!cfg->lags) return fail(SMC_ERR_ARG, "lags required");
+  if (!(cfg->mu >= 0) || !(cfg->rho > 0) || !(cfg->seqlen > 0)) return fail(SMC_ERR_ARG, "mu/rho/seqlen invalid");
+  int rc = use_device(cfg->device);
+  if (rc) return rc;
+  smc_engine* e = new smc_engine();
+  e->cfg = *cfg;
+  Params& P = e->P;
+  memset(&P, 0, sizeof(P));
+  rc = fill_model(P.m, cfg->n, cfg->E, cfg->mu, cfg->rho, cfg->seqlen, cfg->ancestral_aware, cfg->t_start, cfg->inv2N,
+                  cfg->vb_logfac, cfg->rec_mask);
+  if (rc) { delete e; return rc; }
+  P.N = cfg->N; P.parity_scan = cfg->parity_scan; P.seed = cfg->seed; P.chunk = cfg->chunk;
+  P.slot_offset = cfg->slot_offset; P.ess_fraction = cfg->ess_fraction; P.start_pos = cfg->start_pos;
+  // block size: keep every SM busy when there are few particles
+  e->BS = (cfg->N <= 148 * 64 * 2) ? 64 : 128;
+  P.nblocks = (cfg->N + e->BS - 1) / e->BS;
+  e->smem = tree_smem(P.m.nn, P.m.E, e->BS);
+  cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+  if (ce != cudaSuccess) { delete e; return fail(SMC_ERR_CUDA, cudaGetErrorString(ce)); }
+  cudaEventCreate(&e->ev0); cudaEventCreate(&e->ev1);
+  // opt in to the full 227 KB once (the attribute is per function, not per engine)
+  if (e->smem > 230400) { smc_destroy(e); return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has"); }
+  ce = cudaFuncSetAttribute(smc_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
+  const size_t N = cfg->N;
+  const int n = cfg->n, nn = 2 * n - 1;
+  for (int b = 0; b < 2; b++) {
+    if ((rc = dev_alloc(e, &P.buf[b].height, (size_t)(n - 1) * N))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.buf[b].parent, (size_t)nn * N))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.buf[b].logw, N))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.buf[b].next_base, N))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.local_cum[b], N))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.bmax[b], P.nblocks))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.bsum[b], P.nblocks))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.bsq[b], P.nblocks))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.boff[b], P.nblocks + 1))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.bscale[b], P.nblocks))) { smc_destroy(e); return rc; }
+  }
+  if ((rc = dev_alloc(e, &P.psum, cfg->parity_scan ? N + 1 : 1))) { smc_destroy(e); return rc; }
+  if ((rc = dev_alloc(e, &P.tallies, 6 * (size_t)cfg->E))) { smc_destroy(e); return rc; }
+  if ((rc = dev_alloc(e, &P.anc, N))) { smc_destroy(e); return rc; }
+  if ((rc = dev_alloc(e, &P.ctrl, 1))) { smc_destroy(e); return rc; }
+  cudaMemsetAsync(P.anc, 0xff, N * sizeof(int), e->stream);
+  {
+    Ctrl init;
+    memset(&init, 0, sizeof(init));
+    init.cons_done = -1;
+    cudaMemcpyAsync(P.ctrl, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream);
+    ce = cudaStreamSynchronize(e->stream);
+    if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, msg); }
+  }
+  *out = e;
+  return 0;
+}
+
+void smc_destroy(smc_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->cfg.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (void* p : e->allocs) cudaFree(p);
+  if (e->ev0) cudaEventDestroy(e->ev0);
+  if (e->ev1) cudaEventDestroy(e->ev1);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, const uint8_t* is_site,
+                    const int32_t* max_rec_epoch, int64_t R) {
+  if (!e || !x_end || !alleles || !is_site) return fail(SMC_ERR_ARG, "null argument");
+  if (R < 1) return fail(SMC_ERR_ARG, "R must be >= 1");
+  if (e->rows_ready) return fail(SMC_ERR_STATE, "rows already uploaded");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  const int E = e->cfg.E, n = e->cfg.n;
+  for (int64_t r = 0; r < R; r++) {
+    double prev = r ? x_end[r - 1] : e->cfg.start_pos;
+    if (!(x_end[r] > prev)) return fail(SMC_ERR_ARG, "row ends must be strictly increasing and beyond start_pos");
+    if (x_end[r] > e->cfg.seqlen) return fail(SMC_ERR_ARG, "row end beyond seqlen");
+    for (int k = 0; k < n; k++) {
+      int a = alleles[r * n + k];
+      if (a < -1 || a > 2) return fail(SMC_ERR_ARG, "allele code must be -1, 0, 1 or 2");
+      if (a == 2 && !((k % 2 == 0 && k + 1 < n && alleles[r * n + k + 1] == 2) || (k % 2 == 1 && alleles[r * n + k - 1] == 2)))
+        return fail(SMC_ERR_ARG, "unphased het code 2 must come in (even, odd) pairs");
+    }
+  }
+  // ---- lagged-tally schedule: CountModel::extract_and_update_count's update positions (count.cpp:363-385) ----
+  // bucket k of epoch e holds the records whose position lies in [ub[e][k-1], ub[e][k]); it is consumed after the row
+  // whose update made update_to = ub[e][k].  The last bucket (+inf) is consumed by smc_finish.
+  std::vector<std::vector<double>> ub(E);
+  std::vector<double> counted_to(E, 0.0);
+  std::vector<int> cons_off(R + 1, 0);
+  std::vector<int2> cons;
+  for (int64_t r = 0; r < R; r++) {
+    int first = E;
+    for (int ep = 0; ep < E; ep++) {
+      double lagging = e->cfg.lags[ep];
+      double x_e = x_end[r] - lagging;
+      if ((x_e - counted_to[ep]) < lagging * 0.1 && first > ep) continue;   // no update
+      if (ep < first) first = ep;
+      counted_to[ep] = x_e;
+      // a bound at or below the previous one closes an empty window: nothing can be in it, skip the bucket
+      if (!ub[ep].empty() && !(x_e > ub[ep].back())) continue;
+      if (ub[ep].empty() && !(x_e > e->cfg.start_pos)) continue;
+      cons.push_back(make_int2(ep, (int)ub[ep].size()));
+      ub[ep].push_back(x_e);
+    }
+    cons_off[r + 1] = (int)cons.size();
+  }
+  e->first_pending_h.assign(E, 0);
+  std::vector<int> ub_off(E + 1, 0);
+  std::vector<double> ub_flat;
+  for (int ep = 0; ep < E; ep++) {
+    e->first_pending_h[ep] = (int)ub[ep].size();
+    ub[ep].push_back(HUGE_VAL);
+    ub_off[ep + 1] = ub_off[ep] + (int)ub[ep].size();
+    ub_flat.insert(ub_flat.end(), ub[ep].begin(), ub[ep].end());
+  }
+  // bucket at each row's left end, and the ring depth needed: buckets in flight = [next to consume, highest written]
+  std::vector<int> kstart((size_t)R * E);
+  std::vector<int> kcur(E, 0), consumed(E, 0);
+  int B = 1;
+  for (int64_t r = 0; r < R; r++) {
+    double x0 = r ? x_end[r - 1] : e->cfg.start_pos;
+    for (int ep = 0; ep < E; ep++) {
+      while (ub[ep][kcur[ep]] <= x0) kcur[ep]++;
+      kstart[(size_t)r * E + ep] = kcur[ep];
+      int khi = kcur[ep];
+      while (ub[ep][khi] <= x_end[r]) khi++;
+      B = std::max(B, khi - consumed[ep] + 1);
+    }
+    for (int q = cons_off[r]; q < cons_off[r + 1]; q++) consumed[cons[q].x] = cons[q].y + 1;
+  }
+  Params& P = e->P;
+  P.B = B;
+  P.R = R;
+  std::vector<int> mr(R);
+  for (int64_t r = 0; r < R; r++) mr[r] = max_rec_epoch ? max_rec_epoch[r] : E - 1;
+  int rc;
+  double* d_x; signed char* d_al; unsigned char* d_site; int* d_mr; int* d_ks; int* d_uboff; double* d_ub; int* d_co; int2* d_cons;
+  if ((rc = dev_alloc(e, &d_x, R, false)) || (rc = dev_alloc(e, &d_al, (size_t)R * n, false)) ||
+      (rc = dev_alloc(e, &d_site, R, false)) || (rc = dev_alloc(e, &d_mr, R, false)) ||
+      (rc = dev_alloc(e, &d_ks, (size_t)R * E, false)) || (rc = dev_alloc(e, &d_uboff, E + 1, false)) ||
+      (rc = dev_alloc(e, &d_ub, ub_flat.size(), false)) || (rc = dev_alloc(e, &d_co, R + 1, false)) ||
+      (rc = dev_alloc(e, &d_cons, cons.size(), false)) || (rc = dev_alloc(e, &e->first_pending_d, E, false)))
+    return rc;
+  CUDA_TRY(cudaMemcpyAsync(d_x, x_end, R * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_al, alleles, (size_t)R * n, cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_site, is_site, R, cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_mr, mr.data(), R * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_ks, kstart.data(), kstart.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_uboff, ub_off.data(), ub_off.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_ub, ub_flat.data(), ub_flat.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_co, cons_off.data(), cons_off.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  if (!cons.empty())
+    CUDA_TRY(cudaMemcpyAsync(d_cons, cons.data(), cons.size() * sizeof(int2), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, e->first_pending_h.data(), E * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  P.x_end = d_x; P.alleles = d_al; P.is_site = d_site; P.max_rec = d_mr; P.kstart = d_ks; P.ub_off = d_uboff; P.ub = d_ub;
+  P.cons_off = d_co; P.cons = d_cons;
+  // the ring and the resampling log need R / B
+  const size_t cells = (size_t)E * B * 4;
+  for (int b = 0; b < 2; b++)
+    if ((rc = dev_alloc(e, &P.buf[b].ring, cells * (size_t)e->cfg.N))) return rc;
+  P.rs_cap = R;
+  if ((rc = dev_alloc(e, &P.rs_pos, R)) || (rc = dev_alloc(e, &P.rs_ess, R))) return rc;
+  CUDA_TRY(cudaStreamSynchronize(e->stream));   // host vectors go out of scope
+  e->rows_ready = true;
+  return 0;
+}
+
+int smc_init_particles(smc_engine* e) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows before initialising particles");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  smc_init_kernel<<<e->P.nblocks, e->BS, e->smem, e->stream>>>(e->P);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  e->inited = true;
+  return 0;
+}
+
+int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
+  if (e->finished) return fail(SMC_ERR_STATE, "sweep after finish");
+  if (row_begin != e->swept) return fail(SMC_ERR_STATE, "rows must be swept in order, starting where the last sweep ended");
+  if (row_end < row_begin || row_end > e->P.R) return fail(SMC_ERR_ARG, "row range out of bounds");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  cudaEventRecord(e->ev0, e->stream);
+  for (int64_t r = row_begin; r < row_end; r++) launch_row(e, 0);
+  cudaEventRecord(e->ev1, e->stream);
+  CUDA_TRY(cudaGetLastError());
+  // timing is collected lazily: the events are read at the next synchronising call
+  e->swept = row_end;
+  cudaEventSynchronize(e->ev1);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e->ev0, e->ev1);
+  e->kernel_ms += ms;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int smc_finish(smc_engine* e) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
+  if (e->finished) return 0;
+  if (e->swept != e->P.R) return fail(SMC_ERR_STATE, "finish before the last row was swept");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  // buckets the regular schedule still owes for the last row are folded into the flush: both use the final weights
+  std::vector<int> fp(e->cfg.E);
+  for (int ep = 0; ep < e->cfg.E; ep++) fp[ep] = 0;
+  // number of buckets consumed so far per epoch = those scheduled after rows 0..R-2
+  {
+    std::vector<int> co(e->P.R + 1);
+    CUDA_TRY(cudaMemcpy(co.data(), e->P.cons_off, (e->P.R + 1) * sizeof(int), cudaMemcpyDeviceToHost));
+    int upto = co[e->P.R - 1];
+    std::vector<int2> cs(std::max(upto, 1));
+    if (upto) CUDA_TRY(cudaMemcpy(cs.data(), e->P.cons, upto * sizeof(int2), cudaMemcpyDeviceToHost));
+    for (int q = 0; q < upto; q++) fp[cs[q].x] = cs[q].y + 1;
+  }
+  CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, fp.data(), fp.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  cudaEventRecord(e->ev0, e->stream);
+  smc_flush_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
+  e->launches++;
+  cudaEventRecord(e->ev1, e->stream);
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e->ev0, e->ev1);
+  e->kernel_ms += ms;
+  CUDA_TRY(cudaGetLastError());
+  e->finished = true;
+  return 0;
+}
+
+int smc_get_tallies(smc_engine* e, double* out) {
+  if (!e || !out) return fail(SMC_ERR_ARG, "null argument");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  CUDA_TRY(cudaMemcpy(out, e->P.tallies, 6 * (size_t)e->cfg.E * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+static int read_ctrl(smc_engine* e, Ctrl* c) {
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  CUDA_TRY(cudaMemcpy(c, e->P.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int smc_get_lnZ(smc_engine* e, double* lnZ) {
+  if (!e || !lnZ) return fail(SMC_ERR_ARG, "null argument");
+  Ctrl c;
+  int rc = read_ctrl(e, &c);
+  if (rc) return rc;
+  *lnZ = c.lnZ;
+  if (c.err) return fail(SMC_ERR_NUMERIC, "Zero or negative probabilities");
+  return 0;
+}
+
+int smc_get_counters(smc_engine* e, int64_t counters[4]) {
+  if (!e || !counters) return fail(SMC_ERR_ARG, "null argument");
+  Ctrl c;
+  int rc = read_ctrl(e, &c);
+  if (rc) return rc;
+  counters[0] = c.row; counters[1] = c.n_resample; counters[2] = c.n_recomb; counters[3] = c.err;
+  return 0;
+}
+
+int smc_get_resample_log(smc_engine* e, double* position, double* ess, int64_t cap, int64_t* n) {
+  if (!e || !n) return fail(SMC_ERR_ARG, "null argument");
+  Ctrl c;
+  int rc = read_ctrl(e, &c);
+  if (rc) return rc;
+  int64_t have = std::min<int64_t>(c.n_resample, e->P.rs_cap);
+  *n = have;
+  int64_t take = std::min(have, cap);
+  if (take > 0 && position) CUDA_TRY(cudaMemcpy(position, e->P.rs_pos, take * sizeof(double), cudaMemcpyDeviceToHost));
+  if (take > 0 && ess) CUDA_TRY(cudaMemcpy(ess, e->P.rs_ess, take * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int smc_get_particles(smc_engine* e, int32_t* parent, double* height, double* logw, double* next_base) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  if (!e->finished) { int rc = materialise(e); if (rc) return rc; }
+  Ctrl c;
+  int rc = read_ctrl(e, &c);
+  if (rc) return rc;
+  const size_t N = e->cfg.N;
+  const int n = e->cfg.n, nn = 2 * n - 1;
+  const StateBuf& s = e->P.buf[c.cur];
+  std::vector<double> h((size_t)(n - 1) * N);
+  std::vector<signed char> p((size_t)nn * N);
+  CUDA_TRY(cudaMemcpy(h.data(), s.height, h.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(p.data(), s.parent, p.size(), cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; i++)
+    for (int v = 0; v < nn; v++) {
+      if (height) height[i * nn + v] = v < n ? 0.0 : h[(size_t)(v - n) * N + i];
+      if (parent) parent[i * nn + v] = p[(size_t)v * N + i];
+    }
+  if (logw) {
+    CUDA_TRY(cudaMemcpy(logw, s.logw, N * sizeof(double), cudaMemcpyDeviceToHost));
+    if (e->finished) for (size_t i = 0; i < N; i++) logw[i] -= c.lse;
+  }
+  if (next_base) CUDA_TRY(cudaMemcpy(next_base, s.next_base, N * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int smc_set_particles(smc_engine* e, const int32_t* parent, const double* height, const double* logw,
+                      const double* next_base) {
+  if (!e || !parent || !height || !logw || !next_base) return fail(SMC_ERR_ARG, "null argument");
+  if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows first");
+  if (e->swept != 0) return fail(SMC_ERR_STATE, "set_particles only before the first row");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  const size_t N = e->cfg.N;
+  const int n = e->cfg.n, nn = 2 * n - 1;
+  std::vector<double> h((size_t)(n - 1) * N);
+  std::vector<signed char> p((size_t)nn * N);
+  for (size_t i = 0; i < N; i++) {
+    for (int v = 0; v < nn; v++) {
+      int par = parent[i * nn + v];
+      if (par < -1 || par >= nn) return fail(SMC_ERR_ARG, "parent index out of range");
+      p[(size_t)v * N + i] = (signed char)par;
+      if (v >= n) {
+        h[(size_t)(v - n) * N + i] = height[i * nn + v];
+        if (v > n && height[i * nn + v] < height[i * nn + v - 1]) return fail(SMC_ERR_ARG, "internal slots must be height-sorted");
+      } else if (height[i * nn + v] != 0.0) return fail(SMC_ERR_ARG, "leaves must sit at height 0");
+    }
+    if (parent[i * nn + nn - 1] != -1) return fail(SMC_ERR_ARG, "the last slot must be the root");
+  }
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  const StateBuf& s = e->P.buf[0];
+  CUDA_TRY(cudaMemcpy(s.height, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(s.parent, p.data(), p.size(), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(s.logw, logw, N * sizeof(double), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(s.next_base, next_base, N * sizeof(double), cudaMemcpyHostToDevice));
+  e->inited = true;
+  return 0;
+}
+
+int smc_get_last_ancestry(smc_engine* e, int32_t* anc) {
+  if (!e || !anc) return fail(SMC_ERR_ARG, "null argument");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  if (e->inited && !e->finished) { int rc = materialise(e); if (rc) return rc; }
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  CUDA_TRY(cudaMemcpy(anc, e->P.anc, (size_t)e->cfg.N * sizeof(int), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int smc_get_timing(smc_engine* e, double* kernel_ms, int64_t* launches) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (kernel_ms) *kernel_ms = e->kernel_ms;
+  if (launches) *launches = e->launches;
+  return 0;
+}
+
+// ---- stand-alone entry points -----------------------------------------------------------------------------------
+namespace {
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  int alloc(size_t bytes) { CUDA_TRY(cudaMalloc(&p, std::max<size_t>(bytes, 8))); return 0; }
+};
+
+int tree_fn(int device, int n, int64_t count, const int32_t* parent, const double* height, const int8_t* alleles,
+            double mu, int aa, int what, double* o0, double* o1) {
+  if (!parent || !height || !alleles || !o0) return fail(SMC_ERR_ARG, "null argument");
+  if (count < 0) return fail(SMC_ERR_ARG, "negative count");
+  if (count == 0) return 0;
+  int rc = use_device(device);
+  if (rc) return rc;
+  ModelDev m;
+  double t0 = 0.0, inv = 1.0;
+  if ((rc = fill_model(m, n, 1, mu, 1.0, 1.0, aa, &t0, &inv, nullptr, nullptr))) return rc;
+  const int nn = 2 * n - 1, BS = 64;
+  DevBuf dp, dh, da, d0, d1;
+  if ((rc = dp.alloc(count * nn * sizeof(int))) || (rc = dh.alloc(count * nn * sizeof(double))) ||
+      (rc = da.alloc(count * n)) || (rc = d0.alloc(count * sizeof(double))) || (rc = d1.alloc(count * sizeof(double))))
+    return rc;
+  CUDA_TRY(cudaMemcpy(dp.p, parent, count * nn * sizeof(int), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(dh.p, height, count * nn * sizeof(double), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(da.p, alleles, count * n, cudaMemcpyHostToDevice));
+  size_t smem = tree_smem(nn, 1, BS);
+  CUDA_TRY(cudaFuncSetAttribute(k_tree_functions, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+  k_tree_functions<<<(unsigned)((count + BS - 1) / BS), BS, smem>>>(m, count, (const int*)dp.p, (const double*)dh.p,
+                                                                   (const signed char*)da.p, what, (double*)d0.p, (double*)d1.p);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(o0, d0.p, count * sizeof(double), cudaMemcpyDeviceToHost));
+  if (o1) CUDA_TRY(cudaMemcpy(o1, d1.p, count * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+}  // namespace
+
+int smc_site_likelihood(int device, int32_t n, int64_t count, const int32_t* parent, const double* height,
+                        const int8_t* alleles, double mu, int32_t ancestral_aware, double* lik) {
+  return tree_fn(device, n, count, parent, height, alleles, mu, ancestral_aware, 0, lik, nullptr);
+}
+
+int smc_branch_lengths(int device, int32_t n, int64_t count, const int32_t* parent, const double* height,
+                       const int8_t* alleles, double* with_data, double* total) {
+  if (!total) return fail(SMC_ERR_ARG, "null argument");
+  return tree_fn(device, n, count, parent, height, alleles, 0.0, 0, 1, with_data, total);
+}
+
+static int offspring_from_psum(const double* d_psum, int64_t N, double u, int32_t* counts) {
+  DevBuf dc, dn;
+  int rc;
+  if ((rc = dc.alloc(sizeof(Ctrl))) || (rc = dn.alloc(N * sizeof(int)))) return rc;
+  CUDA_TRY(cudaMemset(dc.p, 0, sizeof(Ctrl)));
+  k_build_chain<<<1, 1>>>((Ctrl*)dc.p, u, N);
+  k_offspring_counts<<<(unsigned)((N + 127) / 128), 128>>>((const Ctrl*)dc.p, d_psum, N, (int*)dn.p);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(counts, dn.p, N * sizeof(int), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int smc_systematic_offspring(int device, const double* partial_sum, int64_t N, double u, int32_t* counts) {
+  if (!partial_sum || !counts) return fail(SMC_ERR_ARG, "null argument");
+  if (N < 1) return fail(SMC_ERR_ARG, "N must be >= 1");
+  if (!(u >= 0.0 && u < 1.0)) return fail(SMC_ERR_ARG, "u must be in [0,1)");
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevBuf dp;
+  if ((rc = dp.alloc((N + 1) * sizeof(double)))) return rc;
+  CUDA_TRY(cudaMemcpy(dp.p, partial_sum, (N + 1) * sizeof(double), cudaMemcpyHostToDevice));
+  return offspring_from_psum((const double*)dp.p, N, u, counts);
+}
+
+int smc_resample_counts(int device, const double* w, int64_t N, double u, int32_t parity_scan, double* ess,
+                        int32_t* counts) {
+  if (!w || !counts || !ess) return fail(SMC_ERR_ARG, "null argument");
+  if (N < 1) return fail(SMC_ERR_ARG, "N must be >= 1");
+  if (!(u >= 0.0 && u < 1.0)) return fail(SMC_ERR_ARG, "u must be in [0,1)");
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevBuf dw, dp, de;
+  if ((rc = dw.alloc(N * sizeof(double))) || (rc = dp.alloc((N + 1) * sizeof(double))) || (rc = de.alloc(sizeof(double))))
+    return rc;
+  CUDA_TRY(cudaMemcpy(dw.p, w, N * sizeof(double), cudaMemcpyHostToDevice));
+  if (parity_scan) k_seq_partial_sums<<<1, 1>>>((const double*)dw.p, N, (double*)dp.p, (double*)de.p);
+  else k_par_partial_sums<<<1, 1024>>>((const double*)dw.p, N, (double*)dp.p, (double*)de.p);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(ess, de.p, sizeof(double), cudaMemcpyDeviceToHost));
+  return offspring_from_psum((const double*)dp.p, N, u, counts);
+}
+
+int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* ess) {
+  if (!logw || !lnZ || !ess) return fail(SMC_ERR_ARG, "null argument");
+  if (N < 1) return fail(SMC_ERR_ARG, "N must be >= 1");
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevBuf dw, dout;
+  if ((rc = dw.alloc(N * sizeof(double))) || (rc = dout.alloc(2 * sizeof(double)))) return rc;
+  CUDA_TRY(cudaMemcpy(dw.p, logw, N * sizeof(double), cudaMemcpyHostToDevice));
+  k_normalize_log<<<1, 1024>>>((double*)dw.p, N, (double*)dout.p);
+  CUDA_TRY(cudaGetLastError());
+  double o[2];
+  CUDA_TRY(cudaMemcpy(o, dout.p, sizeof(o), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(logw, dw.p, N * sizeof(double), cudaMemcpyDeviceToHost));
+  *lnZ = o[0]; *ess = o[1];
+  if (!std::isfinite(o[0])) return fail(SMC_ERR_NUMERIC, "Zero or negative probabilities");
+  return 0;
+}
+
+int smc_fastexp(int device, const double* x, int64_t count, double* out) {
+  if (!x || !out) return fail(SMC_ERR_ARG, "null argument");
+  if (count <= 0) return count == 0 ? 0 : fail(SMC_ERR_ARG, "negative count");
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevBuf dx, dout;
+  if ((rc = dx.alloc(count * sizeof(double))) || (rc = dout.alloc(count * sizeof(double)))) return rc;
+  CUDA_TRY(cudaMemcpy(dx.p, x, count * sizeof(double), cudaMemcpyHostToDevice));
+  k_fastexp<<<(unsigned)((count + 255) / 256), 256>>>((const double*)dx.p, count, (double*)dout.p);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(out, dout.p, count * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+}  // extern "C"

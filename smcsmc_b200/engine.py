@@ -1,0 +1,167 @@
+"""Python mirror of the reference's ParticleContainer surface for the hot path, over the C ABI (host buffers in/out).
+
+ParticleFilter plays the role of ParticleContainer + CountModel inside pfARG_core (reference src/smcsmc.cpp:278-400):
+construct (prior trees), update over rows, read ln_normalization_factor and the lagged tallies.
+"""
+import ctypes
+
+import numpy as np
+
+from ._abi import lib, check, SmcConfig
+
+_P = lambda a: a.ctypes.data_as(ctypes.c_void_p)  # noqa: E731
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class ParticleFilter:
+    def __init__(self, n, N, t_start, inv2N, mu, rho, seqlen, lags, seed=1, chunk=0, start_pos=0.0, ess_fraction=0.5,
+                 ancestral_aware=False, parity_scan=False, vb_logfac=None, rec_mask=None, device=0, slot_offset=0):
+        self.n, self.N, self.E = int(n), int(N), len(t_start)
+        self._keep = [_f64(t_start), _f64(inv2N), _f64(lags),
+                      None if vb_logfac is None else _f64(vb_logfac),
+                      None if rec_mask is None else np.ascontiguousarray(rec_mask, dtype=np.uint8)]
+        c = SmcConfig()
+        c.n, c.N, c.E, c.device = self.n, self.N, self.E, device
+        c.seed, c.chunk, c.slot_offset = seed, chunk, slot_offset
+        c.mu, c.rho, c.seqlen, c.start_pos, c.ess_fraction = mu, rho, seqlen, start_pos, ess_fraction
+        c.ancestral_aware, c.parity_scan = int(ancestral_aware), int(parity_scan)
+        c.t_start, c.inv2N, c.lags = (self._keep[0].ctypes.data, self._keep[1].ctypes.data, self._keep[2].ctypes.data)
+        c.vb_logfac = None if self._keep[3] is None else self._keep[3].ctypes.data
+        c.rec_mask = None if self._keep[4] is None else self._keep[4].ctypes.data
+        self._h = ctypes.c_void_p()
+        check(lib().smc_create(ctypes.byref(c), ctypes.byref(self._h)))
+        self.R = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().smc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- Segment rows ---
+    def upload_rows(self, x_end, alleles, is_site, max_rec_epoch=None):
+        x_end = _f64(x_end)
+        alleles = np.ascontiguousarray(alleles, dtype=np.int8)
+        is_site = np.ascontiguousarray(is_site, dtype=np.uint8)
+        mr = None if max_rec_epoch is None else np.ascontiguousarray(max_rec_epoch, dtype=np.int32)
+        assert alleles.shape == (len(x_end), self.n)
+        check(lib().smc_upload_rows(self._h, _P(x_end), _P(alleles), _P(is_site), None if mr is None else _P(mr),
+                                    len(x_end)))
+        self.R = len(x_end)
+
+    def init_particles(self):
+        check(lib().smc_init_particles(self._h))
+
+    def set_particles(self, parent, height, logw, next_base):
+        parent = np.ascontiguousarray(parent, dtype=np.int32)
+        check(lib().smc_set_particles(self._h, _P(parent), _P(_f64(height)), _P(_f64(logw)), _P(_f64(next_base))))
+
+    # --- the hot loop ---
+    def sweep(self, row_begin=0, row_end=None):
+        check(lib().smc_sweep(self._h, row_begin, self.R if row_end is None else row_end))
+
+    def finish(self):
+        check(lib().smc_finish(self._h))
+
+    # --- results ---
+    def particles(self):
+        nn = 2 * self.n - 1
+        parent = np.zeros((self.N, nn), dtype=np.int32)
+        height = np.zeros((self.N, nn))
+        logw, nb = np.zeros(self.N), np.zeros(self.N)
+        check(lib().smc_get_particles(self._h, _P(parent), _P(height), _P(logw), _P(nb)))
+        return parent, height, logw, nb
+
+    def ln_normalization_factor(self):
+        v = ctypes.c_double()
+        check(lib().smc_get_lnZ(self._h, ctypes.byref(v)))
+        return v.value
+
+    def tallies(self):
+        out = np.zeros((6, self.E))
+        check(lib().smc_get_tallies(self._h, _P(out)))
+        return out
+
+    def counters(self):
+        c = np.zeros(4, dtype=np.int64)
+        check(lib().smc_get_counters(self._h, _P(c)))
+        return dict(rows=int(c[0]), resamples=int(c[1]), recombinations=int(c[2]), err=int(c[3]))
+
+    def resample_log(self):
+        pos, ess = np.zeros(max(self.R, 1)), np.zeros(max(self.R, 1))
+        k = ctypes.c_int64()
+        check(lib().smc_get_resample_log(self._h, _P(pos), _P(ess), len(pos), ctypes.byref(k)))
+        return pos[:k.value], ess[:k.value]
+
+    def last_ancestry(self):
+        a = np.zeros(self.N, dtype=np.int32)
+        check(lib().smc_get_last_ancestry(self._h, _P(a)))
+        return a
+
+    def timing(self):
+        ms, k = ctypes.c_double(), ctypes.c_int64()
+        check(lib().smc_get_timing(self._h, ctypes.byref(ms), ctypes.byref(k)))
+        return ms.value, k.value
+
+
+# ---- stand-alone functions (each mirrors one reference member function) ----
+def site_likelihood(parent, height, alleles, mu, ancestral_aware=False, device=0):
+    """ForestState::calculate_likelihood averaged over phasings (particle.cpp:667, particleContainer.cpp:204-221)."""
+    parent = np.ascontiguousarray(parent, dtype=np.int32)
+    height = _f64(height)
+    alleles = np.ascontiguousarray(alleles, dtype=np.int8)
+    count, n = alleles.shape
+    out = np.zeros(count)
+    check(lib().smc_site_likelihood(device, n, count, _P(parent), _P(height), _P(alleles), mu, int(ancestral_aware),
+                                    _P(out)))
+    return out
+
+
+def branch_lengths(parent, height, alleles, device=0):
+    """(trackLocalTreeBranchLength, getLocalTreeLength)  (particle.cpp:699, forest.h:188)."""
+    parent = np.ascontiguousarray(parent, dtype=np.int32)
+    height = _f64(height)
+    alleles = np.ascontiguousarray(alleles, dtype=np.int8)
+    count, n = alleles.shape
+    a, b = np.zeros(count), np.zeros(count)
+    check(lib().smc_branch_lengths(device, n, count, _P(parent), _P(height), _P(alleles), _P(a), _P(b)))
+    return a, b
+
+
+def systematic_offspring(partial_sum, u, device=0):
+    """ParticleContainer::systematic_resampling (particleContainer.cpp:474)."""
+    ps = _f64(partial_sum)
+    N = len(ps) - 1
+    counts = np.zeros(N, dtype=np.int32)
+    check(lib().smc_systematic_offspring(device, _P(ps), N, u, _P(counts)))
+    return counts
+
+
+def resample_counts(w, u, parity_scan=True, device=0):
+    w = _f64(w)
+    counts = np.zeros(len(w), dtype=np.int32)
+    ess = ctypes.c_double()
+    check(lib().smc_resample_counts(device, _P(w), len(w), u, int(parity_scan), ctypes.byref(ess), _P(counts)))
+    return ess.value, counts
+
+
+def normalize_log(logw, device=0):
+    lw = _f64(logw).copy()
+    lnZ, ess = ctypes.c_double(), ctypes.c_double()
+    check(lib().smc_normalize_log(device, _P(lw), len(lw), ctypes.byref(lnZ), ctypes.byref(ess)))
+    return lw, lnZ.value, ess.value
+
+
+def fastexp(x, device=0):
+    x = _f64(x)
+    out = np.zeros_like(x)
+    check(lib().smc_fastexp(device, _P(x), x.size, _P(out)))
+    return out

@@ -50,6 +50,12 @@ class OrcEvents(ctypes.Structure):
                 ("overflow", ctypes.c_int)]
 
 
+class OrcPfConfig(ctypes.Structure):
+    _fields_ = [("N", ctypes.c_int), ("seed", ctypes.c_uint64), ("chunk", ctypes.c_uint32),
+                ("slot_offset", ctypes.c_uint32), ("start_pos", ctypes.c_double), ("ess_fraction", ctypes.c_double),
+                ("ancestral_aware", ctypes.c_int), ("lags", ctypes.c_void_p)]
+
+
 class OrcRecEvent(ctypes.Structure):
     _fields_ = [("row", ctypes.c_int), ("slot", ctypes.c_int), ("ev", OrcEvent)]
 
@@ -60,7 +66,8 @@ _ref = None
 
 def build_oracle():
     so = os.path.join(ORACLE_DIR, "liboracle.so")
-    srcs = [os.path.join(ORACLE_DIR, f) for f in ("smc_oracle.c", "smc_tally_oracle.c", "smc_oracle.h")]
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("smc_oracle.c", "smc_tally_oracle.c", "smc_filter_oracle.c",
+                                                   "smc_oracle.h")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
     return so
@@ -105,8 +112,50 @@ def oracle():
         L.orc_lagged_tallies.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double,
                                          ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
+        L.orc_particle_filter.argtypes = [ctypes.POINTER(OrcModel), ctypes.POINTER(OrcPfConfig), ctypes.c_int,
+                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                          ctypes.c_void_p, c_dp, ctypes.c_void_p, c_ip, ctypes.c_void_p,
+                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_long)]
         _oracle = L
     return _oracle
+
+
+def oracle_filter(model, N, seed, chunk, start_pos, ess_fraction, lags, row_end, data, is_site, max_rec=None,
+                  ancestral_aware=0, slot_offset=0):
+    """Run the CPU restatement of the whole per-chunk filter.  Returns a dict with parent[N,2n-1], height, logw,
+    next_base, lnZ, tallies[6,E], n_resample, rs_pos, rs_ess, last_anc, n_recomb."""
+    L = oracle()
+    n, E = model.n, model.E
+    nn = 2 * n - 1
+    R = len(row_end)
+    lags = np.ascontiguousarray(lags, dtype=np.float64)
+    cfg = OrcPfConfig(N, seed, chunk, slot_offset, start_pos, ess_fraction, ancestral_aware, lags.ctypes.data)
+    parts = (OrcParticle * N)()
+    row_end = np.ascontiguousarray(row_end, dtype=np.float64)
+    data = np.ascontiguousarray(data, dtype=np.int32)
+    is_site = np.ascontiguousarray(is_site, dtype=np.int32)
+    mr = None if max_rec is None else np.ascontiguousarray(max_rec, dtype=np.int32)
+    lnZ = ctypes.c_double()
+    tallies = np.zeros(6 * E)
+    nres = ctypes.c_int()
+    nrec = ctypes.c_long()
+    rs_pos, rs_ess = np.zeros(R), np.zeros(R)
+    last_anc = np.zeros(N, dtype=np.int32)
+    rc = L.orc_particle_filter(ctypes.byref(model), ctypes.byref(cfg), R, P(row_end), P(data), P(is_site),
+                               None if mr is None else P(mr), parts, ctypes.byref(lnZ), P(tallies),
+                               ctypes.byref(nres), P(rs_pos), P(rs_ess), P(last_anc), ctypes.byref(nrec))
+    if rc:
+        raise RuntimeError("oracle filter failed (event buffer overflow or zero weight)")
+    parent = np.zeros((N, nn), dtype=np.int32)
+    height = np.zeros((N, nn))
+    logw, nb = np.zeros(N), np.zeros(N)
+    for i in range(N):
+        parent[i] = np.ctypeslib.as_array(parts[i].parent)[:nn]
+        height[i] = np.ctypeslib.as_array(parts[i].height)[:nn]
+        logw[i], nb[i] = parts[i].logw, parts[i].next_base
+    return dict(parent=parent, height=height, logw=logw, next_base=nb, lnZ=lnZ.value, tallies=tallies.reshape(6, E),
+                n_resample=nres.value, rs_pos=rs_pos[:nres.value], rs_ess=rs_ess[:nres.value], last_anc=last_anc,
+                n_recomb=nrec.value)
 
 
 def make_model(n, t_start, inv2N, mu, rho, seqlen, vb_logfac=None, rec_mask=None):
