@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py -- particle*sites/s of the SMCSMC particle-filter sweep on B200 (BASELINE.json metric), one JSON line.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our engine (libsmcgpu.so through the C ABI)
+  python bench.py --impl reference [...]                          the reference's own CPU implementation (oracle/_ref)
+
+Workload (BASELINE.json configs[1]): 8 haplotypes x 100 Mb scrm-simulated under the zigzag
+piecewise-constant demography (bench_data/zigzag_n8_100Mb_seed1.seg.gz, made by tools/make_seg.py with the reference's
+scrm), inferred under 11 epochs at the zigzag change times starting from all-ones sizes, 10 000 particles.  A "step" is
+one EM iteration's sweep over the whole chunk: prior trees, every .seg row (extend + prune + normalise + tally +
+resample), end-of-data flush.  With --gpus N every rank sweeps its own 100 Mb chunk (the reference's own decomposition:
+independent chunks, tallies summed; weak scaling), the tallies are all-reduced once per step over NCCL.
+
+  value  particle*sites/s with the rows already resident in HBM (engine re-used, smc_reset between steps)
+  e2e    the same through the public C-ABI calls with HOST buffers: create + upload rows (H2D from pinned memory) +
+         sweep + finish + read tallies/lnZ (D2H), engine destroyed afterwards
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N0, MU, RHO = 1e4, 2.5e-8, 1e-8
+ZIGZAG_TIMES = [0, .0025, .005, .01, .02, .04, .08, .16, .32, .64, 1.28]       # units of 4*N0 generations
+# CountModel lags for this model as calibrated by the reference itself (calculate_median_survival_distances,
+# smcsmc.cpp:169-263, lag_fraction 2; run of oracle/_ref/smcsmc recorded in DESIGN.md).  Device calibration is row f1.
+ZIGZAG_LAGS = [1.48082e+06, 489354, 240986, 120483, 67150.3, 38647.3, 21660.1, 14104.1, 8775.52, 5010.28, 2619.84]
+SEG = os.path.join(ROOT, "bench_data", "zigzag_n8_100Mb_seed1.seg.gz")
+NSAM = 8
+
+
+def workload(len_mb):
+    from smcsmc_b200.segdata import read_seg
+    seqlen = len_mb * 1e6
+    max_seg_len = int(2.0 / (RHO * 4 * N0))                    # pfparam.cpp:364
+    rows = read_seg(SEG, NSAM, seqlen, data_start=1, max_segment_length=max_seg_len)
+    t_start = [4 * N0 * t for t in ZIGZAG_TIMES]
+    inv2N = [1.0 / (2 * N0)] * len(t_start)
+    return rows, t_start, inv2N, seqlen
+
+
+class Clocks(threading.Thread):
+    """nvidia-smi clock / throttle-reason samples during the timed region (B200_PROFILING.md recipe)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.lines, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.lines.append(line.strip())
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, smax, reasons = [], 0.0, set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax = max(smax, float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes_per_launch(n, N, E, resample_fraction):
+    """DESIGN.md 'roofline': per particle and row the state is read and written once, S = 8(n-1) + (2n-1) + 16 bytes,
+    plus one read-modify-write of the open recombination-opportunity cell per epoch (16 E) and the 8-byte weight prefix;
+    a resampling row additionally gathers the parent's S bytes.  The lag-bucket ring the gather also moves is NOT
+    counted: it is overhead of the current design, visible as traffic > algorithmic."""
+    S = 8 * (n - 1) + (2 * n - 1) + 16
+    return N * (2 * S + 16 * E + 8 + resample_fraction * S)
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    import smcsmc_b200 as S
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    rows, t_start, inv2N, seqlen = workload(a.len_mb)
+    R, E, N = len(rows.x_end), len(t_start), a.particles
+    max_rec = rows.max_epoch_to_record(ZIGZAG_LAGS)
+    # pinned host staging of the step's inputs (the e2e leg copies from here)
+    pin = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in
+           dict(x_end=rows.x_end, alleles=rows.alleles, is_site=rows.is_site, max_rec=max_rec).items()}
+    h2d = sum(t.numel() * t.element_size() for t in pin.values())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+
+    def make_engine(seed):
+        pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, chunk=rank, device=local)
+        pf.upload_rows(pin["x_end"].numpy(), pin["alleles"].numpy(), pin["is_site"].numpy(), pin["max_rec"].numpy())
+        return pf
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_tallies(t):
+        tt = torch.from_numpy(t).cuda()
+        if world > 1:
+            dist.all_reduce(tt)
+        return tt.cpu().numpy()
+
+    # ---- resident leg: rows in HBM, engine re-used ----
+    pf = make_engine(1)
+    def step_resident(seed):
+        flush.fill_(seed & 0xff)                     # flush L2 between iterations
+        torch.cuda.synchronize()
+        pf.reset(seed=seed)
+        pf.init_particles()
+        pf.sweep()
+        pf.finish()
+        return reduce_tallies(pf.tallies()), pf.ln_normalization_factor()
+    for w in range(a.warmup):
+        step_resident(100 + w)
+    clk = Clocks(local)
+    clk.start()
+    time.sleep(0.3)
+    ms0, l0 = pf.timing()
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(a.steps):
+        tallies, lnZ = step_resident(200 + k)
+    barrier()
+    wall = time.perf_counter() - t0
+    ms1, l1 = pf.timing()
+    counters = pf.counters()
+    pf.close()
+    dev_ms = ms1 - ms0
+    launches = l1 - l0
+    # ---- e2e leg: host buffers through the public calls, H2D + D2H inside the timed region ----
+    def step_e2e(seed):
+        p = make_engine(seed)
+        p.init_particles()
+        p.sweep()
+        p.finish()
+        out = reduce_tallies(p.tallies()), p.ln_normalization_factor()
+        p.close()
+        return out
+    step_e2e(300)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(a.steps):
+        step_e2e(400 + k)
+    barrier()
+    wall_e2e = time.perf_counter() - t0
+    clocks = clk.stop()
+    # max over ranks
+    if world > 1:
+        tt = torch.tensor([wall, wall_e2e, dev_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        wall, wall_e2e, dev_ms = [float(x) for x in tt.cpu()]
+    units = float(N) * seqlen * a.steps * world
+    rs_frac = counters["resamples"] / max(counters["rows"], 1)
+    row_launches = a.steps * R
+    avg_launch_s = dev_ms * 1e-3 / max(launches, 1)
+    abytes = algorithmic_bytes_per_launch(NSAM, N, E, rs_frac)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = abytes / avg_launch_s / 1e9
+    line = {
+        "metric": "particle*sites/sec (s per EM iteration in ms_per_step)", "value": units / wall,
+        "unit": "particle*sites/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": wall / a.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic (scrm-simulated zigzag, bench_data/, seed 1)",
+        "config": {"workload": "configs[1]: 8 haplotypes x %g Mb zigzag, %d particles, 11 epochs, 1 EM iteration per step"
+                               % (a.len_mb, N), "rows": R, "particles": N, "haplotypes": NSAM, "epochs": E,
+                   "per_gpu": "one 100 Mb chunk per GPU", "l2": "flushed between steps (256 MiB write)",
+                   "lags": "reference-calibrated (DESIGN.md)"},
+        "e2e": {"value": units / wall_e2e, "unit": "particle*sites/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 6 * E * 8 + 8, "ms_per_step": wall_e2e / a.steps * 1e3},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "smc_row_kernel", "avg_launch_us": avg_launch_s * 1e6,
+                     "algorithmic_bytes_per_launch": abytes, "peak_source": "measured" if peaks else "fallback",
+                     "note": "latency-bound at 10k particles: one launch per .seg row, %d rows/step" % R},
+        "clocks": clocks,
+        "device_ms_per_step": dev_ms / a.steps,
+        "particle_rows_per_s": float(N) * R * a.steps * world / wall,
+        "resample_fraction": rs_frac, "lnZ": lnZ,
+    }
+    if rank == 0:
+        if not a.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_reference_sample(a)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the reference's own CPU implementation of the path (oracle/_ref/smcsmc, built unmodified from the reference)
+# ---------------------------------------------------------------------------------------------------------------
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "smcsmc")
+
+
+def _host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def _ref_chunk_cmd(seg_path, out_prefix, start, length, particles, seed):
+    theta, R = 4 * N0 * MU * length, 4 * N0 * RHO * length
+    cmd = [REF_BIN, "-nsam", str(NSAM), "-Np", str(particles), "-N0", repr(N0), "-t", repr(theta), "-r", repr(R),
+           str(int(length))]
+    for t in ZIGZAG_TIMES:
+        cmd += ["-eN", repr(t), "1"]
+    cmd += ["-EM", "0", "-seed", str(seed), "-seg", seg_path, "-startpos", str(int(start)), "-o", out_prefix]
+    return cmd
+
+
+def reference_sample(particles, chunk_mb, cores, seed=1):
+    """Time the reference binary the way smc2 parallelises it (model.py:563-662,1094-1100): `cores` independent chunk
+    processes of chunk_mb Mb each, one per host core, wall time of the slowest.  Returns (particle*sites/s, seconds)."""
+    import gzip
+    if not os.path.exists(REF_BIN):
+        raise RuntimeError("oracle/_ref/smcsmc missing (built by __graft_entry__.build() where /root/reference exists)")
+    length = chunk_mb * 1e6
+    with tempfile.TemporaryDirectory() as tmp:
+        seg = os.path.join(tmp, "sample.seg")
+        need = cores * length + 1
+        with gzip.open(SEG, "rt") as f, open(seg, "w") as g:
+            for line in f:
+                g.write(line)
+                if int(line.split("\t", 1)[0]) > need:
+                    break
+        t0 = time.perf_counter()
+        procs = [subprocess.Popen(_ref_chunk_cmd(seg, os.path.join(tmp, "c%d" % c), 1 + c * length, length, particles,
+                                                 seed + c), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                 for c in range(cores)]
+        rcs = [p.wait() for p in procs]
+        wall = time.perf_counter() - t0
+        if any(rcs):
+            raise RuntimeError("reference smcsmc exited with %s" % rcs)
+        ok = all("LogL" in open(os.path.join(tmp, "c%d.out" % c)).read() for c in range(cores))
+        if not ok:
+            raise RuntimeError("reference run wrote no LogL row")
+    return cores * particles * length / wall, wall
+
+
+def cpu_reference_sample(a):
+    cores = _host_cores()
+    particles, chunk_mb = a.cpu_particles, a.cpu_chunk_mb
+    v, wall = reference_sample(particles, chunk_mb, cores)
+    return {"value": v, "unit": "particle*sites/s", "cores": cores, "kind": "reference",
+            "sample": "%d chunk processes x %g Mb of the same .seg x %d particles, same 11-epoch model, -EM 0, wall of the "
+                      "slowest (%.1f s, includes the reference's ~3 s per-process lag calibration)"
+                      % (cores, chunk_mb, particles, wall)}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = _host_cores()
+    for w in range(min(a.warmup, 1)):                       # one warm-up pass is enough for a CPU binary (page cache)
+        reference_sample(max(a.cpu_particles // 10, 10), a.cpu_chunk_mb, cores, seed=50)
+    t0 = time.perf_counter()
+    vals = []
+    for k in range(a.steps):
+        v, wall = reference_sample(a.cpu_particles, a.cpu_chunk_mb, cores, seed=60 + k)
+        vals.append(v)
+    total = time.perf_counter() - t0
+    value = cores * a.cpu_particles * a.cpu_chunk_mb * 1e6 * a.steps / total
+    sample = ("%d chunk processes x %g Mb x %d particles per step (bounded sample of configs[1]; the reference is linear "
+              "in particles x length)" % (cores, a.cpu_chunk_mb, a.cpu_particles))
+    line = {"impl": "reference", "metric": "particle*sites/sec (s per EM iteration in ms_per_step)", "value": value,
+            "unit": "particle*sites/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": total / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic (scrm-simulated zigzag, bench_data/, seed 1)",
+            "config": {"workload": "configs[1]: 8 haplotypes x 100 Mb zigzag, 11 epochs -- bounded sample: " + sample},
+            "cpu_baseline": {"value": value, "unit": "particle*sites/s", "cores": cores, "kind": "reference",
+                             "sample": sample},
+            "e2e": {"value": value, "unit": "particle*sites/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=10000)
+    ap.add_argument("--len-mb", type=float, default=100.0)
+    ap.add_argument("--cpu-particles", type=int, default=300)
+    ap.add_argument("--cpu-chunk-mb", type=float, default=1.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

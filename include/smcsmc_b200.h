@@ -84,6 +84,12 @@ int smc_init_particles(smc_engine* e);
  * Asynchronous: returns after enqueueing; any getter synchronises. */
 int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end);
 
+/* Start another EM iteration on the same rows (the reference re-enters pfARG_core, smcsmc.cpp:83): clears particles,
+ * tallies, ln normaliser and counters; optionally replaces the rates the M-step changed (CountModel::reset_Ne /
+ * reset_recomb_rate, count.cpp:267-325).  inv2N / vb_logfac may be NULL (unchanged); rho <= 0 means unchanged.
+ * The lags (and with them the tally schedule) stay as uploaded. */
+int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_logfac, uint64_t seed);
+
 /* End of data: final normalisation and flush of all pending tallies with lag 0 (smcsmc.cpp:371-373). */
 int smc_finish(smc_engine* e);
 

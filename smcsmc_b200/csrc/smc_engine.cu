@@ -797,7 +797,8 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
   const int E = e->cfg.E, n = e->cfg.n;
   for (int64_t r = 0; r < R; r++) {
     double prev = r ? x_end[r - 1] : e->cfg.start_pos;
-    if (!(x_end[r] > prev)) return fail(SMC_ERR_ARG, "row ends must be strictly increasing and beyond start_pos");
+    // a zero-length row is legal: two typed sites at one position (the reference just skips the extension loop)
+    if (!(x_end[r] >= prev)) return fail(SMC_ERR_ARG, "row ends must be non-decreasing and not before start_pos");
     if (x_end[r] > e->cfg.seqlen) return fail(SMC_ERR_ARG, "row end beyond seqlen");
     for (int k = 0; k < n; k++) {
       int a = alleles[r * n + k];
@@ -919,6 +920,31 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
   cudaEventElapsedTime(&ms, e->ev0, e->ev1);
   e->kernel_ms += ms;
   CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_logfac, uint64_t seed) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows first");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  Params& P = e->P;
+  const int E = e->cfg.E;
+  for (int ep = 0; ep < E; ep++) {
+    if (inv2N) { if (!(inv2N[ep] > 0)) return fail(SMC_ERR_ARG, "inv2N must be positive"); P.m.inv2N[ep] = inv2N[ep]; }
+    if (vb_logfac) P.m.vb_logfac[ep] = vb_logfac[ep];
+  }
+  if (rho > 0) P.m.rho = rho;
+  P.seed = seed;
+  const size_t cells = (size_t)E * P.B * 4;
+  for (int b = 0; b < 2; b++) CUDA_TRY(cudaMemsetAsync(P.buf[b].ring, 0, cells * (size_t)P.N * sizeof(double), e->stream));
+  CUDA_TRY(cudaMemsetAsync(P.tallies, 0, 6 * (size_t)E * sizeof(double), e->stream));
+  CUDA_TRY(cudaMemsetAsync(P.anc, 0xff, (size_t)P.N * sizeof(int), e->stream));
+  Ctrl init;
+  memset(&init, 0, sizeof(init));
+  init.cons_done = -1;
+  CUDA_TRY(cudaMemcpyAsync(P.ctrl, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  e->swept = 0; e->inited = false; e->finished = false;
   return 0;
 }
 

@@ -71,6 +71,12 @@ class ParticleFilter:
     def finish(self):
         check(lib().smc_finish(self._h))
 
+    def reset(self, inv2N=None, rho=0.0, vb_logfac=None, seed=1):
+        """next EM iteration on the same rows, optionally with the rates the M-step produced"""
+        a = None if inv2N is None else _f64(inv2N)
+        b = None if vb_logfac is None else _f64(vb_logfac)
+        check(lib().smc_reset(self._h, None if a is None else _P(a), rho, None if b is None else _P(b), seed))
+
     # --- results ---
     def particles(self):
         nn = 2 * self.n - 1

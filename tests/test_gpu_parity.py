@@ -130,10 +130,13 @@ def test_normalize_log(S):
         S.normalize_log(np.full(4, -np.inf))
 
 
-def _rows(n, R, seqlen, seed, p_missing=0.0, p_unphased=0.0, p_var=0.3, partial=0.0):
+def _rows(n, R, seqlen, seed, p_missing=0.0, p_unphased=0.0, p_var=0.3, partial=0.0, dup=False):
     rng = np.random.default_rng(seed)
     x_end = np.sort(rng.choice(np.arange(50, int(seqlen)), size=R - 1, replace=False)).astype(np.float64)
     x_end = np.append(x_end, float(seqlen))
+    if dup:      # two typed sites at one position: zero-length rows are legal .seg input
+        x_end[5] = x_end[4]
+        x_end[R // 2] = x_end[R // 2 - 1]
     al = (rng.random((R, n)) < p_var).astype(np.int8)
     for r in range(R):
         for i in range(0, n - 1, 2):
@@ -149,7 +152,7 @@ def _rows(n, R, seqlen, seed, p_missing=0.0, p_unphased=0.0, p_var=0.3, partial=
 
 CASES = {
     # name: (n, N, R, seqlen, t_start, inv2N, lags, row kwargs)
-    "const4": (4, 96, 60, 60000.0, [0.0], [1 / 2e4], [5000.0], {}),
+    "const4": (4, 96, 60, 60000.0, [0.0], [1 / 2e4], [5000.0], dict(dup=True)),
     "epochs3_n4_missing": (4, 130, 80, 80000.0, [0.0, 4000.0, 20000.0], [1 / 2e4, 1 / 8e3, 1 / 3e4],
                            [9000.0, 2500.0, 800.0], dict(p_missing=0.2, partial=0.2)),
     "zigzag11_n8": (8, 200, 50, 40000.0, [4e4 * t for t in (0, .0025, .005, .01, .02, .04, .08, .16, .32, .64, 1.28)],
