@@ -38,11 +38,15 @@ SEG = os.path.join(ROOT, "bench_data", "zigzag_n8_100Mb_seed1.seg.gz")
 NSAM = 8
 
 
-def workload(len_mb):
-    from smcsmc_b200.segdata import read_seg
-    seqlen = len_mb * 1e6
+def workload(len_mb, chunks):
+    """rows of the `chunks` equal windows of the first len_mb Mb -- the -startpos / -chunks decomposition of the
+    reference frontend (smcsmc/model.py:563-662): each chunk is an independent sweep that restarts from the prior"""
+    from smcsmc_b200.segdata import parse_seg, window_rows
+    seqlen = len_mb * 1e6 / chunks
     max_seg_len = int(2.0 / (RHO * 4 * N0))                    # pfparam.cpp:364
-    rows = read_seg(SEG, NSAM, seqlen, data_start=1, max_segment_length=max_seg_len)
+    raw = parse_seg(SEG, NSAM)
+    rows = [window_rows(raw, seqlen, data_start=1 + int(c * seqlen), max_segment_length=max_seg_len)
+            for c in range(chunks)]
     t_start = [4 * N0 * t for t in ZIGZAG_TIMES]
     inv2N = [1.0 / (2 * N0)] * len(t_start)
     return rows, t_start, inv2N, seqlen
@@ -106,66 +110,89 @@ def run_ours(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
-    rows, t_start, inv2N, seqlen = workload(a.len_mb)
-    R, E, N = len(rows.x_end), len(t_start), a.particles
-    max_rec = rows.max_epoch_to_record(ZIGZAG_LAGS)
+    C = a.chunks
+    rows, t_start, inv2N, seqlen = workload(a.len_mb, C)
+    R, E, N = sum(len(r.x_end) for r in rows), len(t_start), a.particles
     # pinned host staging of the step's inputs (the e2e leg copies from here)
-    pin = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in
-           dict(x_end=rows.x_end, alleles=rows.alleles, is_site=rows.is_site, max_rec=max_rec).items()}
-    h2d = sum(t.numel() * t.element_size() for t in pin.values())
+    pin = []
+    for r in rows:
+        d = dict(x_end=r.x_end, alleles=r.alleles, is_site=r.is_site, max_rec=r.max_epoch_to_record(ZIGZAG_LAGS))
+        pin.append({k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in d.items()})
+    h2d = sum(t.numel() * t.element_size() for d in pin for t in d.values())
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
 
-    def make_engine(seed):
-        pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, chunk=rank, device=local)
-        pf.upload_rows(pin["x_end"].numpy(), pin["alleles"].numpy(), pin["is_site"].numpy(), pin["max_rec"].numpy())
-        return pf
+    def make_engines(seed):
+        pfs = []
+        for c in range(C):
+            pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, chunk=rank * C + c,
+                                  device=local, ess_fraction=a.ess)
+            d = pin[c]
+            pf.upload_rows(d["x_end"].numpy(), d["alleles"].numpy(), d["is_site"].numpy(), d["max_rec"].numpy())
+            pfs.append(pf)
+        return pfs
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def reduce_tallies(t):
+    def collect(pfs):
+        t = np.sum([pf.tallies() for pf in pfs], axis=0)          # chunk tallies are summed (model.py:1176-1184)
+        lnz = float(np.sum([pf.ln_normalization_factor() for pf in pfs]))
         tt = torch.from_numpy(t).cuda()
         if world > 1:
-            dist.all_reduce(tt)
-        return tt.cpu().numpy()
+            dist.all_reduce(tt)                                    # once per EM iteration
+        return tt.cpu().numpy(), lnz
 
-    # ---- resident leg: rows in HBM, engine re-used ----
-    pf = make_engine(1)
+    def timing(pfs):
+        ms, k = 0.0, 0
+        for pf in pfs:
+            m_, k_ = pf.timing()
+            ms += m_; k += k_
+        return ms, k
+
+    def sweep_all(pfs):
+        for pf in pfs:
+            pf.init_particles()
+        S.sweep_many(pfs, a.rows_per_turn)
+        for pf in pfs:
+            pf.finish()
+
+    # ---- resident leg: rows in HBM, engines re-used ----
+    pfs = make_engines(1)
     def step_resident(seed):
         flush.fill_(seed & 0xff)                     # flush L2 between iterations
         torch.cuda.synchronize()
-        pf.reset(seed=seed)
-        pf.init_particles()
-        pf.sweep()
-        pf.finish()
-        return reduce_tallies(pf.tallies()), pf.ln_normalization_factor()
+        for pf in pfs:
+            pf.reset(seed=seed)
+        sweep_all(pfs)
+        return collect(pfs)
     for w in range(a.warmup):
         step_resident(100 + w)
     clk = Clocks(local)
     clk.start()
     time.sleep(0.3)
-    ms0, l0 = pf.timing()
+    ms0, l0 = timing(pfs)
     barrier()
     t0 = time.perf_counter()
     for k in range(a.steps):
         tallies, lnZ = step_resident(200 + k)
     barrier()
     wall = time.perf_counter() - t0
-    ms1, l1 = pf.timing()
-    counters = pf.counters()
-    pf.close()
+    ms1, l1 = timing(pfs)
+    cs = [pf.counters() for pf in pfs]
+    counters = {k: sum(c[k] for c in cs) for k in cs[0]}
+    for pf in pfs:
+        pf.close()
     dev_ms = ms1 - ms0
     launches = l1 - l0
     # ---- e2e leg: host buffers through the public calls, H2D + D2H inside the timed region ----
     def step_e2e(seed):
-        p = make_engine(seed)
-        p.init_particles()
-        p.sweep()
-        p.finish()
-        out = reduce_tallies(p.tallies()), p.ln_normalization_factor()
-        p.close()
+        p = make_engines(seed)
+        sweep_all(p)
+        out = collect(p)
+        for pf in p:
+            pf.close()
         return out
     step_e2e(300)
     barrier()
@@ -180,9 +207,8 @@ def run_ours(a):
         tt = torch.tensor([wall, wall_e2e, dev_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         wall, wall_e2e, dev_ms = [float(x) for x in tt.cpu()]
-    units = float(N) * seqlen * a.steps * world
+    units = float(N) * seqlen * C * a.steps * world
     rs_frac = counters["resamples"] / max(counters["rows"], 1)
-    row_launches = a.steps * R
     avg_launch_s = dev_ms * 1e-3 / max(launches, 1)
     abytes = algorithmic_bytes_per_launch(NSAM, N, E, rs_frac)
     peaks = {}
@@ -197,17 +223,18 @@ def run_ours(a):
         "unit": "particle*sites/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": wall / a.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic (scrm-simulated zigzag, bench_data/, seed 1)",
-        "config": {"workload": "configs[1]: 8 haplotypes x %g Mb zigzag, %d particles, 11 epochs, 1 EM iteration per step"
-                               % (a.len_mb, N), "rows": R, "particles": N, "haplotypes": NSAM, "epochs": E,
-                   "per_gpu": "one 100 Mb chunk per GPU", "l2": "flushed between steps (256 MiB write)",
+        "config": {"workload": "configs[1]: 8 haplotypes x %g Mb zigzag, %d particles, 11 epochs, 1 EM iteration per step, "
+                               "swept as %d concurrent chunks (smc2 -chunks)" % (a.len_mb, N, C), "chunks": C, "rows": R, "particles": N, "haplotypes": NSAM, "epochs": E,
+                   "per_gpu": "the whole %g Mb data set per GPU" % a.len_mb, "l2": "flushed between steps (256 MiB write)",
                    "lags": "reference-calibrated (DESIGN.md)"},
         "e2e": {"value": units / wall_e2e, "unit": "particle*sites/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 6 * E * 8 + 8, "ms_per_step": wall_e2e / a.steps * 1e3},
+                "d2h_bytes_per_step": C * (6 * E * 8 + 8), "ms_per_step": wall_e2e / a.steps * 1e3},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "kernel": "smc_row_kernel", "avg_launch_us": avg_launch_s * 1e6,
                      "algorithmic_bytes_per_launch": abytes, "peak_source": "measured" if peaks else "fallback",
-                     "note": "latency-bound at 10k particles: one launch per .seg row, %d rows/step" % R},
+                     "note": "one launch per .seg row and chunk (%d rows/step), %d chunks concurrent; avg_launch_us = "
+                             "device time / launches" % (R, C)},
         "clocks": clocks,
         "device_ms_per_step": dev_ms / a.steps,
         "particle_rows_per_s": float(N) * R * a.steps * world / wall,
@@ -319,6 +346,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--particles", type=int, default=10000)
     ap.add_argument("--len-mb", type=float, default=100.0)
+    ap.add_argument("--chunks", type=int, default=16, help="independent chunks swept concurrently (smc2 -chunks)")
+    ap.add_argument("--rows-per-turn", type=int, default=4)
+    ap.add_argument("--ess", type=float, default=0.5, help="-ESS resampling threshold fraction (reference default 0.5)")
     ap.add_argument("--cpu-particles", type=int, default=300)
     ap.add_argument("--cpu-chunk-mb", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

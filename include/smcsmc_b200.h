@@ -81,8 +81,14 @@ int smc_init_particles(smc_engine* e);
  *   extend_ARGs + update_weight_at_site + normalize_probability   (particleContainer.cpp:441-466)
  *   CountModel::extract_and_update_count                          (count.cpp:355-415)
  *   ParticleContainer::resample                                   (particleContainer.cpp:247-311)
- * Asynchronous: returns after enqueueing; any getter synchronises. */
+ * Returns when the rows are done (the launches themselves queue back to back without host round trips). */
 int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end);
+
+/* Sweep ALL remaining rows of `count` engines (one per chunk; the reference runs chunks as independent processes,
+ * smcsmc/model.py:563-662,1094-1100).  Launches are issued round-robin, rows_per_turn rows of each engine at a time, on
+ * the engines' own streams, so the chunks' row kernels run concurrently on the device.  Returns when all are done; the
+ * device time of the whole group is booked on engines[0] (smc_get_timing). */
+int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn);
 
 /* Start another EM iteration on the same rows (the reference re-enters pfARG_core, smcsmc.cpp:83): clears particles,
  * tallies, ln normaliser and counters; optionally replaces the rates the M-step changed (CountModel::reset_Ne /

@@ -35,6 +35,7 @@ SYMBOLS = {
     "smc_init_particles": (_I, [_V]),
     "smc_sweep": (_I, [_V, _I64, _I64]),
     "smc_finish": (_I, [_V]),
+    "smc_sweep_many": (_I, [_V, ctypes.c_int32, _I64]),
     "smc_reset": (_I, [_V, _V, _D, _V, ctypes.c_uint64]),
     "smc_get_tallies": (_I, [_V, _V]),
     "smc_get_lnZ": (_I, [_V, c_dp]),

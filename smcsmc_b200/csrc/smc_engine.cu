@@ -290,8 +290,20 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int v = 0; v < nn; v++) T.par(v) = src.parent[(size_t)v * P.N + a];
     // ring: gather everything on a pull; consumed buckets are cleared either way
     if (resampled) {
+      // 8 independent loads in flight per thread before the stores (the two copies never alias)
       const int cells = E * P.B * 4;
-      for (int q = 0; q < cells; q++) dst.ring[(size_t)q * P.N + i] = src.ring[(size_t)q * P.N + a];
+      const double* __restrict__ sp = src.ring + a;
+      double* __restrict__ dp = dst.ring + i;
+      const size_t NN = (size_t)P.N;
+      int q = 0;
+      for (; q + 8 <= cells; q += 8) {
+        double v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = __ldcs(sp + (size_t)(q + k) * NN);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dp[(size_t)(q + k) * NN] = v[k];
+      }
+      for (; q < cells; q++) dp[(size_t)q * NN] = sp[(size_t)q * NN];
     }
     for (int q = c0; q < c1; q++) {
       int2 ek = P.cons[q];
@@ -919,6 +931,56 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
   float ms = 0;
   cudaEventElapsedTime(&ms, e->ev0, e->ev1);
   e->kernel_ms += ms;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
+  if (!engines || count < 1) return fail(SMC_ERR_ARG, "no engines");
+  if (rows_per_turn < 1) rows_per_turn = 1;
+  for (int k = 0; k < count; k++) {
+    smc_engine* e = engines[k];
+    if (!e) return fail(SMC_ERR_ARG, "null engine");
+    if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
+    if (e->finished) return fail(SMC_ERR_STATE, "sweep after finish");
+  }
+  // every engine has its own stream: launches of different chunks interleave and run concurrently on the device
+  CUDA_TRY(cudaSetDevice(engines[0]->cfg.device));
+  cudaEventRecord(engines[0]->ev0, engines[0]->stream);
+  for (int k = 1; k < count; k++) {
+    CUDA_TRY(cudaSetDevice(engines[k]->cfg.device));
+    if (engines[k]->cfg.device == engines[0]->cfg.device) cudaStreamWaitEvent(engines[k]->stream, engines[0]->ev0, 0);
+  }
+  bool more = true;
+  while (more) {
+    more = false;
+    for (int k = 0; k < count; k++) {
+      smc_engine* e = engines[k];
+      if (e->swept >= e->P.R) continue;
+      CUDA_TRY(cudaSetDevice(e->cfg.device));
+      int64_t stop = std::min<int64_t>(e->P.R, e->swept + rows_per_turn);
+      for (int64_t r = e->swept; r < stop; r++) launch_row(e, 0);
+      e->swept = stop;
+      if (e->swept < e->P.R) more = true;
+    }
+  }
+  double span = 0.0;
+  for (int k = 0; k < count; k++) {
+    smc_engine* e = engines[k];
+    CUDA_TRY(cudaSetDevice(e->cfg.device));
+    cudaEventRecord(e->ev1, e->stream);
+  }
+  for (int k = 0; k < count; k++) {
+    smc_engine* e = engines[k];
+    CUDA_TRY(cudaSetDevice(e->cfg.device));
+    CUDA_TRY(cudaEventSynchronize(e->ev1));
+    if (e->cfg.device == engines[0]->cfg.device) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, engines[0]->ev0, e->ev1);
+      span = std::max(span, (double)ms);
+    }
+  }
+  engines[0]->kernel_ms += span;     // device span of the whole group, booked on the first engine
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

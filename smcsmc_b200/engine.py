@@ -118,6 +118,12 @@ class ParticleFilter:
         return ms.value, k.value
 
 
+def sweep_many(filters, rows_per_turn=8):
+    """sweep all remaining rows of several ParticleFilters (chunks) concurrently on the device"""
+    arr = (ctypes.c_void_p * len(filters))(*[f._h for f in filters])
+    check(lib().smc_sweep_many(arr, len(filters), rows_per_turn))
+
+
 # ---- stand-alone functions (each mirrors one reference member function) ----
 def site_likelihood(parent, height, alleles, mu, ancestral_aware=False, device=0):
     """ForestState::calculate_likelihood averaged over phasings (particle.cpp:667, particleContainer.cpp:204-221)."""

@@ -49,10 +49,11 @@ def _alleles(field, nsam):
     return out
 
 
-def read_seg(path, nsam, seqlen, data_start=1, max_segment_length=1e99):
-    """Segment::prepare + the row stream of read_new_line, up to the row that reaches seqlen."""
+def parse_seg(path, nsam):
+    """Segment::prepare's line parser (segdata.cpp:55-120): every data line of the file, validated, as arrays
+    (start[int64], length[int64], alleles[int8, nsam])."""
     opener = gzip.open if str(path).endswith(".gz") else open
-    buf = []   # (start, length, state, alleles)
+    starts, lens, als = [], [], []
     next_start = -1
     with opener(path, "rt") as f:
         for line in f:
@@ -86,51 +87,65 @@ def read_seg(path, nsam, seqlen, data_start=1, max_segment_length=1e99):
             if next_start > -1 and next_start != seg_start:
                 raise InvalidSeg("Segments are not consecutive")
             next_start = seg_start + seg_len
-            if seg_start >= data_start + seqlen:
-                break
-            if seg_start + seg_len > data_start:
-                while True:
-                    if seg_len > max_segment_length:
-                        seg_len = int(max_segment_length)
-                        state = 0   # SEGMENT_INVARIANT_PARTIAL
-                    else:
-                        state = 1   # SEGMENT_INVARIANT
-                    if seg_start + seg_len > data_start:
-                        buf.append((seg_start, seg_len, state, al))
-                    seg_start += seg_len
-                    seg_len = next_start - seg_start
-                    if not seg_start < next_start:
-                        break
+            starts.append(seg_start); lens.append(seg_len); als.append(al)
+    return (np.array(starts, dtype=np.int64), np.array(lens, dtype=np.int64),
+            np.array(als, dtype=np.int8).reshape(len(starts), nsam))
+
+
+def window_rows(raw, seqlen, data_start=1, max_segment_length=1e99, path="<seg>"):
+    """The row stream of Segment for the window [data_start, data_start + seqlen): long rows split into
+    INVARIANT_PARTIAL pieces (segdata.cpp:125-144), stream cut at the row that reaches seqlen (smcsmc.cpp:353-356)."""
+    starts_all, lens_all, al_all = raw
+    buf = []   # (start, length, state, allele row index)
+    lo = int(np.searchsorted(starts_all + lens_all, data_start, side="right"))
+    for idx in range(lo, len(starts_all)):
+        seg_start, seg_len = int(starts_all[idx]), int(lens_all[idx])
+        next_start = seg_start + seg_len
+        if seg_start >= data_start + seqlen:
+            break
+        if seg_start + seg_len > data_start:
+            while True:
+                if seg_len > max_segment_length:
+                    seg_len = int(max_segment_length)
+                    state = 0   # SEGMENT_INVARIANT_PARTIAL
+                else:
+                    state = 1   # SEGMENT_INVARIANT
+                if seg_start + seg_len > data_start:
+                    buf.append((seg_start, seg_len, state, idx))
+                seg_start += seg_len
+                seg_len = next_start - seg_start
+                if not seg_start < next_start:
+                    break
     if not buf:
         raise InvalidSeg("No data found in file %s between positions %d and %d" % (path, data_start, data_start + seqlen))
     R = len(buf)
     starts = np.array([b[0] for b in buf], dtype=np.int64)
     lens = np.array([b[1] for b in buf], dtype=np.int64)
-    al = np.array([b[3] for b in buf], dtype=np.int8)
+    al = al_all[np.array([b[3] for b in buf])]
     state = np.array([b[2] for b in buf], dtype=np.uint8)
     s = np.maximum(starts - data_start, 0).astype(np.float64)
     e = (starts - data_start + lens).astype(np.float64)
-    # the sweep stops at the row that reaches the locus end (smcsmc.cpp:353-356)
     stop = R
-    for r in range(R):
-        if e[r] >= seqlen:
-            stop = r + 1
-            break
+    hit = np.nonzero(e >= seqlen)[0]
+    if len(hit):
+        stop = int(hit[0]) + 1
     allmiss = (al == -1).all(axis=1)
     dist = np.zeros(R)
-    for r in range(R):
-        d = 0.0
+    for r in np.nonzero(allmiss)[0]:
         i = r
+        d = 0.0
         while i >= 0 and allmiss[i]:
             d = float(starts[r] - starts[i])
             i -= 1
-        if not allmiss[r]:
-            d = 0.0
-        else:
-            j = r
-            while j < R and allmiss[j]:
-                j += 1
-            if j < R:
-                d = min(d, float(starts[j] + lens[j] - starts[r]))
+        j = r
+        while j < R and allmiss[j]:
+            j += 1
+        if j < R:
+            d = min(d, float(starts[j] + lens[j] - starts[r]))
         dist[r] = d
     return SegRows(s[:stop], np.minimum(e[:stop], seqlen), al[:stop], state[:stop], dist[:stop], float(seqlen))
+
+
+def read_seg(path, nsam, seqlen, data_start=1, max_segment_length=1e99):
+    """Segment::prepare + the row stream of read_new_line, up to the row that reaches seqlen."""
+    return window_rows(parse_seg(path, nsam), seqlen, data_start, max_segment_length, path)

@@ -336,6 +336,31 @@ def test_large_population_properties(S):
     pf.close()
 
 
+def test_sweep_many_concurrent_chunks(S):
+    """several chunks swept concurrently on their own streams give exactly what separate sweeps give"""
+    n, N, R, seqlen, t_start, inv2N, lags, kw = CASES["epochs3_n4_missing"]
+    sets = [_rows(n, R - 7 * c, seqlen, seed=40 + c, **kw) for c in range(3)]
+
+    def make(c):
+        pf = S.ParticleFilter(n, N, t_start, inv2N, 2.5e-8, 1e-8, seqlen, lags, seed=6, chunk=c)
+        pf.upload_rows(*sets[c])
+        pf.init_particles()
+        return pf
+    a = [make(c) for c in range(3)]
+    S.sweep_many(a, rows_per_turn=3)
+    b = [make(c) for c in range(3)]
+    for pf in b:
+        pf.sweep()
+    for x, y in zip(a, b):
+        x.finish(); y.finish()
+        assert x.counters() == y.counters()
+        px, py = x.particles(), y.particles()
+        assert np.array_equal(px[0], py[0]) and np.array_equal(px[1], py[1]) and np.array_equal(px[2], py[2])
+        assert x.ln_normalization_factor() == y.ln_normalization_factor()
+        np.testing.assert_allclose(x.tallies(), y.tallies(), rtol=1e-12, atol=1e-300)
+        x.close(); y.close()
+
+
 def test_errors(S):
     with pytest.raises(S.SmcError):
         S.ParticleFilter(1, 10, [0.0], [1.0], 1e-8, 1e-8, 1e5, [1e3])
