@@ -94,6 +94,7 @@ struct TreeView {
   double* L0;         // [nn][BS] scratch
   double* L1;         // [nn][BS] scratch
   double* LEN;        // [E][BS]  local branch length inside each epoch
+  double* ACC;        // [E][BS]  recombination opportunity summed over the current row
   int BS, t;
   __device__ __forceinline__ double& h(int v) const { return H[v * BS + t]; }
   __device__ __forceinline__ signed char& par(int v) const { return PAR[v * BS + t]; }
@@ -234,16 +235,17 @@ struct NullSink {
   __device__ void coal(int, double, int, double) const {}
   __device__ void rec_event(int, double) const {}
   __device__ void rec_opp(int, double, double, double) const {}
+  __device__ void row_begin(double) const {}
+  __device__ void row_end() const {}
 };
 
 // One SMC' transition at position x (Forest::sampleNextGenealogy with exact window 0).  The test-side CPU restatement
 // consumes the same Philox draws in the same order, so the two can be compared draw for draw.
 template <class Sink>
 __device__ inline void smc_move(const ModelDev& m, const TreeView& T, Rng& r, double x, int max_rec_epoch, Sink& sink,
-                                double& logw) {
+                                double& logw, double tl) {
   const int n = m.n, nn = m.nn;
-  // 1. recombination point, uniform on the local tree (forest.cc:370-412)
-  double tl = tree_length(m, T);
+  // 1. recombination point, uniform on the local tree (forest.cc:370-412); tl = tree_length of the current tree
   double target = rng_uniform(r) * tl;
   int b = -1;
   double hh = 0.0, cum = 0.0;
@@ -342,8 +344,10 @@ __device__ inline int extend_row(const ModelDev& m, const TreeView& T, Rng& r, d
   int nmiss = 0;
   for (int i = 0; i < n; i++) nmiss += data[i] == -1;
   const int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);   // particleContainer.cpp:103-111
-  double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tree_length(m, T) : branch_length_with_data(m, T, data);
+  double tl = tree_length(m, T);
+  double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
   epoch_tree_length(m, T);
+  sink.row_begin(x1);
   double updated_to = x0;
   int nrec = 0;
   while (updated_to < x1) {
@@ -355,14 +359,16 @@ __device__ inline int extend_row(const ModelDev& m, const TreeView& T, Rng& r, d
     }
     updated_to = new_to;
     if (updated_to < x1) {
-      smc_move(m, T, r, updated_to, max_rec_epoch, sink, logw);
+      smc_move(m, T, r, updated_to, max_rec_epoch, sink, logw, tl);
       nrec++;
+      tl = tree_length(m, T);
       if (leaf_status == 0) L_obs = branch_length_with_data(m, T, data);
-      if (leaf_status == 1) L_obs = tree_length(m, T);
+      if (leaf_status == 1) L_obs = tl;
       epoch_tree_length(m, T);
-      next_base = draw_next_base(m, tree_length(m, T), r, updated_to);
+      next_base = draw_next_base(m, tl, r, updated_to);
     }
   }
+  sink.row_end();
   if (is_site) logw += log(site_likelihood(m, T, data));
   return nrec;
 }

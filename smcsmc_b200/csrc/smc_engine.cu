@@ -80,6 +80,7 @@ struct Params {
   const unsigned char* is_site;
   const int* max_rec;
   const int* kstart;       // [R][E] bucket index at the row's left end
+  const int* kslot;        // [R][E] kstart modulo the ring depth B
   const int* ub_off;       // [E+1]
   const double* ub;        // bucket upper bounds per epoch (last = +inf: the end-of-data bucket)
   const int* cons_off;     // [R+1]
@@ -97,12 +98,18 @@ struct Params {
   double* rs_pos; double* rs_ess; long long rs_cap;
 };
 
-// Tally sink writing into the particle's lag-bucket ring.
+// Tally sink writing into the particle's lag-bucket ring.  Recombination opportunity (the dense record: every epoch,
+// every stretch) is summed in shared memory over the row and written once per epoch at the row end, unless a bucket
+// bound of that epoch falls inside the row (then each stretch is split at the bound and written directly).
 struct RingSink {
   const Params* P;
   double* ring;    // destination copy
   int i;           // particle index
-  const int* ks;   // kstart of this row [E]
+  const int* ks;   // bucket index of this row's left end [E]
+  const int* ksl;  // the same modulo the ring depth [E]
+  double* ACC;     // [E][BS] shared
+  int BS, t;
+  unsigned long long split;   // bit e: a bound of epoch e lies inside this row
   __device__ __forceinline__ int bucket(int e, double x) const {
     int k = ks[e];
     const double* ub = P->ub + P->ub_off[e];
@@ -110,15 +117,34 @@ struct RingSink {
     return k;
   }
   __device__ __forceinline__ double* cell(int e, int k, int q) const {
-    return ring + ((size_t)((e * P->B + (k % P->B)) * 4 + q)) * P->N + i;
+    int s = ksl[e] + (k - ks[e]);
+    if (s >= P->B) s -= P->B;
+    return ring + ((size_t)((e * P->B + s) * 4 + q)) * (size_t)P->N + i;
+  }
+  __device__ void row_begin(double x1) {
+    split = 0ull;
+    for (int e = 0; e < P->m.E; e++) {
+      ACC[e * BS + t] = 0.0;
+      if (P->ub[P->ub_off[e] + ks[e]] < x1) split |= 1ull << e;
+    }
+  }
+  __device__ void row_end() const {
+    for (int e = 0; e < P->m.E; e++) {
+      double a = ACC[e * BS + t];
+      if (a != 0.0) *cell(e, ks[e], 3) += a;
+    }
   }
   __device__ void coal(int e, double x, int cnt, double opp) const {
-    int k = bucket(e, x);
+    int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
     if (cnt) *cell(e, k, 0) += 1.0;
     *cell(e, k, 1) += opp;
   }
-  __device__ void rec_event(int e, double x) const { *cell(e, bucket(e, x), 2) += 1.0; }
+  __device__ void rec_event(int e, double x) const {
+    int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
+    *cell(e, k, 2) += 1.0;
+  }
   __device__ void rec_opp(int e, double xa, double xb, double rate) const {
+    if (!((split >> e) & 1ull)) { ACC[e * BS + t] += rate * (xb - xa); return; }
     int k = bucket(e, xa);
     const double* ub = P->ub + P->ub_off[e];
     while (xa < xb) {
@@ -219,7 +245,8 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   T.L0 = T.H + (size_t)nn * BS;
   T.L1 = T.L0 + (size_t)nn * BS;
   T.LEN = T.L1 + (size_t)nn * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.LEN + (size_t)E * BS);
+  T.ACC = T.LEN + (size_t)E * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)E * BS);
   __shared__ double red[3][4];
   __shared__ double tal[6][4];
   __shared__ bool is_last;
@@ -326,7 +353,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
-    RingSink sink{&P, dst.ring, (int)i, P.kstart + row * E};
+    RingSink sink{&P, dst.ring, (int)i, P.kstart + row * E, P.kslot + row * E, T.ACC, BS, t, 0ull};
     nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
   }
 
@@ -512,8 +539,8 @@ __global__ void __launch_bounds__(128) smc_init_kernel(const __grid_constant__ P
   TreeView T;
   T.BS = BS; T.t = t;
   T.H = reinterpret_cast<double*>(smem_raw);
-  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.LEN + (size_t)m.E * BS);
+  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS; T.ACC = T.LEN + (size_t)m.E * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)m.E * BS);
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= P.N) return;
   Rng r;
@@ -539,8 +566,8 @@ __global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long co
   TreeView T;
   T.BS = BS; T.t = t;
   T.H = reinterpret_cast<double*>(smem_raw);
-  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.LEN + (size_t)m.E * BS);
+  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS; T.ACC = T.LEN + (size_t)m.E * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)m.E * BS);
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= count) return;
   for (int v = 0; v < nn; v++) { T.h(v) = height[i * nn + v]; T.par(v) = (signed char)parent[i * nn + v]; }
@@ -687,7 +714,7 @@ int use_device(int device) {
   return 0;
 }
 
-size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * ((size_t)nn * 25 + (size_t)E * 8) + 16; }
+size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * ((size_t)nn * 25 + (size_t)E * 16) + 16; }
 
 int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, int aa, const double* t_start,
                const double* inv2N, const double* vb, const uint8_t* mask) {
@@ -852,7 +879,7 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
     ub_flat.insert(ub_flat.end(), ub[ep].begin(), ub[ep].end());
   }
   // bucket at each row's left end, and the ring depth needed: buckets in flight = [next to consume, highest written]
-  std::vector<int> kstart((size_t)R * E);
+  std::vector<int> kstart((size_t)R * E), kslot((size_t)R * E);
   std::vector<int> kcur(E, 0), consumed(E, 0);
   int B = 1;
   for (int64_t r = 0; r < R; r++) {
@@ -872,10 +899,10 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
   std::vector<int> mr(R);
   for (int64_t r = 0; r < R; r++) mr[r] = max_rec_epoch ? max_rec_epoch[r] : E - 1;
   int rc;
-  double* d_x; signed char* d_al; unsigned char* d_site; int* d_mr; int* d_ks; int* d_uboff; double* d_ub; int* d_co; int2* d_cons;
+  double* d_x; signed char* d_al; unsigned char* d_site; int* d_mr; int* d_ks; int* d_ksl; int* d_uboff; double* d_ub; int* d_co; int2* d_cons;
   if ((rc = dev_alloc(e, &d_x, R, false)) || (rc = dev_alloc(e, &d_al, (size_t)R * n, false)) ||
       (rc = dev_alloc(e, &d_site, R, false)) || (rc = dev_alloc(e, &d_mr, R, false)) ||
-      (rc = dev_alloc(e, &d_ks, (size_t)R * E, false)) || (rc = dev_alloc(e, &d_uboff, E + 1, false)) ||
+      (rc = dev_alloc(e, &d_ks, (size_t)R * E, false)) || (rc = dev_alloc(e, &d_ksl, (size_t)R * E, false)) || (rc = dev_alloc(e, &d_uboff, E + 1, false)) ||
       (rc = dev_alloc(e, &d_ub, ub_flat.size(), false)) || (rc = dev_alloc(e, &d_co, R + 1, false)) ||
       (rc = dev_alloc(e, &d_cons, cons.size(), false)) || (rc = dev_alloc(e, &e->first_pending_d, E, false)))
     return rc;
@@ -883,14 +910,16 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
   CUDA_TRY(cudaMemcpyAsync(d_al, alleles, (size_t)R * n, cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_site, is_site, R, cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_mr, mr.data(), R * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  for (size_t q = 0; q < kstart.size(); q++) kslot[q] = kstart[q] % B;
   CUDA_TRY(cudaMemcpyAsync(d_ks, kstart.data(), kstart.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_ksl, kslot.data(), kslot.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_uboff, ub_off.data(), ub_off.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_ub, ub_flat.data(), ub_flat.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_co, cons_off.data(), cons_off.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   if (!cons.empty())
     CUDA_TRY(cudaMemcpyAsync(d_cons, cons.data(), cons.size() * sizeof(int2), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, e->first_pending_h.data(), E * sizeof(int), cudaMemcpyHostToDevice, e->stream));
-  P.x_end = d_x; P.alleles = d_al; P.is_site = d_site; P.max_rec = d_mr; P.kstart = d_ks; P.ub_off = d_uboff; P.ub = d_ub;
+  P.x_end = d_x; P.alleles = d_al; P.is_site = d_site; P.max_rec = d_mr; P.kstart = d_ks; P.kslot = d_ksl; P.ub_off = d_uboff; P.ub = d_ub;
   P.cons_off = d_co; P.cons = d_cons;
   // the ring and the resampling log need R / B
   const size_t cells = (size_t)E * B * 4;
