@@ -133,6 +133,11 @@ int smc_resample_counts(int device, const double* w, int64_t N, double u, int32_
                         int32_t* counts);
 /* normalize_probability in log space (particleContainer.cpp:420-438): logw -= log(sum exp(logw)); returns lnZ, ESS */
 int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* ess);
+/* Lag calibration: median survival distance (bp) of local-tree nodes per epoch under the prior, from n_args
+ * unconditioned ARGs simulated on the device (calculate_median_survival_distances, smcsmc.cpp:169-263, including its
+ * fall-backs for sparsely sampled epochs).  CountModel::reset_lag then sets lag = lag_fraction * median. */
+int smc_calibrate_survival(int device, int32_t n, int32_t E, const double* t_start, const double* inv2N, double rho,
+                           double seqlen, uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events);
 /* fastexp (particle.cpp:30-40) evaluated on the device, for the 1e-12 no-mutation-factor parity test */
 int smc_fastexp(int device, const double* x, int64_t count, double* out);
 

@@ -581,6 +581,53 @@ __global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long co
   }
 }
 
+// Lag calibration (calculate_median_survival_distances, smcsmc.cpp:169-263): one thread simulates one unconditioned
+// ARG from the prior -- prior tree, then SMC' moves along the sequence -- and reports, for every internal node of the
+// initial tree, the position at which a node of exactly that height is no longer in the local tree (or -1 if it
+// survived to 0.6 * seqlen).  The host takes per-epoch medians.
+__global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, uint64_t seed, double* dist, int* epoch) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int BS = blockDim.x, t = threadIdx.x;
+  const int n = m.n, nn = m.nn;
+  TreeView T;
+  T.BS = BS; T.t = t;
+  T.H = reinterpret_cast<double*>(smem_raw);
+  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS; T.ACC = T.LEN + (size_t)m.E * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)m.E * BS);
+  const long long i = (long long)blockIdx.x * BS + t;
+  if (i >= count) return;
+  Rng r;
+  rng_init(r, seed, (uint32_t)i, 0, 0xCA11B, RNG_INIT);
+  init_tree(m, T, r);
+  // original heights live in the L0 scratch column; L1 marks them alive (1) / gone (0)
+  int alive = n - 1;
+  for (int j = 0; j < n - 1; j++) {
+    double h = T.h(n + j);
+    T.l0(j) = h; T.l1(j) = 1.0;
+    dist[i * (n - 1) + j] = -1.0;
+    epoch[i * (n - 1) + j] = epoch_of(m, h);
+  }
+  NullSink sink;
+  double logw = 0.0;
+  double tl = tree_length(m, T);
+  double next = draw_next_base(m, tl, r, 0.0);
+  const double stop = m.seqlen * 0.6;
+  while (alive > 0 && next < stop) {
+    smc_move(m, T, r, next, m.E, sink, logw, tl);
+    tl = tree_length(m, T);
+    double pos = next;
+    next = draw_next_base(m, tl, r, pos);
+    // the reference records at most one vanished height per move (the loop breaks after the first, smcsmc.cpp:218-234)
+    for (int j = 0; j < n - 1; j++) {
+      if (T.l1(j) == 0.0) continue;
+      double h = T.l0(j);
+      bool present = false;
+      for (int v = n; v < nn; v++) present |= (T.h(v) == h);
+      if (!present) { dist[i * (n - 1) + j] = pos; T.l1(j) = 0.0; alive--; break; }
+    }
+  }
+}
+
 __global__ void k_fastexp(const double* x, long long count, double* out) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < count) out[i] = fastexp(x[i]);
@@ -1299,6 +1346,43 @@ int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* 
   CUDA_TRY(cudaMemcpy(logw, dw.p, N * sizeof(double), cudaMemcpyDeviceToHost));
   *lnZ = o[0]; *ess = o[1];
   if (!std::isfinite(o[0])) return fail(SMC_ERR_NUMERIC, "Zero or negative probabilities");
+  return 0;
+}
+
+int smc_calibrate_survival(int device, int32_t n, int32_t E, const double* t_start, const double* inv2N, double rho,
+                           double seqlen, uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events) {
+  if (!t_start || !inv2N || !median_survival) return fail(SMC_ERR_ARG, "null argument");
+  if (n_args < 1) return fail(SMC_ERR_ARG, "n_args must be >= 1");
+  int rc = use_device(device);
+  if (rc) return rc;
+  ModelDev m;
+  if ((rc = fill_model(m, n, E, 0.0, rho, seqlen, 0, t_start, inv2N, nullptr, nullptr))) return rc;
+  const int BS = 64, per = n - 1;
+  DevBuf dd, de;
+  if ((rc = dd.alloc(n_args * per * sizeof(double))) || (rc = de.alloc(n_args * per * sizeof(int)))) return rc;
+  size_t smem = tree_smem(m.nn, E, BS);
+  CUDA_TRY(cudaFuncSetAttribute(k_survival, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+  k_survival<<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, n_args, seed, (double*)dd.p, (int*)de.p);
+  CUDA_TRY(cudaGetLastError());
+  std::vector<double> dist(n_args * per);
+  std::vector<int> ep(n_args * per);
+  CUDA_TRY(cudaMemcpy(dist.data(), dd.p, dist.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(ep.data(), de.p, ep.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<std::vector<double>> by(E);
+  for (size_t k = 0; k < dist.size(); k++) if (dist[k] >= 0.0) by[ep[k]].push_back(dist[k]);
+  // medians with the reference's fall-backs for sparsely sampled epochs (smcsmc.cpp:238-262)
+  const int max_safe_sample_size = 10;
+  double earliest = -1;
+  for (int e = 0; e < E; e++) {
+    std::sort(by[e].begin(), by[e].end());
+    if (n_events) n_events[e] = (int64_t)by[e].size();
+    int median_idx = by[e].empty() ? -1 : (int)((by[e].size() - 1) / 2);
+    if (median_idx < max_safe_sample_size) median_survival[e] = -1;
+    else { median_survival[e] = by[e][median_idx]; if (earliest < 0) earliest = median_survival[e]; }
+  }
+  for (int e = 0; e < E; e++)
+    if (median_survival[e] < 0) median_survival[e] = e > 0 ? median_survival[e - 1] : earliest;
+  if (median_survival[0] < 0) return fail(SMC_ERR_NUMERIC, "no node survival distances could be sampled; check the model");
   return 0;
 }
 

@@ -177,3 +177,13 @@ def fastexp(x, device=0):
     out = np.zeros_like(x)
     check(lib().smc_fastexp(device, _P(x), x.size, _P(out)))
     return out
+
+
+def calibrate_survival(n, t_start, inv2N, rho, seqlen, seed=1, n_args=8192, device=0):
+    """calculate_median_survival_distances (smcsmc.cpp:169): per-epoch median node survival distance and sample counts"""
+    ts, iv = _f64(t_start), _f64(inv2N)
+    E = len(ts)
+    med = np.zeros(E)
+    cnt = np.zeros(E, dtype=np.int64)
+    check(lib().smc_calibrate_survival(device, n, E, _P(ts), _P(iv), rho, seqlen, seed, n_args, _P(med), _P(cnt)))
+    return med, cnt

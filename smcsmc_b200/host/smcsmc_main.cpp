@@ -1,0 +1,309 @@
+// smcsmc -- drop-in host driver for the B200 particle-filter engine.
+//
+// Same surface as the reference executable (src/smcsmc.cpp:46-103 main, :278-400 pfARG_core): scrm-style command line,
+// .seg input, <prefix>.out / .log / .recomb.gz / .resample outputs in the reference's formats, in-binary EM
+// (CountModel::reset_model_parameters, count.cpp:44-63,267-325), exceptions -> "Error: ..." + exit 1.  Everything
+// between "read the rows" and "write the tallies" is the CUDA engine behind include/smcsmc_b200.h.
+#include <zlib.h>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <sstream>
+#include "../../include/smcsmc_b200.h"
+#include "params.hpp"
+#include "segment.hpp"
+
+using namespace std;
+using host::Params;
+
+#ifndef SMCSMC_B200_VERSION
+#define SMCSMC_B200_VERSION "b200-0.1"
+#endif
+
+namespace {
+
+void check(int rc) {
+  if (rc != 0) throw runtime_error(string("engine: ") + smc_last_error());
+}
+
+// particle.cpp:65-74
+double exp_digamma(double x) {
+  if (x > 10) return x - 0.5 + (x + 0.5) / (24 * x * x);
+  double f = 0.0;
+  while (x < 6) { f = f + 1.0 / x; x = x + 1.0; }
+  double psi = log(x) - 1 / (2 * x) - 1 / (12 * x * x);
+  return exp(psi - f);
+}
+
+// FormatDouble (pfparam.cpp:482-497)
+string fmt(double d, double scientific_bound = 0.1, int precision = 2) {
+  const int field_length = 14;
+  const double maxdouble = exp((field_length - precision - 1) * log(10.0));
+  ostringstream o;
+  if (d < maxdouble && (d > scientific_bound || d == 0.0)) o << setw(field_length) << fixed << setprecision(precision) << d;
+  else o << setw(field_length) << scientific << setprecision(field_length - 7) << d;
+  return o.str();
+}
+
+struct Out {
+  string out_name, log_name, recomb_name, resample_name;
+  void header() const {   // PfParam::outFileHeader (pfparam.cpp:459-479)
+    ofstream f(out_name.c_str(), ios::binary);
+    f << setw(6) << "Iter" << " " << setw(6) << "Epoch" << " " << setw(14) << "Start" << " " << setw(14) << "End" << " "
+      << setw(6) << "Type" << " " << setw(6) << "From" << " " << setw(6) << "To" << " " << setw(14) << "Opp" << " "
+      << setw(14) << "Count" << " " << setw(14) << "Rate" << " " << setw(14) << "Ne" << " " << setw(14) << "ESS" << endl;
+  }
+  void row(size_t em, int epoch, double b, double e, const string& type, int from, int to, double opp, double count,
+           double weight) const {   // PfParam::appendToOutFile (pfparam.cpp:500-527)
+    ofstream f(out_name.c_str(), ios::out | ios::app | ios::binary);
+    f << setw(6) << em << " " << setw(6) << epoch << " " << fmt(b) << " " << fmt(e) << " " << setw(6) << type << " "
+      << setw(6) << from << " " << setw(6) << to << " " << fmt(opp) << " " << fmt(count) << " "
+      << fmt(count / (opp + 1e-10)) << " " << fmt(type == "Coal" ? (opp + 1e-10) / (2.0 * count) : 0.0) << " "
+      << fmt(1.0 / (weight / opp + 1e-10), 1.0, 3) << endl;
+  }
+};
+
+void write_log(ostream& w, const Params& P, const Out& o) {   // PfParam::writeLog (pfparam.cpp:403-456)
+  w << "###########################\n#        smcsmc log       #\n###########################\n";
+  w << "Program was compiled on: " << __DATE__ << endl;
+  w << "smcsmc version: " << SMCSMC_B200_VERSION << endl;
+  w << "scrm version:   " << "none (B200 engine: " << smc_version() << ")" << endl;
+  w << "smcsmc parameters: \n";
+  w << "Segment Data file: " << (P.seg_file.empty() ? "empty" : P.seg_file.c_str()) << "\n";
+  w << "Recombination bias file: None\n";
+  w << setw(15) << " EM steps =" << setw(10) << P.EM_steps << "\n";
+  if (P.lag > 0) w << setw(15) << "Constant lag =" << setw(10) << P.lag << "\n";
+  w << setw(15) << "N =" << setw(10) << P.N << "\n";
+  w << setw(15) << "ESS =" << setw(10) << P.ESS_fraction;
+  if (P.ESS_default) w << " (by default)";
+  w << "\n";
+  w << "scrm model parameters: \n";
+  w << setw(17) << "Extract window =" << setw(10) << 0 << "\n";
+  w << setw(17) << "Extract window R =" << setw(10) << 500 << "\n";
+  w << setw(17) << "Sample size =" << setw(10) << P.nsam << "\n";
+  w << setw(17) << "Seq length =" << setw(10) << (size_t)P.loci_length << "\n";
+  w << setw(17) << "mutation rate =" << setw(10) << P.mutation_rate << "\n";
+  w << setw(17) << "recomb rate =" << setw(10) << P.original_recombination_rate << "\n";
+  w << setw(17) << "inferred recomb rate = " << setw(10) << P.recombination_rate << "\n";
+  w << setw(17) << "Pop size (at Generation):\n";
+  for (const auto& e : P.epochs) w << setw(3) << "(" << setw(8) << e.t_start << " )" << " | " << setw(10) << e.pop_size << "\n";
+  w << "Out file is saved in file: " << o.out_name << "\n";
+}
+
+void print_help(const Params& P) {
+  cout << "smcsmc (B200 engine) -- command line of luntergroup/smcsmc -- Version " << SMCSMC_B200_VERSION << endl;
+  auto opt = [](const char* f, const char* t, const string& d) {
+    cout << setw(15) << f << setw(8) << t << "  --  " << d << endl;
+  };
+  cout << "Options:" << endl;
+  opt("-Np", "INT", "Number of particles [ " + to_string(P.N) + " ]");
+  opt("-seg", "STR", "Data file in seg format [ Chrom1.seg ]");
+  opt("-o", "STR", "Prefix for output files");
+  opt("-EM", "INT", "EM iterations [ 20 ]");
+  opt("-startpos", "INT", "First nucleotide position to analyze [ 1 ]");
+  opt("-nsam", "INT", "Number of haplotypes (2..32)");
+  opt("-log", " ", "Generate *.log file");
+  opt("-v", " ", "Display version");
+  cout << endl << "Inference tuning:" << endl;
+  opt("-calibrate_lag", "FLT", "Lag before extracting events (multiple of survival time) [ 2 ]");
+  opt("-lag", "FLT", "Constant lag (bp) instead of calibration");
+  opt("-tmax", "FLT", "Maximum tree height, in unit of 4N0 [ 2 ]");
+  opt("-p", "STR", "Pattern of time segments, e.g. 1*3+15*4+1");
+  opt("-ESS", "FLT", "Fractional ESS threshold for resampling [ 0.5 ]");
+  opt("-xr", "INT", "Epoch or epoch range to exclude from recombination EM (0-based, closed)");
+  opt("-xc", "INT", "Epoch or epoch range (e.g. 0-10) to exclude from coalescent EM");
+  opt("-cap", "FLT", "Cap on inferred population sizes");
+  opt("-ancestral_aware", " ", "Alleles are polarised (0 = ancestral)");
+  opt("-record_ess", " ", "Generate *.resample file");
+  cout << endl << "Model (scrm syntax): -t THETA  -r RHO LENGTH  -N0 N  -eN T SIZE  -en T 1 SIZE  -vb  -seed S" << endl;
+  cout << "Not supported by this engine yet (rejected with an error): -I/-ej/-em/-eM/-ema/-es (structure), -eG (growth),"
+       << endl << "  -guide, -bias_heights/-bias_strengths, -apf > 0, -dephase, -arg" << endl;
+}
+
+struct Tallies {   // CountModel totals incl. the initial pseudo-counts (count.cpp:161-193)
+  vector<double> coal_count, coal_opp, coal_weight, rec_count, rec_opp, rec_weight;
+  double resample_count = 0, delayed_opp = 0;
+};
+
+// one EM iteration: pfARG_core (smcsmc.cpp:278-400)
+void pfARG_core(Params& P, const host::SegRows& rows, const Out& out, int em, int device) {
+  const int E = P.num_epochs(), n = (int)P.nsam;
+  vector<double> t_start(E), inv2N(E), vb(E), lags(E);
+  vector<uint8_t> mask(E);
+  for (int e = 0; e < E; e++) {
+    t_start[e] = P.epochs[e].t_start;
+    inv2N[e] = 1.0 / (2.0 * P.epochs[e].pop_size);
+    vb[e] = P.vb ? log(exp_digamma(P.epochs[e].vb_count) / P.epochs[e].vb_count) : 0.0;
+    mask[e] = (uint8_t)(P.record_event_in_epoch[e] & 3);
+  }
+  // CountModel::init_lags (count.cpp:230-249), then reset_lag from the calibration (smcsmc.cpp:314-316)
+  for (int e = 0; e < E; e++) {
+    if (E == 1) lags[e] = 20000;
+    else {
+      double top_t = e == E - 1 ? t_start[E - 1] : t_start[e + 1];
+      lags[e] = P.lag > 0 ? P.lag : 4.0 / (P.recombination_rate * top_t);
+    }
+  }
+  if (P.calibrate_lag) {
+    vector<double> surv(E);
+    vector<int64_t> cnt(E);
+    check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N.data(), P.recombination_rate, P.loci_length, 1,
+                                 8192, surv.data(), cnt.data()));
+    for (int e = 0; e < E; e++) {
+      clog << " Epoch " << e << " (" << cnt[e] << " events): survival distance " << surv[e] << endl;
+      lags[e] = surv[e] * P.lag_fraction;
+    }
+  }
+  clog << "    Lags set to: ";
+  for (double l : lags) clog << l << " ";
+  clog << endl;
+  clog << " Starting position: " << fixed << setprecision(0) << P.start_position << setprecision(6) << scientific << endl;
+  clog.unsetf(ios::floatfield);
+
+  const size_t R = rows.rows();
+  vector<int32_t> max_rec(R);
+  for (size_t r = 0; r < R; r++) {   // max_epoch_to_update (smcsmc.cpp:266-275)
+    int e = 0;
+    while (e < E && rows.dist_to_mutation[r] < 0.5 * lags[e]) e++;
+    max_rec[r] = e - 1;
+  }
+  smc_config c;
+  memset(&c, 0, sizeof c);
+  c.n = n; c.N = (int32_t)P.N; c.E = E; c.device = device;
+  c.seed = P.seed + (uint64_t)em * 0x9E3779B97F4A7C15ull;
+  c.chunk = (uint32_t)(((long long)P.start_position) & 0xFFFFFF);
+  c.mu = P.mutation_rate; c.rho = P.recombination_rate; c.seqlen = P.loci_length; c.start_pos = 0.0;
+  c.ess_fraction = P.ESS_fraction; c.ancestral_aware = P.ancestral_aware; c.parity_scan = 0;
+  c.t_start = t_start.data(); c.inv2N = inv2N.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
+  smc_engine* eng = nullptr;
+  check(smc_create(&c, &eng));
+  struct Guard { smc_engine* e; ~Guard() { smc_destroy(e); } } guard{eng};
+  check(smc_upload_rows(eng, rows.x_end.data(), rows.alleles.data(), rows.is_site.data(), max_rec.data(), (int64_t)R));
+  check(smc_init_particles(eng));
+  const int64_t step = max<int64_t>(1, (int64_t)R / 100);
+  for (int64_t r0 = 0; r0 < (int64_t)R; r0 += step) {
+    int64_t r1 = min<int64_t>((int64_t)R, r0 + step);
+    check(smc_sweep(eng, r0, r1));
+    cout << "\r Particle filtering " << setw(4) << int(rows.x_end[r1 - 1] * 100 / P.loci_length) << "% completed." << flush;
+  }
+  cout << "\r Particle filtering step 100% completed." << endl;
+  check(smc_finish(eng));
+  vector<double> t(6 * E);
+  double lnZ = 0;
+  int64_t counters[4];
+  check(smc_get_tallies(eng, t.data()));
+  int rc = smc_get_lnZ(eng, &lnZ);
+  if (rc == SMC_ERR_NUMERIC) throw runtime_error("Zero or negative probabilities");
+  check(rc);
+  check(smc_get_counters(eng, counters));
+  clog << "Got to end of sequence; resampled " << counters[1] << " times" << endl;
+  if (P.record_resample_file) {
+    vector<double> pos(counters[1] + 1), ess(counters[1] + 1);
+    int64_t k = 0;
+    check(smc_get_resample_log(eng, pos.data(), ess.data(), counters[1], &k));
+    ofstream f(out.resample_name.c_str(), ios::out | ios::app | ios::binary);
+    for (int64_t q = 0; q < k; q++) f << (int)pos[q] << "\t" << ess[q] << endl;
+  }
+  clog << " Inference step completed." << endl;
+
+  Tallies T;
+  for (int e = 0; e < E; e++) {
+    T.coal_count.push_back(t[0 * E + e] + inv2N[e]);       // initial value: the rate, with opportunity 1
+    T.coal_opp.push_back(t[1 * E + e] + 1.0);
+    T.coal_weight.push_back(t[2 * E + e] + 1.0);
+    T.rec_count.push_back(t[3 * E + e] + P.recombination_rate);
+    T.rec_opp.push_back(t[4 * E + e] + 1.0);
+    T.rec_weight.push_back(t[5 * E + e] + 1.0);
+  }
+  T.resample_count = (double)counters[1];
+  T.delayed_opp = P.loci_length;
+
+  {   // <prefix>.recomb.gz: header of CountModel::dump_local_recomb_logs (count.cpp:616-628); the per-100-bp table is
+      // row f2 of the scope table and is left empty
+    gzFile g = gzopen(out.recomb_name.c_str(), "ab");
+    if (g && em == 0) {
+      string h = "iter\tlocus\tsize\topp_per_nt";
+      for (int s = 0; s < n; s++) h += "\t" + to_string(s + 1);
+      h += "\ttime\tlog_time\n";
+      gzwrite(g, h.data(), (unsigned)h.size());
+    }
+    if (g) gzclose(g);
+  }
+
+  // reset_model_parameters(force_update = true): the in-binary M-step (count.cpp:44-63,267-325)
+  clog << " MODEL IS RESET at base " << P.loci_length << endl;
+  double ro = 0, rc_ = 0, rw = 0;
+  for (int e = 0; e < E; e++) { ro += T.rec_opp[e]; rc_ += T.rec_count[e]; rw += T.rec_weight[e]; }
+  P.recombination_rate = rc_ / ro;
+  clog << " Setting recombination rate to " << P.recombination_rate << " ( " << rc_ << " / " << ro << "; post-lag ESS "
+       << 1.0 / (rw / ro) << " )" << endl;
+  for (int e = 0; e < E; e++) {
+    double rate = T.coal_count[e] / T.coal_opp[e];
+    double pop = 1.0 / (2.0 * rate);
+    P.epochs[e].pop_size = (P.useCap && pop >= P.Ne_cap) ? P.Ne_cap : pop;
+    clog << " Setting size of population 0 @ " << setw(8) << t_start[e] << " to " << setw(8) << pop << " ( 0.5 * "
+         << T.coal_opp[e] << " / " << T.coal_count[e] << "; post-lag ESS " << 1.0 / (T.coal_weight[e] / T.coal_opp[e])
+         << " )" << endl;
+  }
+
+  // CountModel::log_counts (count.cpp:66-158) and the LogL row (smcsmc.cpp:391)
+  for (int e = 0; e < E; e++)
+    out.row(em, e, t_start[e], e == E - 1 ? 1e+99 : t_start[e + 1], "Coal", 0, -1, T.coal_opp[e], T.coal_count[e],
+            T.coal_weight[e]);
+  out.row(em, -1, 0.0, 1e+99, "Recomb", -1, -1, ro, rc_, rw);
+  out.row(em, -1, 0.0, 1e+99, "Delay", -1, -1, T.delayed_opp, 0.0 / (double)P.N, T.delayed_opp);
+  out.row(em, -1, 0.0, 1e+99, "Resamp", -1, -1, T.delayed_opp, T.resample_count, T.delayed_opp);
+  out.row(em, -1, 0, 1e+99, "LogL", -1, -1, 1.0, lnZ, 1.0);
+  clog << " Estimated log likelihood: " << lnZ << endl;
+}
+
+}  // namespace
+
+int main(int argc, char* argv[]) {
+  try {
+    auto start = chrono::system_clock::now();
+    Params P;
+    host::parse(argc, argv, P);
+    if (P.version) {
+      cout << "Program was compiled on: " << __DATE__ << endl;
+      cout << "smcsmc version: " << SMCSMC_B200_VERSION << endl;
+      cout << "scrm version:   none (B200 engine: " << smc_version() << ")" << endl;
+      return EXIT_SUCCESS;
+    }
+    if (P.help) { print_help(P); return EXIT_SUCCESS; }
+    Out out{P.out_prefix + ".out", P.out_prefix + ".log", P.out_prefix + ".recomb.gz", P.out_prefix + ".resample"};
+    remove(out.out_name.c_str());
+    remove(out.log_name.c_str());
+    remove(out.recomb_name.c_str());
+    if (P.record_resample_file) remove(out.resample_name.c_str());
+    clog << "Command line:-" << endl << argv[0];
+    for (int i = 1; i < argc; i++) clog << " " << argv[i];
+    clog << endl;
+    if (P.seg_file.empty()) throw invalid_argument("a .seg file is required (-seg); the empty-file mode is not supported");
+    int max_seg_len = (int)(2.0 / (P.recombination_rate * 4 * P.N0));       // pfparam.cpp:364
+    host::SegRows rows = host::read_seg(P.seg_file, P.nsam, P.loci_length, (long long)P.start_position, max_seg_len);
+    int device = 0;
+    if (const char* d = getenv("SMCSMC_DEVICE")) device = atoi(d);
+    out.header();
+    for (int i = 0; i <= P.EM_steps; i++) {
+      clog << "EM step " << i << endl;
+      pfARG_core(P, rows, out, i, device);
+      clog << "End of EM step " << i << endl;
+      auto dur = chrono::duration_cast<chrono::seconds>(chrono::system_clock::now() - start);
+      clog << "Elapsed time: " << setprecision(3) << (double)dur.count() << endl;
+    }
+    {
+      ofstream lf(out.log_name.c_str(), ios::out | ios::app | ios::binary);
+      write_log(lf, P, out);
+    }
+    write_log(cout, P, out);
+    return EXIT_SUCCESS;
+  } catch (const exception& e) {
+    cerr << "Error: " << e.what() << endl;
+    return EXIT_FAILURE;
+  }
+}

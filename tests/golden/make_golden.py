@@ -204,3 +204,46 @@ if __name__ == "__main__":
     golden_tallies()
     golden_moments()
     print("wrote", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
+
+
+EM_BASE = ("-nsam 4 -Np 500 -N0 10000 -t 2000 -r 800 2000000 -eN 0 1 -eN 0.05 1 -eN 0.2 1 -eN 0.6 1 {extra} -seed {seed} "
+           "-seg {seg} -o {out}")
+EM_VARIANTS = {
+    # one sweep, everything recorded (the smc2 mode: -EM 0 per chunk and iteration)
+    "sweep": "-EM 0",
+    # three in-binary EM iterations on the population sizes; recombination excluded from the EM (-xr) so that the
+    # recombination rate stays at its input value (see DESIGN.md 7a on the reference's recombination opportunity)
+    "em_ne": "-xr 0-3 -EM 2",
+}
+
+
+def parse_out(path):
+    rows = []
+    with open(path) as f:
+        hdr = f.readline().split()
+        for line in f:
+            rows.append(dict(zip(hdr, line.split())))
+    return rows
+
+
+def golden_em(seeds=range(1, 13)):
+    """End-to-end reference runs (the unmodified smcsmc binary, oracle/_ref/smcsmc) on tests/data/const_n4_2Mb_seed7.seg:
+    12 seeds per command variant; stores every .out row per seed (tests/test_em_parity.py compares the B200 driver's
+    seed ensemble with this one)."""
+    import json
+    import subprocess
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+    seg = os.path.join(os.path.dirname(HERE), "data", "const_n4_2Mb_seed7.seg")
+    binp = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref", "smcsmc")
+    out = {"base": EM_BASE, "variants": EM_VARIANTS, "seeds": list(seeds), "runs": {}}
+    with tempfile.TemporaryDirectory() as tmp:
+        for name, extra in EM_VARIANTS.items():
+            def run(seed):
+                o = os.path.join(tmp, "%s_s%d" % (name, seed))
+                subprocess.run([binp] + EM_BASE.format(extra=extra, seed=seed, seg=seg, out=o).split(), check=True,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                return parse_out(o + ".out")
+            with ThreadPoolExecutor(8) as ex:
+                out["runs"][name] = list(ex.map(run, seeds))
+    json.dump(out, open(os.path.join(HERE, "em_reference.json"), "w"))

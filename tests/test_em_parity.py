@@ -1,0 +1,158 @@
+"""GPU end-to-end test of the drop-in `smcsmc` driver (smcsmc_b200/bin/smcsmc) against the UNMODIFIED reference binary:
+same .seg, same command lines, 12 seeds each (one sweep; three EM iterations on the population sizes).  RNG streams differ by design, so the comparison is
+between seed ensembles (template: the reference's own test/old/newtests/test_generic.py:313-398): per-epoch coalescent
+opportunity / count / Ne, recombination opportunity / count, and the log-likelihood estimate must agree within
+Monte-Carlo error (Welch z < 4.5) and within 10 % in the mean.  The reference ensemble is the committed fixture
+tests/golden/em_reference.json (tests/golden/make_golden.py::golden_em, oracle/_ref/smcsmc)."""
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "smcsmc_b200", "bin", "smcsmc")
+SEG = os.path.join(ROOT, "tests", "data", "const_n4_2Mb_seed7.seg")
+REF = os.path.join(ROOT, "tests", "golden", "em_reference.json")
+
+
+def parse_out(path):
+    rows = []
+    with open(path) as f:
+        hdr = f.readline().split()
+        for line in f:
+            rows.append(dict(zip(hdr, line.split())))
+    return hdr, rows
+
+
+@pytest.fixture(scope="module")
+def runs(tmp_path_factory):
+    ref = json.load(open(REF))
+    tmp = tmp_path_factory.mktemp("em")
+    mine = {}
+    for name, extra in ref["variants"].items():
+        mine[name] = []
+        for seed in ref["seeds"]:
+            out = str(tmp / ("%s_s%d" % (name, seed)))
+            cmd = [BIN] + ref["base"].format(extra=extra, seed=seed, seg=SEG, out=out).split()
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            assert r.returncode == 0, r.stderr[-2000:]
+            mine[name].append((out, r))
+    return ref, mine
+
+
+def test_out_file_format(runs):
+    ref, mine = runs
+    out, r = mine["em_ne"][0]
+    raw = open(out + ".out").read().splitlines()
+    # header exactly as PfParam::outFileHeader writes it (pfparam.cpp:459-479)
+    assert raw[0] == ("  Iter  Epoch          Start            End   Type   From     To            Opp          Count"
+                      "           Rate             Ne            ESS")
+    hdr, rows = parse_out(out + ".out")
+    types = [(x["Iter"], x["Type"]) for x in rows]
+    assert types == [(str(i), t) for i in (0, 1, 2) for t in ["Coal"] * 4 + ["Recomb", "Delay", "Resamp", "LogL"]]
+    ref_rows = ref["runs"]["em_ne"][0]
+    for a, b in zip(rows, ref_rows):       # identical layout: epochs, boundaries, From/To columns
+        for k in ("Iter", "Epoch", "Start", "End", "Type", "From", "To"):
+            assert a[k] == b[k], (k, a, b)
+        if a["Type"] in ("Recomb", "Delay"):           # -xr: only the pseudo-counts; Delay: locus length, 0
+            assert (a["Opp"], a["Count"], a["Rate"]) == (b["Opp"], b["Count"], b["Rate"]), (a, b)
+    for line in raw[1:]:
+        assert re.match(r"^ {1,5}\d+ +-?\d+ +\S+ +\S+ +\w+ +-?\d+ +-?\d+( +\S+){5}$", line), line
+        assert len(line) == len(raw[0])
+    assert os.path.exists(out + ".log") and "smcsmc log" in open(out + ".log").read()
+    import gzip
+    assert gzip.open(out + ".recomb.gz", "rt").readline().startswith("iter\tlocus\tsize\topp_per_nt\t1\t2\t3\t4\ttime")
+    assert "Lags set to:" in r.stderr and "survival distance" in r.stderr and "resampled" in r.stderr
+
+
+def _compare(ref_runs, mine_rows, skip=()):
+    nrows = len(ref_runs[0])
+    report = []
+    for k in range(nrows):
+        row = ref_runs[0][k]
+        typ = row["Type"]
+        if typ == "Delay":
+            continue
+        for col in ("Opp", "Count") if typ in ("Coal", "Recomb") else ("Count",):
+            if (typ, col) in skip:
+                continue
+            a = np.array([float(r[k][col]) for r in ref_runs])
+            b = np.array([float(r[k][col]) for r in mine_rows])
+            se = np.sqrt(a.var(ddof=1) / len(a) + b.var(ddof=1) / len(b)) + 1e-300
+            report.append((row["Iter"], row["Epoch"], typ, col, a.mean(), b.mean(), (b.mean() - a.mean()) / se,
+                           b.mean() / a.mean() - 1))
+    msg = "\n".join("iter %s epoch %s %-6s %-5s ref %.6g ours %.6g z %+.2f rel %+.3f" % r for r in report)
+    print(msg)
+    for it, ep, typ, col, ma, mb, z, rel in report:
+        tol = 0.25 if (typ == "Coal" and ep == "0") else 0.10      # epoch 0 holds ~25 events per run
+        assert abs(z) < 4.5 and abs(rel) < tol, msg
+    return report
+
+
+def test_single_sweep_within_monte_carlo_error(runs):
+    """one sweep (-EM 0, the mode smc2 drives): coalescent opportunity and counts per epoch, recombination COUNT, number
+    of resampling events and the log-likelihood estimate agree with the reference's seed ensemble"""
+    ref, mine = runs
+    mine_rows = [parse_out(out + ".out")[1] for out, _ in mine["sweep"]]
+    _compare(ref["runs"]["sweep"], mine_rows, skip={("Recomb", "Opp")})
+    # Recombination OPPORTUNITY is the one documented difference: with resampling active the reference
+    # records ~15-20 % less opportunity than sum_i w_i * tree_length_i * bp, which inflates its rate estimate; ours
+    # is consistent with the recombination count and with the data's own total tree length (segregating sites / mu).
+    k = [i for i, r in enumerate(ref["runs"]["sweep"][0]) if r["Type"] == "Recomb"][0]
+    ref_opp = np.mean([float(r[k]["Opp"]) for r in ref["runs"]["sweep"]])
+    opp = np.array([float(r[k]["Opp"]) for r in mine_rows])
+    cnt = np.array([float(r[k]["Count"]) for r in mine_rows])
+    assert 0.75 < ref_opp / opp.mean() < 0.92
+    rho = 800 / 4e4 / (2e6 - 1)
+    assert (cnt / opp).mean() == pytest.approx(rho, rel=0.05)            # self-consistent: count / opportunity = rho
+    n_seg = sum(1 for line in open(SEG) if not line.startswith("#")) - 1
+    assert opp.mean() == pytest.approx(n_seg / 2.5e-8, rel=0.05)         # Watterson: total length = S / mu
+
+
+def test_em_iterations_within_monte_carlo_error(runs):
+    """three in-binary EM iterations on the population sizes (M-step: CountModel::reset_Ne, count.cpp:267-294)"""
+    ref, mine = runs
+    mine_rows = [parse_out(out + ".out")[1] for out, _ in mine["em_ne"]]
+    _compare(ref["runs"]["em_ne"], mine_rows)
+    ref0 = ref["runs"]["em_ne"][0]
+    for k in range(len(ref0)):
+        if ref0[k]["Type"] == "Coal" and ref0[k]["Iter"] == "2" and ref0[k]["Epoch"] != "0":
+            ne = np.array([float(r[k]["Ne"]) for r in mine_rows])
+            assert 8000 < ne.mean() < 12500, (ref0[k]["Epoch"], ne.mean())     # simulated truth: 10 000
+
+
+def test_cli_errors_and_help():
+    r = subprocess.run([BIN, "-v"], capture_output=True, text=True)
+    assert r.returncode == 0 and "smcsmc version" in r.stdout
+    r = subprocess.run([BIN], capture_output=True, text=True)
+    assert r.returncode == 0 and "-Np" in r.stdout
+    r = subprocess.run([BIN, "-Np", "10", "-t", "10"], capture_output=True, text=True)
+    assert r.returncode == 1 and r.stderr.strip().endswith("Error: The option -r is required")
+    r = subprocess.run([BIN, "-Np", "10", "-t", "10", "-r", "10", "1000", "-I", "2", "2", "2", "-seg", SEG],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and "not supported by the B200 engine yet" in r.stderr
+    r = subprocess.run([BIN, "-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", "-seg", "/nonexistent.seg"],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and "Invalid input file" in r.stderr
+
+
+def test_calibration_matches_reference_survival_distances():
+    """device lag calibration vs the reference's own calculate_median_survival_distances for the zigzag model
+    (stderr of oracle/_ref/smcsmc, n = 8, 11 epochs; the reference uses ~200-1000 samples per epoch, i.e. ~10 % noise)"""
+    import smcsmc_b200 as S
+    ref = [740410, 244677, 120493, 60241.7, 33575.1, 19323.7, 10830.1, 7052.04, 4387.76, 2505.14, 1309.92]
+    t = [4e4 * x for x in (0, .0025, .005, .01, .02, .04, .08, .16, .32, .64, 1.28)]
+    med, cnt = S.calibrate_survival(8, t, [1 / 2e4] * 11, 1e-8 * 1e8 / (1e8 - 1), 1e8, seed=3, n_args=16384)
+    assert np.all(cnt[1:] > 200)
+    np.testing.assert_allclose(med[1:7], ref[1:7], rtol=0.15)
+    # deep epochs: the reference counts a node as alive while it lingers UNPRUNED in scrm's node container
+    # (is_height_in_tree, smcsmc.cpp:106-113: any node with a local child, unary leftovers included; pruning is lazy
+    # and rarely reaches high nodes), so its distances are 15-30 % longer there than the local tree's own node
+    # life times that the device measures
+    ratio = med[7:] / np.array(ref[7:])
+    assert np.all(ratio > 0.65) and np.all(ratio < 1.05), ratio
+    assert med[0] == pytest.approx(ref[0], rel=0.35)            # epoch 0: few nodes are that young
