@@ -104,6 +104,7 @@ def run_ours(a):
     import torch
     import torch.distributed as dist
     import smcsmc_b200 as S
+    from smcsmc_b200.sharding import allreduce_tallies
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -139,10 +140,7 @@ def run_ours(a):
     def collect(pfs):
         t = np.sum([pf.tallies() for pf in pfs], axis=0)          # chunk tallies are summed (model.py:1176-1184)
         lnz = float(np.sum([pf.ln_normalization_factor() for pf in pfs]))
-        tt = torch.from_numpy(t).cuda()
-        if world > 1:
-            dist.all_reduce(tt)                                    # once per EM iteration
-        return tt.cpu().numpy(), lnz
+        return allreduce_tallies(t, lnz, device="cuda")           # the one exchange per EM iteration (NCCL when N > 1)
 
     def timing(pfs):
         ms, k = 0.0, 0
@@ -173,12 +171,16 @@ def run_ours(a):
     clk.start()
     time.sleep(0.3)
     ms0, l0 = timing(pfs)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     barrier()
     t0 = time.perf_counter()
+    ev[0].record()
     for k in range(a.steps):
         tallies, lnZ = step_resident(200 + k)
+    ev[1].record()
     barrier()
-    wall = time.perf_counter() - t0
+    wall_host = time.perf_counter() - t0
+    wall = ev[0].elapsed_time(ev[1]) * 1e-3       # device clock; every step ends with a device-wide synchronize
     ms1, l1 = timing(pfs)
     cs = [pf.counters() for pf in pfs]
     counters = {k: sum(c[k] for c in cs) for k in cs[0]}
@@ -196,11 +198,12 @@ def run_ours(a):
         return out
     step_e2e(300)
     barrier()
-    t0 = time.perf_counter()
+    ev[2].record()
     for k in range(a.steps):
         step_e2e(400 + k)
+    ev[3].record()
     barrier()
-    wall_e2e = time.perf_counter() - t0
+    wall_e2e = ev[2].elapsed_time(ev[3]) * 1e-3
     clocks = clk.stop()
     # max over ranks
     if world > 1:
@@ -236,7 +239,7 @@ def run_ours(a):
                      "note": "one launch per .seg row and chunk (%d rows/step), %d chunks concurrent; avg_launch_us = "
                              "device time / launches" % (R, C)},
         "clocks": clocks,
-        "device_ms_per_step": dev_ms / a.steps,
+        "device_ms_per_step": dev_ms / a.steps, "host_wall_ms_per_step": wall_host / a.steps * 1e3,
         "particle_rows_per_s": float(N) * R * a.steps * world / wall,
         "resample_fraction": rs_frac, "lnZ": lnZ,
     }
