@@ -88,14 +88,16 @@ struct ModelDev {
 };
 
 // Per-thread view of the particle's tree in shared memory.
-struct TreeView {
+template <int BS_>
+struct TreeViewT {
+  static constexpr int BS = BS_;   // compile-time block size: column addressing v * BS + t folds into shifts
   double* H;          // [nn][BS]
   signed char* PAR;   // [nn][BS]
-  double* L0;         // [nn][BS] scratch
-  double* L1;         // [nn][BS] scratch
+  double* L0;         // [n-1][BS] scratch for the internal nodes, addressed by node id (base shifted by -n rows)
+  double* L1;         // [n-1][BS]
   double* LEN;        // [E][BS]  local branch length inside each epoch
   double* ACC;        // [E][BS]  recombination opportunity summed over the current row
-  int BS, t;
+  int t;
   __device__ __forceinline__ double& h(int v) const { return H[v * BS + t]; }
   __device__ __forceinline__ signed char& par(int v) const { return PAR[v * BS + t]; }
   __device__ __forceinline__ double& l0(int v) const { return L0[v * BS + t]; }
@@ -103,8 +105,28 @@ struct TreeView {
   __device__ __forceinline__ double& len(int e) const { return LEN[e * BS + t]; }
 };
 
+// Carve a block's dynamic shared memory into the per-thread columns of a TreeView.  Leaves need no likelihood scratch
+// (their partials follow from the allele), so L0/L1 hold n-1 rows and are addressed through a base shifted by n rows.
+__host__ __device__ inline size_t tree_bytes_per_thread(int nn, int E) {
+  return (size_t)nn * 9 + (size_t)(nn - 1) * 8 + (size_t)E * 16;
+}
+template <int BS>
+__device__ __forceinline__ TreeViewT<BS> make_tree_view(unsigned char* smem, int n, int nn, int E, int t) {
+  TreeViewT<BS> T;
+  T.t = t;
+  T.H = reinterpret_cast<double*>(smem);
+  double* l = T.H + (size_t)nn * BS;
+  T.L0 = l - (size_t)n * BS;
+  T.L1 = l + (size_t)(nn - n) * BS - (size_t)n * BS;
+  T.LEN = l + (size_t)2 * (nn - n) * BS;
+  T.ACC = T.LEN + (size_t)E * BS;
+  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)E * BS);
+  return T;
+}
+
 // forest.h:188 getLocalTreeLength: sum of branch lengths in slot order (the order the parity tests assume)
-__device__ inline double tree_length(const ModelDev& m, const TreeView& T) {
+template <class TV>
+__device__ inline double tree_length(const ModelDev& m, const TV& T) {
   double len = 0.0;
   for (int v = 0; v < m.nn; v++) {
     int p = T.par(v);
@@ -117,7 +139,8 @@ __device__ inline double tree_length(const ModelDev& m, const TreeView& T) {
 // Iterative form of the reference's recursion: nodes are visited children-first (leaves, then internal slots in
 // increasing height), each node hands its value to its parent; the lower-numbered child arrives first, which is the
 // reference's left/right order.
-__device__ inline double branch_length_with_data(const ModelDev& m, const TreeView& T, const signed char* data) {
+template <class TV>
+__device__ inline double branch_length_with_data(const ModelDev& m, const TV& T, const signed char* data) {
   const int n = m.n, nn = m.nn;
   for (int v = n; v < nn; v++) { T.l0(v) = -2.0; T.l1(v) = -2.0; }   // -2 = child value not yet delivered
   double total = 0.0;
@@ -142,7 +165,8 @@ __device__ inline double branch_length_with_data(const ModelDev& m, const TreeVi
 }
 
 // particle.cpp:625-680: two-state Felsenstein pruning for one fully specified haplotype (0 / 1 / -1 missing).
-__device__ inline double prune_likelihood(const ModelDev& m, const TreeView& T, const signed char* hap) {
+template <class TV>
+__device__ inline double prune_likelihood(const ModelDev& m, const TV& T, const signed char* hap) {
   const int n = m.n, nn = m.nn;
   for (int v = n; v < nn; v++) { T.l0(v) = 1.0; T.l1(v) = 1.0; }
   double r0 = 1.0, r1 = 1.0;
@@ -169,7 +193,8 @@ __device__ inline double prune_likelihood(const ModelDev& m, const TreeView& T, 
 }
 
 // particleContainer.cpp:138-181,204-221: mean likelihood over the 2^k phasings of the unphased het pairs (code 2).
-__device__ inline double site_likelihood(const ModelDev& m, const TreeView& T, const signed char* data) {
+template <class TV>
+__device__ inline double site_likelihood(const ModelDev& m, const TV& T, const signed char* data) {
   signed char hap[32];
   const int n = m.n;
   int ncfg = 1;
@@ -194,7 +219,8 @@ __device__ inline double site_likelihood(const ModelDev& m, const TreeView& T, c
 // Local branch length inside each epoch = recombination opportunity per bp (record_recomb_extension,
 // particle.cpp:305-357: sum over time slices of #lineages * slice length).  Internal slots are sorted by height and all
 // leaves sit at height 0, so the slice between consecutive internal nodes carries n, n-1, ... lineages.
-__device__ inline void epoch_tree_length(const ModelDev& m, const TreeView& T) {
+template <class TV>
+__device__ inline void epoch_tree_length(const ModelDev& m, const TV& T) {
   const int n = m.n, E = m.E;
   for (int e = 0; e < E; e++) T.len(e) = 0.0;
   int e = 0;
@@ -219,7 +245,8 @@ __device__ inline int epoch_of(const ModelDev& m, double t) {
   return e;
 }
 
-__device__ inline void swap_slots(const ModelDev& m, const TreeView& T, int a, int b) {
+template <class TV>
+__device__ inline void swap_slots(const ModelDev& m, const TV& T, int a, int b) {
   double th = T.h(a); T.h(a) = T.h(b); T.h(b) = th;
   signed char tp = T.par(a); T.par(a) = T.par(b); T.par(b) = tp;
   for (int v = 0; v < m.nn; v++) {
@@ -241,8 +268,8 @@ struct NullSink {
 
 // One SMC' transition at position x (Forest::sampleNextGenealogy with exact window 0).  The test-side CPU restatement
 // consumes the same Philox draws in the same order, so the two can be compared draw for draw.
-template <class Sink>
-__device__ inline void smc_move(const ModelDev& m, const TreeView& T, Rng& r, double x, int max_rec_epoch, Sink& sink,
+template <class TV, class Sink>
+__device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x, int max_rec_epoch, Sink& sink,
                                 double& logw, double tl) {
   const int n = m.n, nn = m.nn;
   // 1. recombination point, uniform on the local tree (forest.cc:370-412); tl = tree_length of the current tree
@@ -270,6 +297,9 @@ __device__ inline void smc_move(const ModelDev& m, const TreeView& T, Rng& r, do
   double tt = hh, tc = 0.0;
   int k = 0;
   bool above_root = false;
+  // coalescence opportunity of consecutive intervals inside one epoch is summed in a register and recorded once
+  double opp = 0.0;
+  bool rec_on = (m.rec_mask[e] & 2) && e <= max_rec_epoch;
   for (;;) {
     double tnode = DBL_MAX;
     above_root = !(tt < hroot);
@@ -282,12 +312,18 @@ __device__ inline void smc_move(const ModelDev& m, const TreeView& T, Rng& r, do
     tc = tt + w;
     bool coal = tc < tend;
     double dt = (coal ? tc : tend) - tt;
-    if ((m.rec_mask[e] & 2) && e <= max_rec_epoch) sink.coal(e, x, coal ? 1 : 0, k * dt);
+    opp += k * dt;
     if (coal) break;
     tt = tend;
-    if (tend == tep) e++;
+    if (tend == tep) {
+      if (rec_on) sink.coal(e, x, 0, opp);
+      opp = 0.0;
+      e++;
+      rec_on = (m.rec_mask[e] & 2) && e <= max_rec_epoch;
+    }
     if (!above_root && tend == tnode) c++;
   }
+  if (rec_on) sink.coal(e, x, 1, opp);
   logw += m.vb_logfac[e];
   // 3. target among the k contemporaries (contemporaries_container.h:343-365) and 4. surgery; the unary node left at
   // the cut is pruned (forest.cc:1245-1257): the parent slot of the cut branch becomes the new coalescence node.
@@ -336,21 +372,26 @@ __device__ inline double draw_next_base(const ModelDev& m, double tree_len, Rng&
 
 // ForestState::extend_ARG for one row (x0, x1] with alleles data[n], followed by update_weight_at_site when is_site.
 // Returns the number of recombinations sampled.
-template <class Sink>
-__device__ inline int extend_row(const ModelDev& m, const TreeView& T, Rng& r, double x0, double x1,
+template <class TV, class Sink>
+__device__ inline int extend_row(const ModelDev& m, const TV& T, Rng& r, double x0, double x1,
                                  const signed char* data, int is_site, int max_rec_epoch, Sink& sink, double& logw,
                                  double& next_base) {
   const int n = m.n;
   int nmiss = 0;
   for (int i = 0; i < n; i++) nmiss += data[i] == -1;
   const int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);   // particleContainer.cpp:103-111
-  double tl = tree_length(m, T);
-  double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
-  epoch_tree_length(m, T);
+  double tl = 0.0, L_obs = 0.0;
   sink.row_begin(x1);
   double updated_to = x0;
   int nrec = 0;
+  bool moved = false;
   while (updated_to < x1) {
+    // (re)derive what depends on the tree: once at the row start and once after every move -- a single copy of this
+    // code keeps the kernel's instruction footprint down
+    tl = tree_length(m, T);
+    L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
+    epoch_tree_length(m, T);
+    if (moved) next_base = draw_next_base(m, tl, r, updated_to);
     double new_to = x1 < next_base ? x1 : next_base;
     logw += log(fastexp(-m.mu * L_obs * (new_to - updated_to)));     // particle.cpp:770
     for (int e = 0; e < m.E; e++) {
@@ -358,14 +399,12 @@ __device__ inline int extend_row(const ModelDev& m, const TreeView& T, Rng& r, d
       if (le > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, updated_to, new_to, le);
     }
     updated_to = new_to;
+    moved = false;
+    // a stretch without a move ends the row: the loop condition fails and nothing tree-dependent is recomputed
     if (updated_to < x1) {
       smc_move(m, T, r, updated_to, max_rec_epoch, sink, logw, tl);
       nrec++;
-      tl = tree_length(m, T);
-      if (leaf_status == 0) L_obs = branch_length_with_data(m, T, data);
-      if (leaf_status == 1) L_obs = tl;
-      epoch_tree_length(m, T);
-      next_base = draw_next_base(m, tl, r, updated_to);
+      moved = true;
     }
   }
   sink.row_end();
@@ -375,7 +414,8 @@ __device__ inline int extend_row(const ModelDev& m, const TreeView& T, Rng& r, d
 
 // Prior tree at the left end (forest.cc:299-347): Kingman coalescent under piecewise-constant epochs; mirrors
 // the test-side CPU restatement draw for draw.
-__device__ inline void init_tree(const ModelDev& m, const TreeView& T, Rng& r) {
+template <class TV>
+__device__ inline void init_tree(const ModelDev& m, const TV& T, Rng& r) {
   const int n = m.n, nn = m.nn;
   signed char active[32];
   for (int i = 0; i < n; i++) { active[i] = (signed char)i; T.h(i) = 0.0; }

@@ -19,6 +19,7 @@
 // all of it twice (ping-pong: resampling gathers from one copy into the other).
 #include <cuda_runtime.h>
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -36,6 +37,8 @@ int fail(int code, const std::string& msg) { g_err = msg; return code; }
 #define CUDA_TRY(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return fail(SMC_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(_e)); } while (0)
 
 constexpr int MAXSEG = 160;
+
+constexpr int AUX_BS = 64;   // block size of the one-off kernels (prior trees, stand-alone tree functions, calibration)
 
 struct USeg { long long j0; double u0; double step; };   // u_j = u0 + (j - j0) * step for j in [j0, next j0)
 
@@ -101,6 +104,7 @@ struct Params {
 // Tally sink writing into the particle's lag-bucket ring.  Recombination opportunity (the dense record: every epoch,
 // every stretch) is summed in shared memory over the row and written once per epoch at the row end, unless a bucket
 // bound of that epoch falls inside the row (then each stretch is split at the bound and written directly).
+template <int BS>
 struct RingSink {
   const Params* P;
   double* ring;    // destination copy
@@ -108,7 +112,7 @@ struct RingSink {
   const int* ks;   // bucket index of this row's left end [E]
   const int* ksl;  // the same modulo the ring depth [E]
   double* ACC;     // [E][BS] shared
-  int BS, t;
+  int t;
   unsigned long long split;   // bit e: a bound of epoch e lies inside this row
   __device__ __forceinline__ int bucket(int e, double x) const {
     int k = ks[e];
@@ -129,9 +133,20 @@ struct RingSink {
     }
   }
   __device__ void row_end() const {
-    for (int e = 0; e < P->m.E; e++) {
-      double a = ACC[e * BS + t];
-      if (a != 0.0) *cell(e, ks[e], 3) += a;
+    // four independent read-modify-writes in flight at a time (the cells of different epochs never alias)
+    const int E = P->m.E;
+    for (int e0 = 0; e0 < E; e0 += 4) {
+      double a[4], v[4];
+      double* cp[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        int e = e0 + j;
+        a[j] = e < E ? ACC[e * BS + t] : 0.0;
+        cp[j] = cell(e < E ? e : 0, ks[e < E ? e : 0], 3);
+        v[j] = a[j] != 0.0 ? *cp[j] : 0.0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) if (a[j] != 0.0) *cp[j] = v[j] + a[j];
     }
   }
   __device__ void coal(int e, double x, int cnt, double opp) const {
@@ -233,22 +248,15 @@ __device__ void build_u_chain(Ctrl* c, double U, long long N) {
 // the row kernel
 // ---------------------------------------------------------------------------------------------------------------
 // mode 0: one row; mode 1: materialise only (apply pending normalisation / resampling, no extension, no finalise)
-__global__ void __launch_bounds__(128)
+template <int BS>
+__global__ void __launch_bounds__(BS)
 smc_row_kernel(const __grid_constant__ Params P, int mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int BS = blockDim.x, t = threadIdx.x;
+  const int t = threadIdx.x;
   const ModelDev& m = P.m;
   const int n = m.n, nn = m.nn, E = m.E;
-  TreeView T;
-  T.BS = BS; T.t = t;
-  T.H = reinterpret_cast<double*>(smem_raw);
-  T.L0 = T.H + (size_t)nn * BS;
-  T.L1 = T.L0 + (size_t)nn * BS;
-  T.LEN = T.L1 + (size_t)nn * BS;
-  T.ACC = T.LEN + (size_t)E * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)E * BS);
+  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, n, nn, E, t);
   __shared__ double red[3][4];
-  __shared__ double tal[6][4];
   __shared__ bool is_last;
 
   Ctrl* c = P.ctrl;
@@ -263,26 +271,37 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   const bool live = i < P.N;
   const StateBuf& src = P.buf[cur];
   const StateBuf& dst = P.buf[resampled ? cur ^ 1 : cur];
-  const int warp = t >> 5, lane = t & 31, nwarp = BS >> 5;
+  constexpr int nwarp = BS >> 5;
+  const int warp = t >> 5, lane = t & 31;
 
   // ---- phase 0: tallies due after the previous row, weighted with the previous row's normalised weights ----------
   int c0 = 0, c1 = 0;
   if (row > 0 && c->cons_done != row) { c0 = P.cons_off[row - 1]; c1 = P.cons_off[row]; }
-  for (int q = c0; q < c1; q++) {
-    int2 ek = P.cons[q];
-    double v[6] = {0, 0, 0, 0, 0, 0};
-    if (live) {
-      double w = exp(src.logw[i] - lse);
-      const double* cell = src.ring + ((size_t)((ek.x * P.B + (ek.y % P.B)) * 4)) * P.N + i;
-      double cc = cell[0], co = cell[(size_t)P.N], rc = cell[(size_t)2 * P.N], ro = cell[(size_t)3 * P.N];
-      v[0] = w * cc; v[1] = w * co; v[2] = w * w * co; v[3] = w * rc; v[4] = w * ro; v[5] = w * w * ro;
+  if (c1 > c0) {
+    // at most one bucket per epoch falls due per row; the per-warp sums of all of them are staged in the (still
+    // unused) tree area and handed to the global tallies with one pass
+    double* scr = reinterpret_cast<double*>(smem_raw);           // [c1 - c0][6][nwarp]
+    const double w = live ? exp(src.logw[i] - lse) : 0.0;
+    const double w2 = w * w;
+    for (int q = c0; q < c1; q++) {
+      int2 ek = P.cons[q];
+      double v[6] = {0, 0, 0, 0, 0, 0};
+      if (live) {
+        const double* cell = src.ring + ((size_t)((ek.x * P.B + (ek.y % P.B)) * 4)) * P.N + i;
+        double cc = cell[0], co = cell[(size_t)P.N], rc = cell[(size_t)2 * P.N], ro = cell[(size_t)3 * P.N];
+        v[0] = w * cc; v[1] = w * co; v[2] = w2 * co; v[3] = w * rc; v[4] = w * ro; v[5] = w2 * ro;
+      }
+#pragma unroll
+      for (int a = 0; a < 6; a++) {
+        v[a] = warp_sum(v[a]);
+        if (lane == 0) scr[((q - c0) * 6 + a) * nwarp + warp] = v[a];
+      }
     }
-    for (int a = 0; a < 6; a++) { v[a] = warp_sum(v[a]); if (lane == 0) tal[a][warp] = v[a]; }
     __syncthreads();
-    if (t < 6) {
+    for (int idx = t; idx < (c1 - c0) * 6; idx += BS) {
       double s = 0;
-      for (int w = 0; w < nwarp; w++) s += tal[t][w];
-      if (s != 0.0) atomicAdd(P.tallies + t * E + ek.x, s);
+      for (int w_ = 0; w_ < nwarp; w_++) s += scr[idx * nwarp + w_];
+      if (s != 0.0) atomicAdd(P.tallies + (idx % 6) * E + P.cons[c0 + idx / 6].x, s);
     }
     __syncthreads();
   }
@@ -353,7 +372,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
-    RingSink sink{&P, dst.ring, (int)i, P.kstart + row * E, P.kslot + row * E, T.ACC, BS, t, 0ull};
+    RingSink<BS> sink{&P, dst.ring, (int)i, P.kstart + row * E, P.kslot + row * E, T.ACC, t, 0ull};
     nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
   }
 
@@ -533,14 +552,11 @@ __global__ void __launch_bounds__(128) smc_flush_kernel(const __grid_constant__ 
 // prior trees + first recombination position + weight 1/N (particleContainer.cpp:33-65)
 __global__ void __launch_bounds__(128) smc_init_kernel(const __grid_constant__ Params P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int BS = blockDim.x, t = threadIdx.x;
+  constexpr int BS = AUX_BS;
+  const int t = threadIdx.x;
   const ModelDev& m = P.m;
   const int n = m.n, nn = m.nn;
-  TreeView T;
-  T.BS = BS; T.t = t;
-  T.H = reinterpret_cast<double*>(smem_raw);
-  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS; T.ACC = T.LEN + (size_t)m.E * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)m.E * BS);
+  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= P.N) return;
   Rng r;
@@ -561,13 +577,10 @@ __global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long co
                                                         const double* height, const signed char* alleles, int what,
                                                         double* out0, double* out1) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int BS = blockDim.x, t = threadIdx.x;
+  constexpr int BS = AUX_BS;
+  const int t = threadIdx.x;
   const int n = m.n, nn = m.nn;
-  TreeView T;
-  T.BS = BS; T.t = t;
-  T.H = reinterpret_cast<double*>(smem_raw);
-  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS; T.ACC = T.LEN + (size_t)m.E * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)m.E * BS);
+  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= count) return;
   for (int v = 0; v < nn; v++) { T.h(v) = height[i * nn + v]; T.par(v) = (signed char)parent[i * nn + v]; }
@@ -587,13 +600,10 @@ __global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long co
 // survived to 0.6 * seqlen).  The host takes per-epoch medians.
 __global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, uint64_t seed, double* dist, int* epoch) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int BS = blockDim.x, t = threadIdx.x;
+  constexpr int BS = AUX_BS;
+  const int t = threadIdx.x;
   const int n = m.n, nn = m.nn;
-  TreeView T;
-  T.BS = BS; T.t = t;
-  T.H = reinterpret_cast<double*>(smem_raw);
-  T.L0 = T.H + (size_t)nn * BS; T.L1 = T.L0 + (size_t)nn * BS; T.LEN = T.L1 + (size_t)nn * BS; T.ACC = T.LEN + (size_t)m.E * BS;
-  T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)m.E * BS);
+  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= count) return;
   Rng r;
@@ -603,7 +613,7 @@ __global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, u
   int alive = n - 1;
   for (int j = 0; j < n - 1; j++) {
     double h = T.h(n + j);
-    T.l0(j) = h; T.l1(j) = 1.0;
+    T.l0(n + j) = h; T.l1(n + j) = 1.0;
     dist[i * (n - 1) + j] = -1.0;
     epoch[i * (n - 1) + j] = epoch_of(m, h);
   }
@@ -619,11 +629,11 @@ __global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, u
     next = draw_next_base(m, tl, r, pos);
     // the reference records at most one vanished height per move (the loop breaks after the first, smcsmc.cpp:218-234)
     for (int j = 0; j < n - 1; j++) {
-      if (T.l1(j) == 0.0) continue;
-      double h = T.l0(j);
+      if (T.l1(n + j) == 0.0) continue;
+      double h = T.l0(n + j);
       bool present = false;
       for (int v = n; v < nn; v++) present |= (T.h(v) == h);
-      if (!present) { dist[i * (n - 1) + j] = pos; T.l1(j) = 0.0; alive--; break; }
+      if (!present) { dist[i * (n - 1) + j] = pos; T.l1(n + j) = 0.0; alive--; break; }
     }
   }
 }
@@ -761,7 +771,7 @@ int use_device(int device) {
   return 0;
 }
 
-size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * ((size_t)nn * 25 + (size_t)E * 16) + 16; }
+size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * smc::tree_bytes_per_thread(nn, E) + 16; }
 
 int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, int aa, const double* t_start,
                const double* inv2N, const double* vb, const uint8_t* mask) {
@@ -783,7 +793,11 @@ int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, 
 
 int launch_row(smc_engine* e, int mode) {
   int nb = e->P.nblocks;
-  smc_row_kernel<<<nb, e->BS, e->smem, e->stream>>>(e->P, mode);
+  switch (e->BS) {
+    case 32: smc_row_kernel<32><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
+    case 64: smc_row_kernel<64><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+    default: smc_row_kernel<128><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+  }
   e->launches++;
   return 0;
 }
@@ -822,14 +836,18 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   P.slot_offset = cfg->slot_offset; P.ess_fraction = cfg->ess_fraction; P.start_pos = cfg->start_pos;
   // block size: keep every SM busy when there are few particles
   e->BS = (cfg->N <= 148 * 64 * 2) ? 64 : 128;
+  if (const char* s = getenv("SMC_BLOCK")) { int b = atoi(s); if (b == 32 || b == 64 || b == 128) e->BS = b; }   // tuning knob
   P.nblocks = (cfg->N + e->BS - 1) / e->BS;
   e->smem = tree_smem(P.m.nn, P.m.E, e->BS);
+  if (const char* s = getenv("SMC_EXTRA_SMEM")) e->smem += (size_t)atoi(s);                                       // occupancy experiments
   cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
   if (ce != cudaSuccess) { delete e; return fail(SMC_ERR_CUDA, cudaGetErrorString(ce)); }
   cudaEventCreate(&e->ev0); cudaEventCreate(&e->ev1);
   // opt in to the full 227 KB once (the attribute is per function, not per engine)
   if (e->smem > 230400) { smc_destroy(e); return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has"); }
-  ce = cudaFuncSetAttribute(smc_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  ce = cudaFuncSetAttribute(smc_row_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
   const size_t N = cfg->N;
@@ -983,7 +1001,7 @@ int smc_init_particles(smc_engine* e) {
   if (!e) return fail(SMC_ERR_ARG, "null engine");
   if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows before initialising particles");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
-  smc_init_kernel<<<e->P.nblocks, e->BS, e->smem, e->stream>>>(e->P);
+  smc_init_kernel<<<(unsigned)((e->cfg.N + AUX_BS - 1) / AUX_BS), AUX_BS, tree_smem(e->P.m.nn, e->P.m.E, AUX_BS), e->stream>>>(e->P);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   e->inited = true;
@@ -1028,6 +1046,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
     if (engines[k]->cfg.device == engines[0]->cfg.device) cudaStreamWaitEvent(engines[k]->stream, engines[0]->ev0, 0);
   }
   bool more = true;
+  const auto host_t0 = std::chrono::steady_clock::now();
   while (more) {
     more = false;
     for (int k = 0; k < count; k++) {
@@ -1041,6 +1060,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
     }
   }
   double span = 0.0;
+  const double host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
   for (int k = 0; k < count; k++) {
     smc_engine* e = engines[k];
     CUDA_TRY(cudaSetDevice(e->cfg.device));
@@ -1057,6 +1077,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
     }
   }
   engines[0]->kernel_ms += span;     // device span of the whole group, booked on the first engine
+  if (getenv("SMC_DEBUG_TIMING")) fprintf(stderr, "[smc] sweep_many: %d engines, host launch loop %.1f ms, device span %.1f ms\n", count, host_ms, span);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
