@@ -221,6 +221,11 @@ def run_ours(a):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = abytes / avg_launch_s / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/r1_row_kernel_ncu_full.csv (n = 8, E = 11,
+    # N = 10 000, ring depth 14): 52.5 MB on a row that pulls after a resampling, 2.2 MB otherwise
+    traffic = None
+    if (NSAM, E, N) == (8, 11, 10000):
+        traffic = rs_frac * 52.5e6 + (1.0 - rs_frac) * 2.2e6
     line = {
         "metric": "particle*sites/sec (s per EM iteration in ms_per_step)", "value": units / wall,
         "unit": "particle*sites/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -234,7 +239,7 @@ def run_ours(a):
                 "d2h_bytes_per_step": C * (6 * E * 8 + 8), "ms_per_step": wall_e2e / a.steps * 1e3},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "smc_row_kernel", "avg_launch_us": avg_launch_s * 1e6,
+                     "traffic": traffic, "kernel": "smc_row_kernel", "avg_launch_us": avg_launch_s * 1e6,
                      "algorithmic_bytes_per_launch": abytes, "peak_source": "measured" if peaks else "fallback",
                      "note": "one launch per .seg row and chunk (%d rows/step), %d chunks concurrent; avg_launch_us = "
                              "device time / launches" % (R, C)},
@@ -307,10 +312,15 @@ def cpu_reference_sample(a):
     cores = _host_cores()
     particles, chunk_mb = a.cpu_particles, a.cpu_chunk_mb
     v, wall = reference_sample(particles, chunk_mb, cores)
+    # the reference's fixed per-process lag calibration (smcsmc.cpp:287-288), timed with a single particle, so that the
+    # sweep alone can be read off as well (SURVEY.md 8d reports it separately)
+    _, cal = reference_sample(1, chunk_mb, cores, seed=7)
+    sweep = max(wall - cal, 1e-9)
     return {"value": v, "unit": "particle*sites/s", "cores": cores, "kind": "reference",
+            "calibration_s": cal, "value_excluding_calibration": cores * particles * chunk_mb * 1e6 / sweep,
             "sample": "%d chunk processes x %g Mb of the same .seg x %d particles, same 11-epoch model, -EM 0, wall of the "
-                      "slowest (%.1f s, includes the reference's ~3 s per-process lag calibration)"
-                      % (cores, chunk_mb, particles, wall)}
+                      "slowest (%.1f s, of which %.1f s is the reference's per-process lag calibration)"
+                      % (cores, chunk_mb, particles, wall, cal)}
 
 
 def run_reference(a):
@@ -352,8 +362,8 @@ def main():
     ap.add_argument("--chunks", type=int, default=16, help="independent chunks swept concurrently (smc2 -chunks)")
     ap.add_argument("--rows-per-turn", type=int, default=4)
     ap.add_argument("--ess", type=float, default=0.5, help="-ESS resampling threshold fraction (reference default 0.5)")
-    ap.add_argument("--cpu-particles", type=int, default=300)
-    ap.add_argument("--cpu-chunk-mb", type=float, default=1.0)
+    ap.add_argument("--cpu-particles", type=int, default=1000)
+    ap.add_argument("--cpu-chunk-mb", type=float, default=2.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
     if a.impl == "reference":
