@@ -90,6 +90,19 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end);
  * device time of the whole group is booked on engines[0] (smc_get_timing). */
 int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn);
 
+/* Particle sharding over GPUs (no counterpart in the reference, whose only parallelism is chunks): the
+ * population of world * N particles is split evenly, one engine (one process, one GPU) per rank, each created with its
+ * local N.  Rank 0 obtains an id, every rank attaches with it after smc_create and before smc_upload_rows (all ranks
+ * upload the same rows).  From then on smc_upload_rows, smc_init_particles, smc_sweep, smc_finish, smc_get_particles and
+ * smc_reset are collective: every rank calls them with the same arguments.  Per row the ranks exchange four doubles
+ * (NCCL all-gather); offspring whose parent lives on another rank read its state straight from that GPU's memory
+ * (CUDA IPC mappings over NVLink).  Philox streams are keyed by the global particle slot, so the result does not
+ * depend on the number of ranks beyond the order of floating-point sums in the normaliser.  After smc_finish every
+ * rank holds the global tallies, ln normaliser, resampling log and counters; smc_get_particles returns the local slice,
+ * smc_get_last_ancestry global parent indices.  Needs libnccl.so.2 at run time (bound with dlopen). */
+int smc_shard_unique_id(uint8_t id[128]);
+int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t id[128]);
+
 /* Start another EM iteration on the same rows (the reference re-enters pfARG_core, smcsmc.cpp:83): clears particles,
  * tallies, ln normaliser and counters; optionally replaces the rates the M-step changed (CountModel::reset_Ne /
  * reset_recomb_rate, count.cpp:267-325).  inv2N / vb_logfac may be NULL (unchanged); rho <= 0 means unchanged.

@@ -5,7 +5,7 @@ The product is `lib/libsmcgpu.so` (hand-written sm_100a CUDA, include/smcsmc_b20
 compute and has NO fallback: loading fails loudly when the CUDA library has not been built.
 """
 from ._abi import lib, lib_path, SmcError, SmcConfig  # noqa: F401
-from .engine import (ParticleFilter, sweep_many, site_likelihood, branch_lengths, systematic_offspring, resample_counts,  # noqa: F401
+from .engine import (ParticleFilter, shard_unique_id, sweep_many, site_likelihood, branch_lengths, systematic_offspring, resample_counts,  # noqa: F401
                      normalize_log, fastexp, calibrate_survival)
 from .segdata import read_seg, SegRows  # noqa: F401
 

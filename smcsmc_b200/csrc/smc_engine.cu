@@ -18,12 +18,15 @@
 //   ring    [E][B][4][N] f64   lag buckets of pending tallies: coal count, coal opp, recomb count, recomb opp
 // all of it twice (ping-pong: resampling gathers from one copy into the other).
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>   // types only: the library is bound with dlopen when an engine is sharded
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 #include "../../include/smcsmc_b200.h"
 #include "smc_device.cuh"
@@ -38,6 +41,7 @@ int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
 constexpr int MAXSEG = 160;
 
+constexpr int SMC_MAX_RANKS = 8;
 constexpr int AUX_BS = 64;   // block size of the one-off kernels (prior trees, stand-alone tree functions, calibration)
 
 struct USeg { long long j0; double u0; double step; };   // u_j = u0 + (j - j0) * step for j in [j0, next j0)
@@ -97,9 +101,25 @@ struct Params {
   double* bscale[2];
   double* psum;            // [N+1] parity-mode sequential partial sums
   double* tallies;         // [6][E]
-  int* anc;                // [N] ancestry of the last resampling
+  int* anc;                // [N] ancestry of the last resampling (global particle index when sharded)
   double* rs_pos; double* rs_ess; long long rs_cap;
+  // particle sharding over ranks: this engine owns particles [base, base + N) of Ntot.  What a
+  // pulling offspring reads of its parent -- tree, next_base, ring, and the weight partials -- lives in two slabs
+  // whose peer mappings differ from the local addresses by a constant byte offset per rank.
+  int rank, world;
+  long long Ntot, base;
+  long long peer_state[SMC_MAX_RANKS];   // byte offset: peer r's state slab - mine
+  long long peer_ring[SMC_MAX_RANKS];    // byte offset: peer r's ring slab - mine
+  double* summ;             // [3] this rank's (max, sum, sum of squares) after a row
+  double* allsumm;          // [world][3] gathered
+  double* rank_off[2];      // [world+1] normalised exclusive prefix of the rank totals, by row parity
+  double* rank_fac[2];      // [world] exp(rank max - ln normaliser), by row parity
 };
+
+template <class Tp>
+__device__ __forceinline__ Tp* at_peer(Tp* p, long long delta) {
+  return reinterpret_cast<Tp*>(reinterpret_cast<char*>(const_cast<typename std::remove_const<Tp>::type*>(p)) + delta);
+}
 
 // Tally sink writing into the particle's lag-bucket ring.  Recombination opportunity (the dense record: every epoch,
 // every stretch) is summed in shared memory over the row and written once per epoch at the row end, unless a bucket
@@ -189,6 +209,38 @@ __device__ __forceinline__ double cum_at(const Params& P, int p, long long i, in
   return v < cap ? v : cap;
 }
 
+// the same for global particle g when the population is sharded: the owner's arrays hold partials relative to the
+// owner's own maximum (all written before the per-row exchange), rank_fac rescales them and rank_off places them; the
+// last particle of a rank sits exactly on the rank's upper bound, so the owner of a parent follows from rank_off alone
+__device__ __forceinline__ double cum_at_sharded(const Params& P, int p, int r, long long l, int bs) {
+  const long long d = P.peer_state[r];
+  const double hi = P.rank_off[p][r + 1];
+  if (l == P.N - 1) return hi;
+  int b = (int)(l / bs);
+  const double* boff = at_peer(P.boff[p], d);
+  double v = boff[b] + __ldcg(at_peer(P.local_cum[p], d) + l) * at_peer(P.bscale[p], d)[b];
+  double cap = boff[b + 1];
+  v = v < cap ? v : cap;
+  v = P.rank_off[p][r] + v * P.rank_fac[p][r];
+  return v < hi ? v : hi;
+}
+
+// global index of the parent of offspring with threshold uj (sharded population)
+__device__ __forceinline__ long long parent_of_sharded(const Params& P, int p, double uj, double norm, int bs) {
+  int r = 0;
+  while (r + 1 < P.world && !(P.rank_off[p][r + 1] / norm > uj)) r++;
+  long long lo = 0, hi = P.N;
+  while (lo < hi) {
+    long long mid = (lo + hi) >> 1;
+    if (cum_at_sharded(P, p, r, mid, bs) / norm > uj) hi = mid; else lo = mid + 1;
+  }
+  if (lo >= P.N) lo = P.N - 1;
+  return (long long)r * P.N + lo;
+}
+__device__ __forceinline__ double cum_at_global(const Params& P, int p, long long g, int bs) {
+  return cum_at_sharded(P, p, (int)(g / P.N), g % P.N, bs);
+}
+
 __device__ __forceinline__ double u_at(const Ctrl* c, long long j) {
   int lo = 0, hi = c->nseg - 1;
   while (lo < hi) {
@@ -242,6 +294,32 @@ __device__ void build_u_chain(Ctrl* c, double U, long long N) {
   }
   // (cannot happen for N < 2^52) fall back to explicit steps being cut short: extend the last piece
   c->nseg = ns;
+}
+
+// End of a row (one thread): book the ln normaliser, decide on resampling (particleContainer.cpp:281) and, if so,
+// draw the systematic-resampling uniform and build the u-chain over all Ntot particles.
+__device__ void commit_row(const Params& P, Ctrl* c, long long row, double new_lse, double ess, bool ok, double norm,
+                           long long Ntot) {
+  if (!ok || !isfinite(new_lse)) c->err = 1;
+  c->lnZ += new_lse;
+  c->lse = new_lse;
+  const bool rs = ess < (double)Ntot * P.ess_fraction - 1e-6;
+  if (c->resampled) c->cur ^= 1;
+  c->resampled = rs ? 1 : 0;
+  if (rs) {
+    Rng rr;
+    rng_init(rr, P.seed, 0, (uint32_t)row, P.chunk, RNG_RESAMPLE);
+    double U = rng_uniform(rr);
+    build_u_chain(c, U, Ntot);
+    c->norm = norm;
+    c->child_logw = log(norm / (double)Ntot);
+    c->resample_pos = P.x_end[row];
+    c->resample_row = row;
+    if (c->n_resample < P.rs_cap) { P.rs_pos[c->n_resample] = P.x_end[row]; P.rs_ess[c->n_resample] = ess; }
+    c->n_resample++;
+  }
+  c->ticket = 0;
+  c->row = row + 1;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -309,36 +387,60 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   // ---- phase 1: load own state, or pull the parent's after a resampling ---------------------------------------
   double logw = 0.0, next_base = 0.0;
   long long a = i;
+  long long dS = 0, dR = 0;      // byte offsets to the parent's owner (0: this rank)
   bool redraw = false;
   if (live) {
     if (resampled) {
       const double norm = c->norm;
-      double uj = u_at(c, i);
-      a = parent_of(P, pprev, uj, norm, BS);
       // did the parent get more than one offspring?  (then every copy re-draws its next recombination position,
       // particleContainer.cpp:357-367 / forest.h:140-151)
-      if (i > 0) {
-        double up = u_at(c, i - 1);
-        if (a == 0 || !(cum_at(P, pprev, a - 1, BS) / norm > up)) redraw = true;
+      if (P.world == 1) {
+        double uj = u_at(c, i);
+        a = parent_of(P, pprev, uj, norm, BS);
+        if (i > 0) {
+          double up = u_at(c, i - 1);
+          if (a == 0 || !(cum_at(P, pprev, a - 1, BS) / norm > up)) redraw = true;
+        }
+        if (!redraw && i + 1 < P.N) {
+          double un = u_at(c, i + 1);
+          if (a == P.N - 1 || cum_at(P, pprev, a, BS) / norm > un) redraw = true;
+        }
+        P.anc[i] = (int)a;
+      } else {
+        const long long gi = P.base + i;
+        double uj = u_at(c, gi);
+        const long long ga = parent_of_sharded(P, pprev, uj, norm, BS);
+        if (gi > 0) {
+          double up = u_at(c, gi - 1);
+          if (ga == 0 || !(cum_at_global(P, pprev, ga - 1, BS) / norm > up)) redraw = true;
+        }
+        if (!redraw && gi + 1 < P.Ntot) {
+          double un = u_at(c, gi + 1);
+          if (ga == P.Ntot - 1 || cum_at_global(P, pprev, ga, BS) / norm > un) redraw = true;
+        }
+        P.anc[i] = (int)ga;
+        const int ra = (int)(ga / P.N);
+        a = ga % P.N;
+        dS = P.peer_state[ra];
+        dR = P.peer_ring[ra];
       }
-      if (!redraw && i + 1 < P.N) {
-        double un = u_at(c, i + 1);
-        if (a == P.N - 1 || cum_at(P, pprev, a, BS) / norm > un) redraw = true;
-      }
-      P.anc[i] = (int)a;
       logw = c->child_logw;
     } else {
       logw = src.logw[i] - lse;
     }
-    next_base = src.next_base[a];
-    for (int v = 0; v < n; v++) T.h(v) = 0.0;
-    for (int v = n; v < nn; v++) T.h(v) = src.height[(size_t)(v - n) * P.N + a];
-    for (int v = 0; v < nn; v++) T.par(v) = src.parent[(size_t)v * P.N + a];
+    next_base = at_peer(src.next_base, dS)[a];
+    {
+      const double* __restrict__ sh_ = at_peer(src.height, dS);
+      const signed char* __restrict__ sp_ = at_peer(src.parent, dS);
+      for (int v = 0; v < n; v++) T.h(v) = 0.0;
+      for (int v = n; v < nn; v++) T.h(v) = sh_[(size_t)(v - n) * P.N + a];
+      for (int v = 0; v < nn; v++) T.par(v) = sp_[(size_t)v * P.N + a];
+    }
     // ring: gather everything on a pull; consumed buckets are cleared either way
     if (resampled) {
       // 8 independent loads in flight per thread before the stores (the two copies never alias)
       const int cells = E * P.B * 4;
-      const double* __restrict__ sp = src.ring + a;
+      const double* __restrict__ sp = at_peer(src.ring, dR) + a;
       double* __restrict__ dp = dst.ring + i;
       const size_t NN = (size_t)P.N;
       int q = 0;
@@ -450,14 +552,17 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   __syncthreads();
   S = 0.0; Q = 0.0;
   for (int w = 0; w < nwarp; w++) { S += red[1][w]; Q += red[2][w]; }
+  const bool sharded = P.world > 1;
   const double new_lse = gm + log(S);
   const double ess = S * S / Q;
+  // a sharded rank scales its partials by its own maximum only: peers read them before the global normaliser is known
+  const double ref = sharded ? gm : new_lse;
   // exclusive prefix over blocks of the normalised block totals: each thread owns a contiguous run of blocks
   const int per = (nb + BS - 1) / BS;
   const int b0 = t * per, b1 = min(nb, b0 + per);
   double run = 0.0;
   for (int b = b0; b < b1; b++) {
-    double sc = exp(__ldcg(P.bmax[pnow] + b) - new_lse);
+    double sc = exp(__ldcg(P.bmax[pnow] + b) - ref);
     P.bscale[pnow][b] = sc;
     run += __ldcg(P.bsum[pnow] + b) * sc;
   }
@@ -476,37 +581,51 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   }
   if (t == 0) P.boff[pnow][nb] = sh[BS];
   __syncthreads();
-  if (t == 0) {
-    double norm = sh[BS];
-    const StateBuf& now = dst;
-    if (P.parity_scan) {
-      // order-faithful partial sums (particleContainer.cpp:256-262): left to right, one thread
-      double acc = 0.0;
-      for (long long k = 0; k < P.N; k++) { P.psum[k] = acc; acc += exp(__ldcg(now.logw + k) - new_lse); }
-      P.psum[P.N] = acc;
-      norm = acc;
-    }
-    if (!(S > 0.0) || !isfinite(new_lse)) c->err = 1;
-    c->lnZ += new_lse;
-    c->lse = new_lse;
-    const bool rs = ess < (double)P.N * P.ess_fraction - 1e-6;    // particleContainer.cpp:281
-    if (resampled) c->cur = cur ^ 1;
-    c->resampled = rs ? 1 : 0;
-    if (rs) {
-      Rng rr;
-      rng_init(rr, P.seed, 0, (uint32_t)row, P.chunk, RNG_RESAMPLE);
-      double U = rng_uniform(rr);
-      build_u_chain(c, U, P.N);
-      c->norm = norm;
-      c->child_logw = log(norm / (double)P.N);
-      c->resample_pos = P.x_end[row];
-      c->resample_row = row;
-      if (c->n_resample < P.rs_cap) { P.rs_pos[c->n_resample] = P.x_end[row]; P.rs_ess[c->n_resample] = ess; }
-      c->n_resample++;
-    }
+  if (t != 0) return;
+  if (sharded) {
+    // hand (max, sum, sum of squares, prefix total) to the exchange; smc_shard_commit_kernel finishes the row
+    P.summ[0] = gm; P.summ[1] = S; P.summ[2] = Q; P.summ[3] = sh[BS];
     c->ticket = 0;
-    c->row = row + 1;
+    return;
   }
+  double norm = sh[BS];
+  if (P.parity_scan) {
+    // order-faithful partial sums (particleContainer.cpp:256-262): left to right, one thread
+    double acc = 0.0;
+    for (long long k = 0; k < P.N; k++) { P.psum[k] = acc; acc += exp(__ldcg(dst.logw + k) - new_lse); }
+    P.psum[P.N] = acc;
+    norm = acc;
+  }
+  commit_row(P, c, row, new_lse, ess, S > 0.0, norm, (long long)P.N);
+}
+
+// second half of a sharded row, after the ranks' summaries were gathered: every rank derives the same ln normaliser,
+// ESS, rank offsets and resampling decision from the same numbers in the same order
+__global__ void smc_shard_commit_kernel(const __grid_constant__ Params P) {
+  Ctrl* c = P.ctrl;
+  const long long row = c->row;
+  if (row >= P.R) return;
+  const int pnow = (int)(row & 1), G = P.world;
+  const double* all = P.allsumm;
+  double gm = -DBL_MAX;
+  for (int r = 0; r < G; r++) gm = fmax(gm, all[r * 4]);
+  double S = 0.0, Q = 0.0;
+  for (int r = 0; r < G; r++) {
+    double f = exp(all[r * 4] - gm);
+    S += all[r * 4 + 1] * f;
+    Q += all[r * 4 + 2] * f * f;
+  }
+  const double new_lse = gm + log(S);
+  const double ess = S * S / Q;
+  double acc = 0.0;
+  for (int r = 0; r < G; r++) {
+    double fac = exp(all[r * 4] - new_lse);
+    P.rank_fac[pnow][r] = fac;
+    P.rank_off[pnow][r] = acc;
+    acc += all[r * 4 + 3] * fac;
+  }
+  P.rank_off[pnow][G] = acc;
+  commit_row(P, c, row, new_lse, ess, S > 0.0, acc, P.Ntot);
 }
 
 // commit of a materialise-only pass
@@ -566,7 +685,7 @@ __global__ void __launch_bounds__(128) smc_init_kernel(const __grid_constant__ P
   const StateBuf& d = P.buf[0];
   for (int v = n; v < nn; v++) d.height[(size_t)(v - n) * P.N + i] = T.h(v);
   for (int v = 0; v < nn; v++) d.parent[(size_t)v * P.N + i] = T.par(v);
-  d.logw[i] = -log((double)P.N);
+  d.logw[i] = -log((double)P.Ntot);
   d.next_base[i] = nb;
 }
 
@@ -745,7 +864,46 @@ struct smc_engine {
   long long swept = 0;
   std::vector<int> first_pending_h;     // per epoch: number of buckets the regular schedule consumes
   int* first_pending_d = nullptr;
+  // particle sharding
+  void* state_slab = nullptr;
+  void* ring_slab = nullptr;
+  ncclComm_t comm = nullptr;
+  std::vector<void*> peer_maps;         // cudaIpcOpenMemHandle results, closed in smc_destroy
 };
+
+namespace {
+
+// NCCL, bound at run time (torch's bundled libnccl.so.2 is already in the process when the caller is Python)
+struct NcclApi {
+  void* h = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+
+int nccl_load() {
+  if (g_nccl.h) return 0;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return fail(SMC_ERR_CUDA, std::string("cannot load libnccl.so.2: ") + dlerror());
+  g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
+  g_nccl.AllGather = (decltype(g_nccl.AllGather))dlsym(h, "ncclAllGather");
+  g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(h, "ncclAllReduce");
+  g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
+  g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.AllReduce || !g_nccl.CommDestroy ||
+      !g_nccl.GetErrorString)
+    return fail(SMC_ERR_CUDA, "libnccl.so.2 lacks a required symbol");
+  g_nccl.h = h;
+  return 0;
+}
+#define NCCL_TRY(call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) return fail(SMC_ERR_CUDA, std::string("NCCL: ") + g_nccl.GetErrorString(r_)); } while (0)
+
+}  // namespace
 
 namespace {
 
@@ -788,6 +946,30 @@ int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, 
     if (!(m.inv2N[e] > 0)) return fail(SMC_ERR_ARG, "inv2N must be positive");
   }
   if (m.t_start[0] != 0.0) return fail(SMC_ERR_ARG, "t_start[0] must be 0");
+  return 0;
+}
+
+// All ranks publish the IPC handle of one slab and map everybody else's; delta[r] = peer r's address - mine.
+int exchange_slab(smc_engine* e, void* slab, long long* delta) {
+  const int G = e->P.world, me = e->P.rank;
+  cudaIpcMemHandle_t mine;
+  CUDA_TRY(cudaIpcGetMemHandle(&mine, slab));
+  char* d_in = nullptr; char* d_out = nullptr;
+  int rc;
+  if ((rc = dev_alloc(e, &d_in, sizeof(mine), false)) || (rc = dev_alloc(e, &d_out, sizeof(mine) * (size_t)G, false))) return rc;
+  CUDA_TRY(cudaMemcpyAsync(d_in, &mine, sizeof(mine), cudaMemcpyHostToDevice, e->stream));
+  NCCL_TRY(g_nccl.AllGather(d_in, d_out, sizeof(mine), ncclChar, e->comm, e->stream));
+  std::vector<cudaIpcMemHandle_t> all(G);
+  CUDA_TRY(cudaMemcpyAsync(all.data(), d_out, sizeof(mine) * (size_t)G, cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  for (int r = 0; r < G; r++) {
+    delta[r] = 0;
+    if (r == me) continue;
+    void* ptr = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, all[r], cudaIpcMemLazyEnablePeerAccess));
+    e->peer_maps.push_back(ptr);
+    delta[r] = (long long)((char*)ptr - (char*)slab);
+  }
   return 0;
 }
 
@@ -852,18 +1034,35 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
   const size_t N = cfg->N;
   const int n = cfg->n, nn = 2 * n - 1;
+  // everything a pulling offspring may read of a parent on another rank sits in one slab (one IPC handle per rank)
+  {
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t s_h = up((size_t)(n - 1) * N * 8), s_p = up((size_t)nn * N), s_d = up(N * 8),
+                 s_b1 = up(((size_t)P.nblocks + 1) * 8), s_b = up((size_t)P.nblocks * 8);
+    const size_t per = s_h + s_p + s_d + s_d + s_b1 + s_b;
+    void* slab = nullptr;
+    ce = cudaMalloc(&slab, 2 * per);
+    if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "state slab: " + msg); }
+    cudaMemsetAsync(slab, 0, 2 * per, e->stream);
+    e->allocs.push_back(slab);
+    e->state_slab = slab;
+    char* q = (char*)slab;
+    for (int b = 0; b < 2; b++) {
+      P.buf[b].height = (double*)q; q += s_h;
+      P.buf[b].parent = (signed char*)q; q += s_p;
+      P.buf[b].next_base = (double*)q; q += s_d;
+      P.local_cum[b] = (double*)q; q += s_d;
+      P.boff[b] = (double*)q; q += s_b1;
+      P.bscale[b] = (double*)q; q += s_b;
+    }
+  }
   for (int b = 0; b < 2; b++) {
-    if ((rc = dev_alloc(e, &P.buf[b].height, (size_t)(n - 1) * N))) { smc_destroy(e); return rc; }
-    if ((rc = dev_alloc(e, &P.buf[b].parent, (size_t)nn * N))) { smc_destroy(e); return rc; }
     if ((rc = dev_alloc(e, &P.buf[b].logw, N))) { smc_destroy(e); return rc; }
-    if ((rc = dev_alloc(e, &P.buf[b].next_base, N))) { smc_destroy(e); return rc; }
-    if ((rc = dev_alloc(e, &P.local_cum[b], N))) { smc_destroy(e); return rc; }
     if ((rc = dev_alloc(e, &P.bmax[b], P.nblocks))) { smc_destroy(e); return rc; }
     if ((rc = dev_alloc(e, &P.bsum[b], P.nblocks))) { smc_destroy(e); return rc; }
     if ((rc = dev_alloc(e, &P.bsq[b], P.nblocks))) { smc_destroy(e); return rc; }
-    if ((rc = dev_alloc(e, &P.boff[b], P.nblocks + 1))) { smc_destroy(e); return rc; }
-    if ((rc = dev_alloc(e, &P.bscale[b], P.nblocks))) { smc_destroy(e); return rc; }
   }
+  P.rank = 0; P.world = 1; P.Ntot = (long long)N; P.base = 0;
   if ((rc = dev_alloc(e, &P.psum, cfg->parity_scan ? N + 1 : 1))) { smc_destroy(e); return rc; }
   if ((rc = dev_alloc(e, &P.tallies, 6 * (size_t)cfg->E))) { smc_destroy(e); return rc; }
   if ((rc = dev_alloc(e, &P.anc, N))) { smc_destroy(e); return rc; }
@@ -885,11 +1084,48 @@ void smc_destroy(smc_engine* e) {
   if (!e) return;
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  for (void* p : e->peer_maps) cudaIpcCloseMemHandle(p);
+  if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
   for (void* p : e->allocs) cudaFree(p);
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
+}
+
+int smc_shard_unique_id(uint8_t id[128]) {
+  if (!id) return fail(SMC_ERR_ARG, "null argument");
+  int rc = nccl_load();
+  if (rc) return rc;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId u;
+  NCCL_TRY(g_nccl.GetUniqueId(&u));
+  memcpy(id, &u, 128);
+  return 0;
+}
+
+int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t id[128]) {
+  if (!e || !id) return fail(SMC_ERR_ARG, "null argument");
+  if (world < 2 || world > SMC_MAX_RANKS || rank < 0 || rank >= world) return fail(SMC_ERR_ARG, "rank/world out of range (2..8 ranks)");
+  if (e->rows_ready || e->inited) return fail(SMC_ERR_STATE, "attach the shard before uploading rows");
+  if (e->P.world > 1) return fail(SMC_ERR_STATE, "engine is already sharded");
+  if (e->cfg.parity_scan) return fail(SMC_ERR_ARG, "parity_scan is a single-rank mode");
+  if ((long long)e->cfg.N * world > 0x7fffffffLL) return fail(SMC_ERR_ARG, "more than 2^31 particles in total");
+  int rc = nccl_load();
+  if (rc) return rc;
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  ncclUniqueId u;
+  memcpy(&u, id, 128);
+  NCCL_TRY(g_nccl.CommInitRank(&e->comm, world, u, rank));
+  Params& P = e->P;
+  P.rank = rank; P.world = world;
+  P.Ntot = (long long)e->cfg.N * world;
+  P.base = (long long)e->cfg.N * rank;
+  P.slot_offset = e->cfg.slot_offset + (uint32_t)P.base;      // Philox streams are keyed by the global particle slot
+  if ((rc = dev_alloc(e, &P.summ, 4)) || (rc = dev_alloc(e, &P.allsumm, 4 * (size_t)world))) return rc;
+  for (int b = 0; b < 2; b++)
+    if ((rc = dev_alloc(e, &P.rank_off[b], world + 1)) || (rc = dev_alloc(e, &P.rank_fac[b], world))) return rc;
+  return exchange_slab(e, e->state_slab, P.peer_state);
 }
 
 int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, const uint8_t* is_site,
@@ -988,8 +1224,14 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
   P.cons_off = d_co; P.cons = d_cons;
   // the ring and the resampling log need R / B
   const size_t cells = (size_t)E * B * 4;
-  for (int b = 0; b < 2; b++)
-    if ((rc = dev_alloc(e, &P.buf[b].ring, cells * (size_t)e->cfg.N))) return rc;
+  {
+    double* ring = nullptr;
+    if ((rc = dev_alloc(e, &ring, 2 * cells * (size_t)e->cfg.N))) return rc;
+    e->ring_slab = ring;
+    P.buf[0].ring = ring;
+    P.buf[1].ring = ring + cells * (size_t)e->cfg.N;
+    if (P.world > 1 && (rc = exchange_slab(e, ring, P.peer_ring))) return rc;
+  }
   P.rs_cap = R;
   if ((rc = dev_alloc(e, &P.rs_pos, R)) || (rc = dev_alloc(e, &P.rs_ess, R))) return rc;
   CUDA_TRY(cudaStreamSynchronize(e->stream));   // host vectors go out of scope
@@ -1016,7 +1258,18 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
   if (row_end < row_begin || row_end > e->P.R) return fail(SMC_ERR_ARG, "row range out of bounds");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   cudaEventRecord(e->ev0, e->stream);
-  for (int64_t r = row_begin; r < row_end; r++) launch_row(e, 0);
+  if (e->P.world == 1) {
+    for (int64_t r = row_begin; r < row_end; r++) launch_row(e, 0);
+  } else {
+    // sharded: row kernel (rank-local partials) -> exchange of the ranks' summaries -> commit (identical on all ranks).
+    // The exchange is also what orders a rank's writes against its peers' pulls.
+    for (int64_t r = row_begin; r < row_end; r++) {
+      launch_row(e, 0);
+      NCCL_TRY(g_nccl.AllGather(e->P.summ, e->P.allsumm, 4, ncclDouble, e->comm, e->stream));
+      smc_shard_commit_kernel<<<1, 1, 0, e->stream>>>(e->P);
+      e->launches += 2;
+    }
+  }
   cudaEventRecord(e->ev1, e->stream);
   CUDA_TRY(cudaGetLastError());
   // timing is collected lazily: the events are read at the next synchronising call
@@ -1037,6 +1290,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
     if (!e) return fail(SMC_ERR_ARG, "null engine");
     if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
     if (e->finished) return fail(SMC_ERR_STATE, "sweep after finish");
+    if (e->P.world > 1) return fail(SMC_ERR_STATE, "smc_sweep_many takes unsharded engines; sweep a sharded one with smc_sweep on every rank");
   }
   // every engine has its own stream: launches of different chunks interleave and run concurrently on the device
   CUDA_TRY(cudaSetDevice(engines[0]->cfg.device));
@@ -1129,6 +1383,11 @@ int smc_finish(smc_engine* e) {
   cudaEventRecord(e->ev0, e->stream);
   smc_flush_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
   e->launches++;
+  if (e->P.world > 1) {
+    // the ranks' tallies and recombination counts add up (the ln normaliser and the resampling log are already global)
+    NCCL_TRY(g_nccl.AllReduce(e->P.tallies, e->P.tallies, 6 * (size_t)e->cfg.E, ncclDouble, ncclSum, e->comm, e->stream));
+    NCCL_TRY(g_nccl.AllReduce(&e->P.ctrl->n_recomb, &e->P.ctrl->n_recomb, 1, ncclUint64, ncclSum, e->comm, e->stream));
+  }
   cudaEventRecord(e->ev1, e->stream);
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   float ms = 0;

@@ -16,9 +16,20 @@ def _f64(a):
     return np.ascontiguousarray(a, dtype=np.float64)
 
 
+def shard_unique_id():
+    """128-byte NCCL id for one sharded population (call on rank 0, pass to every rank's ParticleFilter)"""
+    buf = np.zeros(128, dtype=np.uint8)
+    check(lib().smc_shard_unique_id(_P(buf)))
+    return buf.tobytes()
+
+
 class ParticleFilter:
     def __init__(self, n, N, t_start, inv2N, mu, rho, seqlen, lags, seed=1, chunk=0, start_pos=0.0, ess_fraction=0.5,
-                 ancestral_aware=False, parity_scan=False, vb_logfac=None, rec_mask=None, device=0, slot_offset=0):
+                 ancestral_aware=False, parity_scan=False, vb_logfac=None, rec_mask=None, device=0, slot_offset=0,
+                 shard=None):
+        """N is the number of particles THIS engine holds.  shard = (rank, world, unique_id) splits a population of
+        world * N particles over `world` engines, one per process and GPU (smc_shard_attach); unique_id comes from
+        shard_unique_id() on rank 0 and is handed to the other ranks by the caller (smcsmc_b200.sharding)."""
         self.n, self.N, self.E = int(n), int(N), len(t_start)
         self._keep = [_f64(t_start), _f64(inv2N), _f64(lags),
                       None if vb_logfac is None else _f64(vb_logfac),
@@ -34,6 +45,13 @@ class ParticleFilter:
         self._h = ctypes.c_void_p()
         check(lib().smc_create(ctypes.byref(c), ctypes.byref(self._h)))
         self.R = 0
+        self.shard = None
+        if shard is not None:
+            rank, world, uid = shard
+            uid = np.ascontiguousarray(np.frombuffer(bytes(uid), dtype=np.uint8))
+            assert uid.size == 128
+            check(lib().smc_shard_attach(self._h, int(rank), int(world), _P(uid)))
+            self.shard = (int(rank), int(world))
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:

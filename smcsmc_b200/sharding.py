@@ -34,3 +34,18 @@ def allreduce_tallies(tallies, lnZ, device=None):
     dist.all_reduce(t)
     out = t.cpu().numpy()
     return out[:-1].reshape(np.shape(tallies)), float(out[-1])
+
+
+def broadcast_unique_id(device=None):
+    """rank 0 draws the id of a sharded population (smc_shard_unique_id) and every rank of the default process group
+    receives it; returns the 128 bytes to pass as ParticleFilter(shard=(rank, world, id))"""
+    import torch
+    import torch.distributed as dist
+    from .engine import shard_unique_id
+    t = torch.zeros(128, dtype=torch.uint8)
+    if dist.get_rank() == 0:
+        t = torch.frombuffer(bytearray(shard_unique_id()), dtype=torch.uint8).clone()
+    if device is not None:
+        t = t.to(device)
+    dist.broadcast(t, src=0)
+    return bytes(t.cpu().numpy().tobytes())
