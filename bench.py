@@ -111,9 +111,15 @@ def run_ours(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
-    C = a.chunks
+    shard = a.shard and world > 1
+    C = 1 if shard else a.chunks
     rows, t_start, inv2N, seqlen = workload(a.len_mb, C)
     R, E, N = sum(len(r.x_end) for r in rows), len(t_start), a.particles
+    if shard:
+        # ONE population of a.particles split over the ranks (smc_shard_attach): total work fixed => strong scaling
+        from smcsmc_b200.sharding import broadcast_unique_id
+        assert a.particles % world == 0
+        N = a.particles // world
     # pinned host staging of the step's inputs (the e2e leg copies from here)
     pin = []
     for r in rows:
@@ -125,8 +131,13 @@ def run_ours(a):
     def make_engines(seed):
         pfs = []
         for c in range(C):
-            pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, chunk=rank * C + c,
-                                  device=local, ess_fraction=a.ess)
+            if shard:
+                pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, chunk=c,
+                                      device=local, ess_fraction=a.ess,
+                                      shard=(rank, world, broadcast_unique_id(device="cuda")))
+            else:
+                pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed,
+                                      chunk=rank * C + c, device=local, ess_fraction=a.ess)
             d = pin[c]
             pf.upload_rows(d["x_end"].numpy(), d["alleles"].numpy(), d["is_site"].numpy(), d["max_rec"].numpy())
             pfs.append(pf)
@@ -140,6 +151,8 @@ def run_ours(a):
     def collect(pfs):
         t = np.sum([pf.tallies() for pf in pfs], axis=0)          # chunk tallies are summed (model.py:1176-1184)
         lnz = float(np.sum([pf.ln_normalization_factor() for pf in pfs]))
+        if shard:
+            return t, lnz                                           # smc_finish already made them global
         return allreduce_tallies(t, lnz, device="cuda")           # the one exchange per EM iteration (NCCL when N > 1)
 
     def timing(pfs):
@@ -152,7 +165,11 @@ def run_ours(a):
     def sweep_all(pfs):
         for pf in pfs:
             pf.init_particles()
-        S.sweep_many(pfs, a.rows_per_turn)
+        if shard:
+            for pf in pfs:
+                pf.sweep()
+        else:
+            S.sweep_many(pfs, a.rows_per_turn)
         for pf in pfs:
             pf.finish()
 
@@ -210,7 +227,7 @@ def run_ours(a):
         tt = torch.tensor([wall, wall_e2e, dev_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         wall, wall_e2e, dev_ms = [float(x) for x in tt.cpu()]
-    units = float(N) * seqlen * C * a.steps * world
+    units = float(N) * seqlen * C * a.steps * world        # sharded: N is the per-rank share, so this is the whole population
     rs_frac = counters["resamples"] / max(counters["rows"], 1)
     avg_launch_s = dev_ms * 1e-3 / max(launches, 1)
     abytes = algorithmic_bytes_per_launch(NSAM, N, E, rs_frac)
@@ -229,9 +246,11 @@ def run_ours(a):
     line = {
         "metric": "particle*sites/sec (s per EM iteration in ms_per_step)", "value": units / wall,
         "unit": "particle*sites/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": wall / a.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": wall / a.steps * 1e3, "higher_is_better": True, "scaling": "strong" if shard else "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic (scrm-simulated zigzag, bench_data/, seed 1)",
-        "config": {"workload": "configs[1]: 8 haplotypes x %g Mb zigzag, %d particles, 11 epochs, 1 EM iteration per step, "
+        "config": {"workload": ("8 haplotypes x %g Mb zigzag, ONE population of %d particles sharded over %d GPUs, 11 epochs"
+                                % (a.len_mb, a.particles, world)) if shard else
+                               "configs[1]: 8 haplotypes x %g Mb zigzag, %d particles, 11 epochs, 1 EM iteration per step, "
                                "swept as %d concurrent chunks (smc2 -chunks)" % (a.len_mb, N, C), "chunks": C, "rows": R, "particles": N, "haplotypes": NSAM, "epochs": E,
                    "per_gpu": "the whole %g Mb data set per GPU" % a.len_mb, "l2": "flushed between steps (256 MiB write)",
                    "lags": "reference-calibrated (DESIGN.md)"},
@@ -365,6 +384,9 @@ def main():
     ap.add_argument("--cpu-particles", type=int, default=1000)
     ap.add_argument("--cpu-chunk-mb", type=float, default=2.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard", action="store_true",
+                    help="with N > 1 ranks: split ONE population of --particles over the GPUs (smc_shard_attach) instead "
+                         "of giving every GPU its own chunks; a single chunk of --len-mb is swept")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)
