@@ -161,7 +161,15 @@ CASES = {
                     dict(p_unphased=0.15)),
     "n16_small": (16, 40, 25, 20000.0, [0.0, 8000.0], [1 / 2e4, 1 / 4e4], [4000.0, 1000.0], dict(p_missing=0.1)),
     "n2": (2, 64, 40, 50000.0, [0.0, 10000.0], [1 / 2e4, 1 / 2e4], [6000.0, 6000.0], {}),
+    # the limits of the ABI (SMC_MAX_HAPLOTYPES = 32, SMC_MAX_EPOCHS = 64) and degenerate shapes
+    "n32_max": (32, 24, 12, 6000.0, [0.0, 6000.0], [1 / 2e4, 1 / 3e4], [1500.0, 700.0], dict(p_missing=0.05, p_unphased=0.05)),
+    "E64_max": (4, 48, 30, 30000.0, [250.0 * k * (1 + 0.05 * k) for k in range(64)], [1 / (2e4 * (1 + (k % 3))) for k in range(64)],
+                [4000.0 - 50.0 * k for k in range(64)], {}),
+    "N1_single_particle": (4, 1, 25, 25000.0, [0.0], [1 / 2e4], [3000.0], {}),
+    "R1_single_row": (4, 64, 1, 5000.0, [0.0, 9000.0], [1 / 2e4, 1 / 2e4], [1000.0, 1000.0], {}),
+    "all_missing": (4, 64, 30, 30000.0, [0.0, 9000.0], [1 / 2e4, 1 / 2e4], [4000.0, 1000.0], dict(p_missing=1.0)),
 }
+NO_RESAMPLING = {"N1_single_particle", "R1_single_row", "all_missing"}   # uniform or single weights: ESS never drops
 
 
 @pytest.mark.parametrize("name", sorted(CASES))
@@ -191,7 +199,7 @@ def test_full_filter_vs_oracle(S, name):
                               ancestral_aware=int(name == "n2"))
     c = pf.counters()
     assert c["err"] == 0 and c["rows"] == R
-    assert c["resamples"] == ref["n_resample"] and ref["n_resample"] > 0
+    assert c["resamples"] == ref["n_resample"] and (ref["n_resample"] > 0 or name in NO_RESAMPLING)
     assert c["recombinations"] == ref["n_recomb"] or max_rec is not None   # the oracle counts RECORDED events
     assert np.array_equal(parent, ref["parent"])
     np.testing.assert_allclose(height, ref["height"], rtol=1e-11, atol=0)
@@ -204,7 +212,7 @@ def test_full_filter_vs_oracle(S, name):
     t = pf.tallies()
     for q in (0, 1, 3, 4):       # counts and opportunities (linear in the weights)
         np.testing.assert_allclose(t[q], ref["tallies"][q], rtol=1e-10, atol=1e-13)
-    assert t[1].sum() > 0 and t[4].sum() > 0 and t[3].sum() > 0
+    assert t[4].sum() > 0 and (name == "R1_single_row" or (t[1].sum() > 0 and t[3].sum() > 0))
     # weight^2 tallies: copies do not share records, so sum(w^2 opp) is a lower bound of the reference's value
     assert np.all(t[2] <= ref["tallies"][2] * (1 + 1e-9) + 1e-300)
     assert np.all(t[5] <= ref["tallies"][5] * (1 + 1e-9) + 1e-300)
