@@ -207,11 +207,19 @@ def run_ours(a):
     launches = l1 - l0
     # ---- e2e leg: host buffers through the public calls, H2D + D2H inside the timed region ----
     def step_e2e(seed):
+        tr = [time.perf_counter()]
         p = make_engines(seed)
+        tr.append(time.perf_counter())
         sweep_all(p)
+        tr.append(time.perf_counter())
         out = collect(p)
+        tr.append(time.perf_counter())
         for pf in p:
             pf.close()
+        tr.append(time.perf_counter())
+        if os.environ.get("BENCH_TRACE") and rank == 0:
+            print("[bench] e2e step: create+upload %.1f ms, sweep %.1f ms, read-back %.1f ms, destroy %.1f ms"
+                  % tuple((tr[k + 1] - tr[k]) * 1e3 for k in range(4)), file=sys.stderr, flush=True)
         return out
     step_e2e(300)
     barrier()

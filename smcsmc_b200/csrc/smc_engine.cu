@@ -15,8 +15,12 @@
 //   height  [n-1][N] f64   internal-node heights (leaves sit at 0), slots height-sorted
 //   parent  [2n-1][N] i8
 //   logw[N], next_base[N] f64
-//   ring    [E][B][4][N] f64   lag buckets of pending tallies: coal count, coal opp, recomb count, recomb opp
-// all of it twice (ping-pong: resampling gathers from one copy into the other).
+//   open    [E][N][4] f64      tallies of the lag bucket each epoch is writing now: coal count, coal opp, recomb count,
+//                              recomb opp -- travels with the particle
+// all of it twice (ping-pong: resampling gathers from one copy into the other), plus, for the CLOSED lag buckets,
+//   frozen  [E][B][N][4] f64   written once, at the slot of the particle that owned the record when the bucket closed
+//   map     [E][B][N] i32      (twice) which slot holds the record of this particle's ancestor: a resampling copies
+//                              4 bytes per closed bucket instead of the 32-byte record
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <nccl.h>   // types only: the library is bound with dlopen when an engine is sharded
@@ -69,7 +73,8 @@ struct StateBuf {
   signed char* parent;  // [nn][N]
   double* logw;
   double* next_base;
-  double* ring;         // [E*B*4][N]
+  double* open;         // [E][N][4]
+  int* map;             // [E][B][N] global slot of the ancestor's frozen record
 };
 
 struct Params {
@@ -86,8 +91,11 @@ struct Params {
   const signed char* alleles;
   const unsigned char* is_site;
   const int* max_rec;
-  const int* kstart;       // [R][E] bucket index at the row's left end
-  const int* kslot;        // [R][E] kstart modulo the ring depth B
+  const int* kstart;       // [R+1][E] bucket index at the row's left end (row R: after the last row)
+  const int* kslot;        // [R+1][E] kstart modulo the ring depth B
+  const int* kfirst;       // [R+1][E] oldest bucket still pending once the row's own hand-over is done
+  const unsigned long long* closes;   // [R] bit e: the bucket open at the row's left end closes by the row end
+  double* frozen;          // [E][B][N][4]
   const int* ub_off;       // [E+1]
   const double* ub;        // bucket upper bounds per epoch (last = +inf: the end-of-data bucket)
   const int* cons_off;     // [R+1]
@@ -104,12 +112,12 @@ struct Params {
   int* anc;                // [N] ancestry of the last resampling (global particle index when sharded)
   double* rs_pos; double* rs_ess; long long rs_cap;
   // particle sharding over ranks: this engine owns particles [base, base + N) of Ntot.  What a
-  // pulling offspring reads of its parent -- tree, next_base, ring, and the weight partials -- lives in two slabs
+  // pulling offspring reads of its parent -- tree, next_base, tallies, and the weight partials -- lives in two slabs
   // whose peer mappings differ from the local addresses by a constant byte offset per rank.
   int rank, world;
   long long Ntot, base;
   long long peer_state[SMC_MAX_RANKS];   // byte offset: peer r's state slab - mine
-  long long peer_ring[SMC_MAX_RANKS];    // byte offset: peer r's ring slab - mine
+  long long peer_tally[SMC_MAX_RANKS];   // byte offset: peer r's tally slab (open, map, frozen) - mine
   double* summ;             // [3] this rank's (max, sum, sum of squares) after a row
   double* allsumm;          // [world][3] gathered
   double* rank_off[2];      // [world+1] normalised exclusive prefix of the rank totals, by row parity
@@ -121,16 +129,31 @@ __device__ __forceinline__ Tp* at_peer(Tp* p, long long delta) {
   return reinterpret_cast<Tp*>(reinterpret_cast<char*>(const_cast<typename std::remove_const<Tp>::type*>(p)) + delta);
 }
 
-// Tally sink writing into the particle's lag-bucket ring.  Recombination opportunity (the dense record: every epoch,
-// every stretch) is summed in shared memory over the row and written once per epoch at the row end, unless a bucket
-// bound of that epoch falls inside the row (then each stretch is split at the bound and written directly).
+// the frozen record (4 doubles) of closed bucket (e, slot s) that belongs to particle i's ancestor
+__device__ __forceinline__ void load_frozen(const Params& P, const int* map, int e, int s, long long i, double out[4]) {
+  const size_t es = (size_t)(e * P.B + s);
+  const int m = map[es * P.N + i];
+  const double* f = P.frozen;
+  long long l = m;
+  if (P.world > 1) { const int r = m / P.N; l = m - r * P.N; f = at_peer(f, P.peer_tally[r]); }
+  const double2* c2 = reinterpret_cast<const double2*>(f + (es * P.N + l) * 4);
+  double2 a = c2[0], b = c2[1];
+  out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
+}
+
+// Tally sink.  Records of the bucket that stays open beyond this row go to the particle's `open` cells, records of
+// buckets that close by the row end go straight to their `frozen` cells (phase 1 has moved the carried values there).
+// Recombination opportunity (the dense record: every epoch, every stretch) is summed in shared memory over the row and
+// written once per epoch at the row end, unless a bucket bound of that epoch falls inside the row (then each stretch
+// is split at the bound and written directly).
 template <int BS>
 struct RingSink {
   const Params* P;
-  double* ring;    // destination copy
+  double* open;    // destination copy of the open cells
   int i;           // particle index
   const int* ks;   // bucket index of this row's left end [E]
   const int* ksl;  // the same modulo the ring depth [E]
+  const int* kn;   // bucket index of the NEXT row's left end [E]: the bucket that stays open
   double* ACC;     // [E][BS] shared
   int t;
   unsigned long long split;   // bit e: a bound of epoch e lies inside this row
@@ -141,9 +164,10 @@ struct RingSink {
     return k;
   }
   __device__ __forceinline__ double* cell(int e, int k, int q) const {
+    if (k == kn[e]) return open + ((size_t)e * P->N + i) * 4 + q;
     int s = ksl[e] + (k - ks[e]);
     if (s >= P->B) s -= P->B;
-    return ring + ((size_t)((e * P->B + s) * 4 + q)) * (size_t)P->N + i;
+    return P->frozen + ((size_t)(e * P->B + s) * P->N + i) * 4 + q;
   }
   __device__ void row_begin(double x1) {
     split = 0ull;
@@ -365,9 +389,9 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       int2 ek = P.cons[q];
       double v[6] = {0, 0, 0, 0, 0, 0};
       if (live) {
-        const double* cell = src.ring + ((size_t)((ek.x * P.B + (ek.y % P.B)) * 4)) * P.N + i;
-        double cc = cell[0], co = cell[(size_t)P.N], rc = cell[(size_t)2 * P.N], ro = cell[(size_t)3 * P.N];
-        v[0] = w * cc; v[1] = w * co; v[2] = w2 * co; v[3] = w * rc; v[4] = w * ro; v[5] = w2 * ro;
+        double f[4];
+        load_frozen(P, src.map, ek.x, ek.y % P.B, i, f);
+        v[0] = w * f[0]; v[1] = w * f[1]; v[2] = w2 * f[1]; v[3] = w * f[2]; v[4] = w * f[3]; v[5] = w2 * f[3];
       }
 #pragma unroll
       for (int a = 0; a < 6; a++) {
@@ -422,7 +446,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
         const int ra = (int)(ga / P.N);
         a = ga % P.N;
         dS = P.peer_state[ra];
-        dR = P.peer_ring[ra];
+        dR = P.peer_tally[ra];
       }
       logw = c->child_logw;
     } else {
@@ -436,27 +460,50 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       for (int v = n; v < nn; v++) T.h(v) = sh_[(size_t)(v - n) * P.N + a];
       for (int v = 0; v < nn; v++) T.par(v) = sp_[(size_t)v * P.N + a];
     }
-    // ring: gather everything on a pull; consumed buckets are cleared either way
-    if (resampled) {
-      // 8 independent loads in flight per thread before the stores (the two copies never alias)
-      const int cells = E * P.B * 4;
-      const double* __restrict__ sp = at_peer(src.ring, dR) + a;
-      double* __restrict__ dp = dst.ring + i;
+    // tallies: the open cells travel by value, closed buckets by reference (4-byte slot ids); a bucket that closes
+    // during this row is frozen now -- its carried value moves to this particle's own frozen cell and the buckets born
+    // inside the row start from zero there -- so that phase 2 only ever adds to cells that exist
+    {
+      const long long rowc = row < P.R ? row : P.R;
+      const int* ks = P.kstart + rowc * E;
+      const int* ksl = P.kslot + rowc * E;
+      const int* kf = P.kfirst + rowc * E;
+      const unsigned long long closes = (mode == 0) ? P.closes[row] : 0ull;
+      const double* __restrict__ osrc = at_peer(src.open, dR);
+      const int* __restrict__ msrc = at_peer(src.map, dR);
+      const int self = (int)(P.base + i);
       const size_t NN = (size_t)P.N;
-      int q = 0;
-      for (; q + 8 <= cells; q += 8) {
-        double v[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = __ldcs(sp + (size_t)(q + k) * NN);
-#pragma unroll
-        for (int k = 0; k < 8; k++) dp[(size_t)(q + k) * NN] = v[k];
+      for (int e = 0; e < E; e++) {
+        const bool closing = (closes >> e) & 1ull;
+        if (resampled || closing) {
+          const double2* o2 = reinterpret_cast<const double2*>(osrc + ((size_t)e * NN + a) * 4);
+          double2 o0 = o2[0], o1 = o2[1];
+          double2* d2 = reinterpret_cast<double2*>(dst.open + ((size_t)e * NN + i) * 4);
+          if (closing) {
+            int s = ksl[e];
+            double2* f2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * 4);
+            f2[0] = o0; f2[1] = o1;
+            dst.map[(size_t)(e * P.B + s) * NN + i] = self;
+            const int kn = P.kstart[(row + 1) * E + e];
+            for (int k = ks[e] + 1; k < kn; k++) {
+              if (++s >= P.B) s = 0;
+              double2* z2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * 4);
+              z2[0] = make_double2(0.0, 0.0); z2[1] = make_double2(0.0, 0.0);
+              dst.map[(size_t)(e * P.B + s) * NN + i] = self;
+            }
+            o0 = make_double2(0.0, 0.0); o1 = o0;
+          }
+          d2[0] = o0; d2[1] = o1;
+        }
+        if (resampled) {
+          int s = ksl[e];
+          for (int k = ks[e] - 1; k >= kf[e]; k--) {
+            if (--s < 0) s = P.B - 1;
+            const size_t at = (size_t)(e * P.B + s) * NN;
+            dst.map[at + i] = msrc[at + a];
+          }
+        }
       }
-      for (; q < cells; q++) dp[(size_t)q * NN] = sp[(size_t)q * NN];
-    }
-    for (int q = c0; q < c1; q++) {
-      int2 ek = P.cons[q];
-      double* cell = dst.ring + ((size_t)((ek.x * P.B + (ek.y % P.B)) * 4)) * P.N + i;
-      cell[0] = 0.0; cell[(size_t)P.N] = 0.0; cell[(size_t)2 * P.N] = 0.0; cell[(size_t)3 * P.N] = 0.0;
     }
     if (redraw) {
       Rng rr;
@@ -474,7 +521,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
-    RingSink<BS> sink{&P, dst.ring, (int)i, P.kstart + row * E, P.kslot + row * E, T.ACC, t, 0ull};
+    RingSink<BS> sink{&P, dst.open, (int)i, P.kstart + row * E, P.kslot + row * E, P.kstart + (row + 1) * E, T.ACC, t, 0ull};
     nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
   }
 
@@ -649,12 +696,18 @@ __global__ void __launch_bounds__(128) smc_flush_kernel(const __grid_constant__ 
   for (int e = 0; e < E; e++) {
     int nbk = P.ub_off[e + 1] - P.ub_off[e];
     double v[6] = {0, 0, 0, 0, 0, 0};
-    for (int k = first_pending[e]; k < nbk; k++) {
-      if (live) {
-        double* cell = src.ring + ((size_t)((e * P.B + (k % P.B)) * 4)) * P.N + i;
-        double cc = cell[0], co = cell[(size_t)P.N], rc = cell[(size_t)2 * P.N], ro = cell[(size_t)3 * P.N];
-        v[0] += w * cc; v[1] += w * co; v[2] += w * w * co; v[3] += w * rc; v[4] += w * ro; v[5] += w * w * ro;
-        cell[0] = 0.0; cell[(size_t)P.N] = 0.0; cell[(size_t)2 * P.N] = 0.0; cell[(size_t)3 * P.N] = 0.0;
+    if (live) {
+      // closed buckets the schedule never reached, through the ancestor maps; then the bucket still open (+inf bound)
+      for (int k = first_pending[e]; k < nbk; k++) {
+        double f[4];
+        if (k < nbk - 1) {
+          load_frozen(P, src.map, e, k % P.B, i, f);
+        } else {
+          const double2* o2 = reinterpret_cast<const double2*>(src.open + ((size_t)e * P.N + i) * 4);
+          double2 a = o2[0], b = o2[1];
+          f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+        }
+        v[0] += w * f[0]; v[1] += w * f[1]; v[2] += w * w * f[1]; v[3] += w * f[2]; v[4] += w * f[3]; v[5] += w * w * f[3];
       }
     }
     for (int a = 0; a < 6; a++) { v[a] = warp_sum(v[a]); if (lane == 0) tal[a][warp] = v[a]; }
@@ -866,7 +919,8 @@ struct smc_engine {
   int* first_pending_d = nullptr;
   // particle sharding
   void* state_slab = nullptr;
-  void* ring_slab = nullptr;
+  void* ring_slab = nullptr;            // tally slab: open[2], map[2], frozen
+  size_t open_bytes = 0;
   ncclComm_t comm = nullptr;
   std::vector<void*> peer_maps;         // cudaIpcOpenMemHandle results, closed in smc_destroy
 };
@@ -1017,7 +1071,7 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   P.N = cfg->N; P.parity_scan = cfg->parity_scan; P.seed = cfg->seed; P.chunk = cfg->chunk;
   P.slot_offset = cfg->slot_offset; P.ess_fraction = cfg->ess_fraction; P.start_pos = cfg->start_pos;
   // block size: keep every SM busy when there are few particles
-  e->BS = (cfg->N <= 148 * 64 * 2) ? 64 : 128;
+  e->BS = (cfg->N < 8192) ? 64 : 128;     // measured: 128 is 3-6 % faster from 10^4 particles on (profiles/r1_occupancy_probe.txt)
   if (const char* s = getenv("SMC_BLOCK")) { int b = atoi(s); if (b == 32 || b == 64 || b == 128) e->BS = b; }   // tuning knob
   P.nblocks = (cfg->N + e->BS - 1) / e->BS;
   e->smem = tree_smem(P.m.nn, P.m.E, e->BS);
@@ -1179,31 +1233,45 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
     ub_off[ep + 1] = ub_off[ep] + (int)ub[ep].size();
     ub_flat.insert(ub_flat.end(), ub[ep].begin(), ub[ep].end());
   }
-  // bucket at each row's left end, and the ring depth needed: buckets in flight = [next to consume, highest written]
-  std::vector<int> kstart((size_t)R * E), kslot((size_t)R * E);
-  std::vector<int> kcur(E, 0), consumed(E, 0);
-  int B = 1;
-  for (int64_t r = 0; r < R; r++) {
+  // bucket at each row's left end (row R: after the last row), which buckets close inside each row, the oldest pending
+  // bucket per launch, and the ring depth: a slot is re-used only by a bucket born after the launch whose hand-over
+  // consumed the old occupant (other blocks of that launch may still be reading it)
+  std::vector<int> kstart((size_t)(R + 1) * E), kslot((size_t)(R + 1) * E), kfirst((size_t)(R + 1) * E);
+  std::vector<unsigned long long> closes(R, 0ull);
+  std::vector<int> kcur(E, 0);
+  for (int64_t r = 0; r <= R; r++) {
     double x0 = r ? x_end[r - 1] : e->cfg.start_pos;
     for (int ep = 0; ep < E; ep++) {
       while (ub[ep][kcur[ep]] <= x0) kcur[ep]++;
       kstart[(size_t)r * E + ep] = kcur[ep];
-      int khi = kcur[ep];
-      while (ub[ep][khi] <= x_end[r]) khi++;
-      B = std::max(B, khi - consumed[ep] + 1);
     }
-    for (int q = cons_off[r]; q < cons_off[r + 1]; q++) consumed[cons[q].x] = cons[q].y + 1;
   }
+  {
+    std::vector<int> done(E, 0);
+    for (int64_t r = 0; r <= R; r++) {       // launch r hands over cons[cons_off[r-1] .. cons_off[r])
+      if (r > 0) for (int q = cons_off[r - 1]; q < cons_off[r]; q++) done[cons[q].x] = cons[q].y + 1;
+      for (int ep = 0; ep < E; ep++) kfirst[(size_t)r * E + ep] = done[ep];
+    }
+  }
+  int B = 2;
+  for (int64_t r = 0; r < R; r++)
+    for (int ep = 0; ep < E; ep++) {
+      const int ks = kstart[(size_t)r * E + ep], kn = kstart[(size_t)(r + 1) * E + ep];
+      if (kn > ks) closes[r] |= 1ull << ep;
+      const int oldest = r > 0 ? kfirst[(size_t)(r - 1) * E + ep] : 0;
+      B = std::max(B, kn - oldest + 1);
+    }
   Params& P = e->P;
   P.B = B;
   P.R = R;
   std::vector<int> mr(R);
   for (int64_t r = 0; r < R; r++) mr[r] = max_rec_epoch ? max_rec_epoch[r] : E - 1;
   int rc;
-  double* d_x; signed char* d_al; unsigned char* d_site; int* d_mr; int* d_ks; int* d_ksl; int* d_uboff; double* d_ub; int* d_co; int2* d_cons;
+  double* d_x; signed char* d_al; unsigned char* d_site; int* d_mr; int* d_ks; int* d_ksl; int* d_uboff; double* d_ub; int* d_co; int2* d_cons; int* d_kf; unsigned long long* d_cl;
   if ((rc = dev_alloc(e, &d_x, R, false)) || (rc = dev_alloc(e, &d_al, (size_t)R * n, false)) ||
       (rc = dev_alloc(e, &d_site, R, false)) || (rc = dev_alloc(e, &d_mr, R, false)) ||
-      (rc = dev_alloc(e, &d_ks, (size_t)R * E, false)) || (rc = dev_alloc(e, &d_ksl, (size_t)R * E, false)) || (rc = dev_alloc(e, &d_uboff, E + 1, false)) ||
+      (rc = dev_alloc(e, &d_ks, (size_t)(R + 1) * E, false)) || (rc = dev_alloc(e, &d_ksl, (size_t)(R + 1) * E, false)) ||
+      (rc = dev_alloc(e, &d_kf, (size_t)(R + 1) * E, false)) || (rc = dev_alloc(e, &d_cl, R, false)) || (rc = dev_alloc(e, &d_uboff, E + 1, false)) ||
       (rc = dev_alloc(e, &d_ub, ub_flat.size(), false)) || (rc = dev_alloc(e, &d_co, R + 1, false)) ||
       (rc = dev_alloc(e, &d_cons, cons.size(), false)) || (rc = dev_alloc(e, &e->first_pending_d, E, false)))
     return rc;
@@ -1214,6 +1282,8 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
   for (size_t q = 0; q < kstart.size(); q++) kslot[q] = kstart[q] % B;
   CUDA_TRY(cudaMemcpyAsync(d_ks, kstart.data(), kstart.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_ksl, kslot.data(), kslot.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_kf, kfirst.data(), kfirst.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_cl, closes.data(), closes.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_uboff, ub_off.data(), ub_off.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_ub, ub_flat.data(), ub_flat.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(d_co, cons_off.data(), cons_off.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
@@ -1221,16 +1291,22 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
     CUDA_TRY(cudaMemcpyAsync(d_cons, cons.data(), cons.size() * sizeof(int2), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, e->first_pending_h.data(), E * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   P.x_end = d_x; P.alleles = d_al; P.is_site = d_site; P.max_rec = d_mr; P.kstart = d_ks; P.kslot = d_ksl; P.ub_off = d_uboff; P.ub = d_ub;
-  P.cons_off = d_co; P.cons = d_cons;
-  // the ring and the resampling log need R / B
-  const size_t cells = (size_t)E * B * 4;
+  P.cons_off = d_co; P.cons = d_cons; P.kfirst = d_kf; P.closes = d_cl;
+  // tally storage (one slab, one IPC handle): open cells and ancestor maps twice, frozen records once
   {
-    double* ring = nullptr;
-    if ((rc = dev_alloc(e, &ring, 2 * cells * (size_t)e->cfg.N))) return rc;
-    e->ring_slab = ring;
-    P.buf[0].ring = ring;
-    P.buf[1].ring = ring + cells * (size_t)e->cfg.N;
-    if (P.world > 1 && (rc = exchange_slab(e, ring, P.peer_ring))) return rc;
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t NN = (size_t)e->cfg.N;
+    const size_t s_open = up((size_t)E * NN * 4 * sizeof(double)), s_map = up((size_t)E * B * NN * sizeof(int)),
+                 s_frozen = up((size_t)E * B * NN * 4 * sizeof(double));
+    char* slab = nullptr;
+    if ((rc = dev_alloc(e, &slab, 2 * s_open + 2 * s_map + s_frozen))) return rc;
+    e->ring_slab = slab;
+    e->open_bytes = s_open;
+    char* q = slab;
+    for (int b = 0; b < 2; b++) { P.buf[b].open = (double*)q; q += s_open; }
+    for (int b = 0; b < 2; b++) { P.buf[b].map = (int*)q; q += s_map; }
+    P.frozen = (double*)q;
+    if (P.world > 1 && (rc = exchange_slab(e, slab, P.peer_tally))) return rc;
   }
   P.rs_cap = R;
   if ((rc = dev_alloc(e, &P.rs_pos, R)) || (rc = dev_alloc(e, &P.rs_ess, R))) return rc;
@@ -1348,8 +1424,8 @@ int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_l
   }
   if (rho > 0) P.m.rho = rho;
   P.seed = seed;
-  const size_t cells = (size_t)E * P.B * 4;
-  for (int b = 0; b < 2; b++) CUDA_TRY(cudaMemsetAsync(P.buf[b].ring, 0, cells * (size_t)P.N * sizeof(double), e->stream));
+  // frozen records and maps are (re)initialised when their bucket is born; only the open cells start from zero
+  for (int b = 0; b < 2; b++) CUDA_TRY(cudaMemsetAsync(P.buf[b].open, 0, e->open_bytes, e->stream));
   CUDA_TRY(cudaMemsetAsync(P.tallies, 0, 6 * (size_t)E * sizeof(double), e->stream));
   CUDA_TRY(cudaMemsetAsync(P.anc, 0xff, (size_t)P.N * sizeof(int), e->stream));
   Ctrl init;
