@@ -94,8 +94,9 @@ class Clocks(threading.Thread):
 def algorithmic_bytes_per_launch(n, N, E, resample_fraction):
     """DESIGN.md 'roofline': per particle and row the state is read and written once, S = 8(n-1) + (2n-1) + 16 bytes,
     plus one read-modify-write of the open recombination-opportunity cell per epoch (16 E) and the 8-byte weight prefix;
-    a resampling row additionally gathers the parent's S bytes.  The lag-bucket ring the gather also moves is NOT
-    counted: it is overhead of the current design, visible as traffic > algorithmic."""
+    a resampling row additionally gathers the parent's S bytes.  What the gather moves of the tallies (32 B of open
+    cells per epoch and a 4-byte ancestor slot per pending lag bucket) is NOT counted: it is overhead of the design,
+    visible as traffic > algorithmic."""
     S = 8 * (n - 1) + (2 * n - 1) + 16
     return N * (2 * S + 16 * E + 8 + resample_fraction * S)
 
@@ -246,11 +247,11 @@ def run_ours(a):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = abytes / avg_launch_s / 1e9
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/r1_row_kernel_ncu_full.csv (n = 8, E = 11,
-    # N = 10 000, ring depth 14): 52.5 MB on a row that pulls after a resampling, 2.2 MB otherwise
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the six launches in
+    # profiles/r1_row_kernel_t2_ncu_full.csv (n = 8, E = 11, N = 10 000; ncu runs every launch cold-cache)
     traffic = None
     if (NSAM, E, N) == (8, 11, 10000):
-        traffic = rs_frac * 52.5e6 + (1.0 - rs_frac) * 2.2e6
+        traffic = 4.99e6
     line = {
         "metric": "particle*sites/sec (s per EM iteration in ms_per_step)", "value": units / wall,
         "unit": "particle*sites/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
