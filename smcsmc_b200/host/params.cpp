@@ -62,6 +62,10 @@ void parse(int argc, char** argv, Params& P) {
     }
     else if (f == "-arg") unsupported(f, "posterior ARG output");
     else if (f == "-EM") P.EM_steps = (int)a.next_double(f);
+    else if (f == "-chunks") {
+      P.chunks = (int)a.next_double(f);
+      if (P.chunks < 1 || P.chunks > 4096) throw std::invalid_argument("Out of range: -chunks " + a.cur());
+    }
     else if (f == "-xr" || f == "-xc") {
       int last, first = read_range(a.next(f), last);
       last++;

@@ -27,6 +27,7 @@ struct Params {
   double ESS_fraction = 0.5;
   bool ESS_default = true;
   int EM_steps = 0;
+  int chunks = 1;                 // extension: sweep this many equal windows of the locus concurrently on the device
   double lag = 0.0;
   bool calibrate_lag = true;
   double lag_fraction = 2.0;

@@ -104,6 +104,7 @@ void print_help(const Params& P) {
   opt("-seg", "STR", "Data file in seg format [ Chrom1.seg ]");
   opt("-o", "STR", "Prefix for output files");
   opt("-EM", "INT", "EM iterations [ 20 ]");
+  opt("-chunks", "INT", "(B200 engine) sweep INT equal windows of the locus concurrently, tallies added [ 1 ]");
   opt("-startpos", "INT", "First nucleotide position to analyze [ 1 ]");
   opt("-nsam", "INT", "Number of haplotypes (2..32)");
   opt("-log", " ", "Generate *.log file");
@@ -130,7 +131,8 @@ struct Tallies {   // CountModel totals incl. the initial pseudo-counts (count.c
 };
 
 // one EM iteration: pfARG_core (smcsmc.cpp:278-400)
-void pfARG_core(Params& P, const host::SegRows& rows, const Out& out, int em, int device) {
+void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<double>& chunk_start, double chunk_len,
+                const Out& out, int em, int device) {
   const int E = P.num_epochs(), n = (int)P.nsam;
   vector<double> t_start(E), inv2N(E), vb(E), lags(E);
   vector<uint8_t> mask(E);
@@ -151,7 +153,7 @@ void pfARG_core(Params& P, const host::SegRows& rows, const Out& out, int em, in
   if (P.calibrate_lag) {
     vector<double> surv(E);
     vector<int64_t> cnt(E);
-    check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N.data(), P.recombination_rate, P.loci_length, 1,
+    check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N.data(), P.recombination_rate, chunk_len, 1,
                                  8192, surv.data(), cnt.data()));
     for (int e = 0; e < E; e++) {
       clog << " Epoch " << e << " (" << cnt[e] << " events): survival distance " << surv[e] << endl;
@@ -164,50 +166,73 @@ void pfARG_core(Params& P, const host::SegRows& rows, const Out& out, int em, in
   clog << " Starting position: " << fixed << setprecision(0) << P.start_position << setprecision(6) << scientific << endl;
   clog.unsetf(ios::floatfield);
 
-  const size_t R = rows.rows();
-  vector<int32_t> max_rec(R);
-  for (size_t r = 0; r < R; r++) {   // max_epoch_to_update (smcsmc.cpp:266-275)
-    int e = 0;
-    while (e < E && rows.dist_to_mutation[r] < 0.5 * lags[e]) e++;
-    max_rec[r] = e - 1;
+  // One engine per chunk.  The reference runs one process per chunk (smc2 -chunks, model.py:563-662) and adds the
+  // .out files; here the chunks of one process are swept concurrently on the device (smc_sweep_many) and added up.
+  const size_t C = chunks.size();
+  vector<smc_engine*> eng(C, nullptr);
+  struct Guard { vector<smc_engine*>& v; ~Guard() { for (smc_engine* e : v) smc_destroy(e); } } guard{eng};
+  size_t Rtot = 0;
+  for (size_t k = 0; k < C; k++) {
+    const host::SegRows& rows = chunks[k];
+    const size_t R = rows.rows();
+    Rtot += R;
+    vector<int32_t> max_rec(R);
+    for (size_t r = 0; r < R; r++) {   // max_epoch_to_update (smcsmc.cpp:266-275)
+      int e = 0;
+      while (e < E && rows.dist_to_mutation[r] < 0.5 * lags[e]) e++;
+      max_rec[r] = e - 1;
+    }
+    smc_config c;
+    memset(&c, 0, sizeof c);
+    c.n = n; c.N = (int32_t)P.N; c.E = E; c.device = device;
+    c.seed = P.seed + (uint64_t)em * 0x9E3779B97F4A7C15ull;
+    c.chunk = (uint32_t)(((long long)chunk_start[k]) & 0xFFFFFF);
+    c.mu = P.mutation_rate; c.rho = P.recombination_rate; c.seqlen = chunk_len; c.start_pos = 0.0;
+    c.ess_fraction = P.ESS_fraction; c.ancestral_aware = P.ancestral_aware; c.parity_scan = 0;
+    c.t_start = t_start.data(); c.inv2N = inv2N.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
+    check(smc_create(&c, &eng[k]));
+    check(smc_upload_rows(eng[k], rows.x_end.data(), rows.alleles.data(), rows.is_site.data(), max_rec.data(), (int64_t)R));
+    check(smc_init_particles(eng[k]));
   }
-  smc_config c;
-  memset(&c, 0, sizeof c);
-  c.n = n; c.N = (int32_t)P.N; c.E = E; c.device = device;
-  c.seed = P.seed + (uint64_t)em * 0x9E3779B97F4A7C15ull;
-  c.chunk = (uint32_t)(((long long)P.start_position) & 0xFFFFFF);
-  c.mu = P.mutation_rate; c.rho = P.recombination_rate; c.seqlen = P.loci_length; c.start_pos = 0.0;
-  c.ess_fraction = P.ESS_fraction; c.ancestral_aware = P.ancestral_aware; c.parity_scan = 0;
-  c.t_start = t_start.data(); c.inv2N = inv2N.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
-  smc_engine* eng = nullptr;
-  check(smc_create(&c, &eng));
-  struct Guard { smc_engine* e; ~Guard() { smc_destroy(e); } } guard{eng};
-  check(smc_upload_rows(eng, rows.x_end.data(), rows.alleles.data(), rows.is_site.data(), max_rec.data(), (int64_t)R));
-  check(smc_init_particles(eng));
-  const int64_t step = max<int64_t>(1, (int64_t)R / 100);
-  for (int64_t r0 = 0; r0 < (int64_t)R; r0 += step) {
-    int64_t r1 = min<int64_t>((int64_t)R, r0 + step);
-    check(smc_sweep(eng, r0, r1));
-    cout << "\r Particle filtering " << setw(4) << int(rows.x_end[r1 - 1] * 100 / P.loci_length) << "% completed." << flush;
+  if (C == 1) {
+    const host::SegRows& rows = chunks[0];
+    const int64_t R = (int64_t)rows.rows();
+    const int64_t step = max<int64_t>(1, R / 100);
+    for (int64_t r0 = 0; r0 < R; r0 += step) {
+      int64_t r1 = min<int64_t>(R, r0 + step);
+      check(smc_sweep(eng[0], r0, r1));
+      cout << "\r Particle filtering " << setw(4) << int(rows.x_end[r1 - 1] * 100 / chunk_len) << "% completed." << flush;
+    }
+  } else {
+    cout << " Particle filtering " << C << " chunks (" << Rtot << " segments) concurrently." << endl;
+    check(smc_sweep_many(eng.data(), (int32_t)C, 4));
   }
   cout << "\r Particle filtering step 100% completed." << endl;
-  check(smc_finish(eng));
-  vector<double> t(6 * E);
+  vector<double> t(6 * E, 0.0);
   double lnZ = 0;
-  int64_t counters[4];
-  check(smc_get_tallies(eng, t.data()));
-  int rc = smc_get_lnZ(eng, &lnZ);
-  if (rc == SMC_ERR_NUMERIC) throw runtime_error("Zero or negative probabilities");
-  check(rc);
-  check(smc_get_counters(eng, counters));
-  clog << "Got to end of sequence; resampled " << counters[1] << " times" << endl;
-  if (P.record_resample_file) {
-    vector<double> pos(counters[1] + 1), ess(counters[1] + 1);
-    int64_t k = 0;
-    check(smc_get_resample_log(eng, pos.data(), ess.data(), counters[1], &k));
-    ofstream f(out.resample_name.c_str(), ios::out | ios::app | ios::binary);
-    for (int64_t q = 0; q < k; q++) f << (int)pos[q] << "\t" << ess[q] << endl;
+  int64_t counters[4] = {0, 0, 0, 0};
+  for (size_t k = 0; k < C; k++) {
+    check(smc_finish(eng[k]));
+    vector<double> tk(6 * E);
+    double lz = 0;
+    int64_t ck[4];
+    check(smc_get_tallies(eng[k], tk.data()));
+    int rc = smc_get_lnZ(eng[k], &lz);
+    if (rc == SMC_ERR_NUMERIC) throw runtime_error("Zero or negative probabilities");
+    check(rc);
+    check(smc_get_counters(eng[k], ck));
+    for (int q = 0; q < 6 * E; q++) t[q] += tk[q];
+    lnZ += lz;
+    for (int q = 0; q < 4; q++) counters[q] += ck[q];
+    if (P.record_resample_file) {
+      vector<double> pos(ck[1] + 1), ess(ck[1] + 1);
+      int64_t got = 0;
+      check(smc_get_resample_log(eng[k], pos.data(), ess.data(), ck[1], &got));
+      ofstream f(out.resample_name.c_str(), ios::out | ios::app | ios::binary);
+      for (int64_t q = 0; q < got; q++) f << (long long)(pos[q] + (C > 1 ? chunk_start[k] - 1 : 0)) << "\t" << ess[q] << endl;
+    }
   }
+  clog << "Got to end of sequence; resampled " << counters[1] << " times" << endl;
   clog << " Inference step completed." << endl;
 
   Tallies T;
@@ -285,13 +310,22 @@ int main(int argc, char* argv[]) {
     clog << endl;
     if (P.seg_file.empty()) throw invalid_argument("a .seg file is required (-seg); the empty-file mode is not supported");
     int max_seg_len = (int)(2.0 / (P.recombination_rate * 4 * P.N0));       // pfparam.cpp:364
-    host::SegRows rows = host::read_seg(P.seg_file, P.nsam, P.loci_length, (long long)P.start_position, max_seg_len);
+    // -chunks C (extension): C equal windows of the locus, as smc2 would hand them to C processes via -startpos
+    vector<host::SegRows> chunks;
+    vector<double> chunk_start;
+    const double chunk_len = P.chunks > 1 ? floor(P.loci_length / P.chunks) : P.loci_length;
+    if (chunk_len < 2) throw invalid_argument("Out of range: -chunks (windows shorter than two bases)");
+    for (int c = 0; c < P.chunks; c++) {
+      double s0 = P.start_position + c * chunk_len;
+      chunk_start.push_back(s0);
+      chunks.push_back(host::read_seg(P.seg_file, P.nsam, chunk_len, (long long)s0, max_seg_len));
+    }
     int device = 0;
     if (const char* d = getenv("SMCSMC_DEVICE")) device = atoi(d);
     out.header();
     for (int i = 0; i <= P.EM_steps; i++) {
       clog << "EM step " << i << endl;
-      pfARG_core(P, rows, out, i, device);
+      pfARG_core(P, chunks, chunk_start, chunk_len, out, i, device);
       clog << "End of EM step " << i << endl;
       auto dur = chrono::duration_cast<chrono::seconds>(chrono::system_clock::now() - start);
       clog << "Elapsed time: " << setprecision(3) << (double)dur.count() << endl;

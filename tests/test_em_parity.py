@@ -156,3 +156,31 @@ def test_calibration_matches_reference_survival_distances():
     ratio = med[7:] / np.array(ref[7:])
     assert np.all(ratio > 0.65) and np.all(ratio < 1.05), ratio
     assert med[0] == pytest.approx(ref[0], rel=0.35)            # epoch 0: few nodes are that young
+
+
+def test_chunks_extension_adds_up(tmp_path):
+    """-chunks C (extension of the drop-in driver): C windows of the locus swept concurrently in one process; the
+    summed tallies must agree with the single-window sweep up to the start-up effect of each window (every window
+    begins from the prior) and the .out layout must not change"""
+    ref = json.load(open(REF))
+    base = ref["base"]
+    outs = {}
+    for C in (1, 4):
+        out = str(tmp_path / ("c%d" % C))
+        cmd = [BIN] + base.format(extra="-EM 0", seed=5, seg=SEG, out=out).split() + (["-chunks", str(C)] if C > 1 else [])
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[C] = parse_out(out + ".out")[1]
+        if C > 1:
+            assert "4 chunks" in r.stdout
+    assert [(x["Type"], x["Epoch"]) for x in outs[1]] == [(x["Type"], x["Epoch"]) for x in outs[4]]
+    for a, b in zip(outs[1], outs[4]):
+        if a["Type"] == "Coal" and a["Epoch"] != "0":
+            assert float(b["Opp"]) == pytest.approx(float(a["Opp"]), rel=0.15), (a, b)
+        if a["Type"] == "Recomb":
+            assert float(b["Opp"]) == pytest.approx(float(a["Opp"]), rel=0.05), (a, b)
+            assert float(b["Count"]) == pytest.approx(float(a["Count"]), rel=0.15), (a, b)
+        if a["Type"] == "LogL":
+            assert float(b["Count"]) == pytest.approx(float(a["Count"]), rel=0.02), (a, b)
+    r = subprocess.run([BIN, "-Np", "10", "-t", "10", "-r", "10", "1000", "-chunks", "0", "-seg", SEG], capture_output=True, text=True)
+    assert r.returncode == 1 and "Out of range: -chunks" in r.stderr
