@@ -132,7 +132,8 @@ struct Tallies {   // CountModel totals incl. the initial pseudo-counts (count.c
 
 // one EM iteration: pfARG_core (smcsmc.cpp:278-400)
 void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<double>& chunk_start, double chunk_len,
-                const Out& out, int em, int device) {
+                const Out& out, int em, const vector<int>& devices) {
+  const int device = devices[0];
   const int E = P.num_epochs(), n = (int)P.nsam;
   vector<double> t_start(E), inv2N(E), vb(E), lags(E);
   vector<uint8_t> mask(E);
@@ -184,7 +185,7 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     }
     smc_config c;
     memset(&c, 0, sizeof c);
-    c.n = n; c.N = (int32_t)P.N; c.E = E; c.device = device;
+    c.n = n; c.N = (int32_t)P.N; c.E = E; c.device = devices[k % devices.size()];   // chunks round-robin over the GPUs
     c.seed = P.seed + (uint64_t)em * 0x9E3779B97F4A7C15ull;
     c.chunk = (uint32_t)(((long long)chunk_start[k]) & 0xFFFFFF);
     c.mu = P.mutation_rate; c.rho = P.recombination_rate; c.seqlen = chunk_len; c.start_pos = 0.0;
@@ -320,12 +321,20 @@ int main(int argc, char* argv[]) {
       chunk_start.push_back(s0);
       chunks.push_back(host::read_seg(P.seg_file, P.nsam, chunk_len, (long long)s0, max_seg_len));
     }
-    int device = 0;
-    if (const char* d = getenv("SMCSMC_DEVICE")) device = atoi(d);
+    // SMCSMC_DEVICE=3 selects one GPU; SMCSMC_DEVICES=0,1,2,3 spreads the chunks of -chunks over several
+    vector<int> devices;
+    if (const char* d = getenv("SMCSMC_DEVICES")) {
+      string list(d), item;
+      for (size_t q = 0; q <= list.size(); q++) {
+        if (q == list.size() || list[q] == ',') { if (!item.empty()) devices.push_back(atoi(item.c_str())); item.clear(); }
+        else item += list[q];
+      }
+    }
+    if (devices.empty()) devices.push_back(getenv("SMCSMC_DEVICE") ? atoi(getenv("SMCSMC_DEVICE")) : 0);
     out.header();
     for (int i = 0; i <= P.EM_steps; i++) {
       clog << "EM step " << i << endl;
-      pfARG_core(P, chunks, chunk_start, chunk_len, out, i, device);
+      pfARG_core(P, chunks, chunk_start, chunk_len, out, i, devices);
       clog << "End of EM step " << i << endl;
       auto dur = chrono::duration_cast<chrono::seconds>(chrono::system_clock::now() - start);
       clog << "Elapsed time: " << setprecision(3) << (double)dur.count() << endl;
