@@ -87,39 +87,38 @@ struct ModelDev {
   unsigned char rec_mask[64];
 };
 
-// Per-thread view of the particle's tree in shared memory.
+// Per-thread view of the particle's tree in shared memory.  Only what varies is stored: the heights of the n-1 internal
+// nodes (leaves sit at 0), the parent slots, likelihood scratch for the internal nodes, and one accumulator per epoch.
 template <int BS_>
 struct TreeViewT {
   static constexpr int BS = BS_;   // compile-time block size: column addressing v * BS + t folds into shifts
-  double* H;          // [nn][BS]
+  double* H;          // [n-1][BS] internal-node heights, addressed by node id (base shifted by -n rows)
   signed char* PAR;   // [nn][BS]
   double* L0;         // [n-1][BS] scratch for the internal nodes, addressed by node id (base shifted by -n rows)
   double* L1;         // [n-1][BS]
-  double* LEN;        // [E][BS]  local branch length inside each epoch
   double* ACC;        // [E][BS]  recombination opportunity summed over the current row
-  int t;
-  __device__ __forceinline__ double& h(int v) const { return H[v * BS + t]; }
+  int t, n;
+  __device__ __forceinline__ double h(int v) const { return v < n ? 0.0 : H[v * BS + t]; }
+  __device__ __forceinline__ double& hw(int v) const { return H[v * BS + t]; }        // internal nodes only
   __device__ __forceinline__ signed char& par(int v) const { return PAR[v * BS + t]; }
   __device__ __forceinline__ double& l0(int v) const { return L0[v * BS + t]; }
   __device__ __forceinline__ double& l1(int v) const { return L1[v * BS + t]; }
-  __device__ __forceinline__ double& len(int e) const { return LEN[e * BS + t]; }
 };
 
-// Carve a block's dynamic shared memory into the per-thread columns of a TreeView.  Leaves need no likelihood scratch
-// (their partials follow from the allele), so L0/L1 hold n-1 rows and are addressed through a base shifted by n rows.
+// Carve a block's dynamic shared memory into the per-thread columns of a TreeView.
 __host__ __device__ inline size_t tree_bytes_per_thread(int nn, int E) {
-  return (size_t)nn * 9 + (size_t)(nn - 1) * 8 + (size_t)E * 16;
+  return (size_t)(nn - 1) / 2 * 8 + (size_t)nn + (size_t)(nn - 1) * 8 + (size_t)E * 8;
 }
 template <int BS>
 __device__ __forceinline__ TreeViewT<BS> make_tree_view(unsigned char* smem, int n, int nn, int E, int t) {
   TreeViewT<BS> T;
-  T.t = t;
-  T.H = reinterpret_cast<double*>(smem);
-  double* l = T.H + (size_t)nn * BS;
-  T.L0 = l - (size_t)n * BS;
-  T.L1 = l + (size_t)(nn - n) * BS - (size_t)n * BS;
-  T.LEN = l + (size_t)2 * (nn - n) * BS;
-  T.ACC = T.LEN + (size_t)E * BS;
+  T.t = t; T.n = n;
+  double* base = reinterpret_cast<double*>(smem);
+  const size_t in = (size_t)(nn - n) * BS;      // one row per internal node
+  T.H = base - (size_t)n * BS;
+  T.L0 = base + in - (size_t)n * BS;
+  T.L1 = base + 2 * in - (size_t)n * BS;
+  T.ACC = base + 3 * in;
   T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)E * BS);
   return T;
 }
@@ -216,27 +215,30 @@ __device__ inline double site_likelihood(const ModelDev& m, const TV& T, const s
   return acc * norm;
 }
 
-// Local branch length inside each epoch = recombination opportunity per bp (record_recomb_extension,
-// particle.cpp:305-357: sum over time slices of #lineages * slice length).  Internal slots are sorted by height and all
-// leaves sit at height 0, so the slice between consecutive internal nodes carries n, n-1, ... lineages.
-template <class TV>
-__device__ inline void epoch_tree_length(const ModelDev& m, const TV& T) {
+// Recombination opportunity of the stretch [xa, xb): the local branch length inside each epoch times the stretch
+// (record_recomb_extension, particle.cpp:305-357: sum over time slices of #lineages * slice length).  Internal slots are
+// sorted by height and all leaves sit at 0, so the slice between consecutive internal nodes carries n, n-1, ...
+// lineages; one ascending sweep completes the epochs in order and hands each one to the sink as soon as it is known.
+template <class TV, class Sink>
+__device__ inline void record_recomb_opportunity(const ModelDev& m, const TV& T, Sink& sink, double xa, double xb,
+                                                 int max_rec_epoch) {
   const int n = m.n, E = m.E;
-  for (int e = 0; e < E; e++) T.len(e) = 0.0;
-  int e = 0;
-  double lo = 0.0;
-  int k = n;
+  int e = 0, k = n;
+  double lo = 0.0, len = 0.0;
   for (int j = n; j < m.nn; j++) {
     double hi = T.h(j);
     while (e + 1 < E && m.t_start[e + 1] < hi) {
       double b = m.t_start[e + 1];
-      if (b > lo) { T.len(e) += k * (b - lo); lo = b; }
+      if (b > lo) { len += k * (b - lo); lo = b; }
+      if (len > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, xa, xb, len);
+      len = 0.0;
       e++;
     }
-    if (hi > lo) T.len(e) += k * (hi - lo);
+    if (hi > lo) len += k * (hi - lo);
     lo = hi;
     k--;
   }
+  if (len > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, xa, xb, len);
 }
 
 __device__ inline int epoch_of(const ModelDev& m, double t) {
@@ -247,7 +249,7 @@ __device__ inline int epoch_of(const ModelDev& m, double t) {
 
 template <class TV>
 __device__ inline void swap_slots(const ModelDev& m, const TV& T, int a, int b) {
-  double th = T.h(a); T.h(a) = T.h(b); T.h(b) = th;
+  double th = T.h(a); T.hw(a) = T.h(b); T.hw(b) = th;
   signed char tp = T.par(a); T.par(a) = T.par(b); T.par(b) = tp;
   for (int v = 0; v < m.nn; v++) {
     int p = T.par(v);
@@ -335,7 +337,7 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
       T.par(root) = (signed char)Pn;
       T.par(Pn) = -1;
     }
-    T.h(Pn) = tc;
+    T.hw(Pn) = tc;
   } else {
     int idx = (int)(rng_uniform(r) * k);
     if (idx >= k) idx = k - 1;
@@ -347,12 +349,12 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
     if (Tg == b) {
       // back-coalescence into the stub: tree unchanged (SMC')
     } else if (Tg == S || Tg == Pn) {
-      T.h(Pn) = tc;
+      T.hw(Pn) = tc;
     } else {
       T.par(S) = T.par(Pn);
       T.par(Pn) = T.par(Tg);
       T.par(Tg) = (signed char)Pn;
-      T.h(Pn) = tc;
+      T.hw(Pn) = tc;
     }
   }
   int s = Pn;
@@ -390,14 +392,10 @@ __device__ inline int extend_row(const ModelDev& m, const TV& T, Rng& r, double 
     // code keeps the kernel's instruction footprint down
     tl = tree_length(m, T);
     L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
-    epoch_tree_length(m, T);
     if (moved) next_base = draw_next_base(m, tl, r, updated_to);
     double new_to = x1 < next_base ? x1 : next_base;
     logw += log(fastexp(-m.mu * L_obs * (new_to - updated_to)));     // particle.cpp:770
-    for (int e = 0; e < m.E; e++) {
-      double le = T.len(e);
-      if (le > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, updated_to, new_to, le);
-    }
+    record_recomb_opportunity(m, T, sink, updated_to, new_to, max_rec_epoch);
     updated_to = new_to;
     moved = false;
     // a stretch without a move ends the row: the loop condition fails and nothing tree-dependent is recomputed
@@ -418,7 +416,7 @@ template <class TV>
 __device__ inline void init_tree(const ModelDev& m, const TV& T, Rng& r) {
   const int n = m.n, nn = m.nn;
   signed char active[32];
-  for (int i = 0; i < n; i++) { active[i] = (signed char)i; T.h(i) = 0.0; }
+  for (int i = 0; i < n; i++) active[i] = (signed char)i;
   for (int v = 0; v < nn; v++) T.par(v) = -1;
   int k = n, e = 0, next_slot = n;
   double t = 0.0;
@@ -434,7 +432,7 @@ __device__ inline void init_tree(const ModelDev& m, const TV& T, Rng& r) {
       int i = 0;
       while (idx >= k - 1 - i) { idx -= k - 1 - i; i++; }
       int j = i + 1 + idx;
-      T.h(next_slot) = t;
+      T.hw(next_slot) = t;
       T.par(active[i]) = (signed char)next_slot;
       T.par(active[j]) = (signed char)next_slot;
       active[i] = (signed char)next_slot;

@@ -456,8 +456,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     {
       const double* __restrict__ sh_ = at_peer(src.height, dS);
       const signed char* __restrict__ sp_ = at_peer(src.parent, dS);
-      for (int v = 0; v < n; v++) T.h(v) = 0.0;
-      for (int v = n; v < nn; v++) T.h(v) = sh_[(size_t)(v - n) * P.N + a];
+      for (int v = n; v < nn; v++) T.hw(v) = sh_[(size_t)(v - n) * P.N + a];
       for (int v = 0; v < nn; v++) T.par(v) = sp_[(size_t)v * P.N + a];
     }
     // tallies: the open cells travel by value, closed buckets by reference (4-byte slot ids); a bucket that closes
@@ -755,7 +754,10 @@ __global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long co
   TreeViewT<BS> T = make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= count) return;
-  for (int v = 0; v < nn; v++) { T.h(v) = height[i * nn + v]; T.par(v) = (signed char)parent[i * nn + v]; }
+  for (int v = 0; v < nn; v++) {      // leaves sit at height 0 (checked on the host)
+    if (v >= n) T.hw(v) = height[i * nn + v];
+    T.par(v) = (signed char)parent[i * nn + v];
+  }
   signed char data[32];
   for (int k = 0; k < n; k++) data[k] = alleles[i * n + k];
   if (what == 0) {
@@ -1616,6 +1618,9 @@ int tree_fn(int device, int n, int64_t count, const int32_t* parent, const doubl
   double t0 = 0.0, inv = 1.0;
   if ((rc = fill_model(m, n, 1, mu, 1.0, 1.0, aa, &t0, &inv, nullptr, nullptr))) return rc;
   const int nn = 2 * n - 1, BS = 64;
+  for (int64_t i = 0; i < count; i++)
+    for (int v = 0; v < n; v++)
+      if (height[i * nn + v] != 0.0) return fail(SMC_ERR_ARG, "leaves must sit at height 0");
   DevBuf dp, dh, da, d0, d1;
   if ((rc = dp.alloc(count * nn * sizeof(int))) || (rc = dh.alloc(count * nn * sizeof(double))) ||
       (rc = da.alloc(count * n)) || (rc = d0.alloc(count * sizeof(double))) || (rc = d1.alloc(count * sizeof(double))))
