@@ -29,6 +29,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <type_traits>
 #include <vector>
@@ -915,6 +917,7 @@ struct smc_engine {
   double kernel_ms = 0.0;
   long long launches = 0;
   std::vector<void*> allocs;
+  std::vector<size_t> alloc_bytes;
   bool rows_ready = false, inited = false, finished = false;
   long long swept = 0;
   std::vector<int> first_pending_h;     // per epoch: number of buckets the regular schedule consumes
@@ -963,13 +966,48 @@ int nccl_load() {
 
 namespace {
 
+// Device blocks of destroyed engines are kept for the next engine of the same shape (every EM iteration builds new
+// engines with identical sizes; cudaMalloc / cudaFree of the multi-MB slabs cost up to hundreds of ms and synchronise the
+// device).  Bounded: beyond POOL_CAP bytes per device blocks are really freed.  Slabs peers have mapped are not pooled.
+struct BlockPool {
+  std::mutex mu;
+  std::multimap<std::pair<int, size_t>, void*> free_blocks;   // (device, bytes) -> block
+  std::map<int, size_t> held;
+  static constexpr size_t POOL_CAP = (size_t)16 << 30;
+  void* take(int device, size_t bytes) {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = free_blocks.find({device, bytes});
+    if (it == free_blocks.end()) return nullptr;
+    void* p = it->second;
+    free_blocks.erase(it);
+    held[device] -= bytes;
+    return p;
+  }
+  bool give(int device, size_t bytes, void* p) {
+    std::lock_guard<std::mutex> g(mu);
+    if (held[device] + bytes > POOL_CAP) return false;
+    free_blocks.insert({{device, bytes}, p});
+    held[device] += bytes;
+    return true;
+  }
+};
+BlockPool g_pool;
+
+int raw_alloc(smc_engine* e, void** q, size_t bytes) {
+  *q = g_pool.take(e->cfg.device, bytes);
+  if (!*q) CUDA_TRY(cudaMalloc(q, bytes));
+  e->allocs.push_back(*q);
+  e->alloc_bytes.push_back(bytes);
+  return 0;
+}
+
 template <class Tp>
 int dev_alloc(smc_engine* e, Tp** p, size_t count, bool zero = true) {
   void* q = nullptr;
   size_t bytes = std::max<size_t>(count, 1) * sizeof(Tp);
-  CUDA_TRY(cudaMalloc(&q, bytes));
+  int rc_ = raw_alloc(e, &q, bytes);
+  if (rc_) return rc_;
   if (zero) CUDA_TRY(cudaMemsetAsync(q, 0, bytes, e->stream));
-  e->allocs.push_back(q);
   *p = (Tp*)q;
   return 0;
 }
@@ -1097,10 +1135,8 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
                  s_b1 = up(((size_t)P.nblocks + 1) * 8), s_b = up((size_t)P.nblocks * 8);
     const size_t per = s_h + s_p + s_d + s_d + s_b1 + s_b;
     void* slab = nullptr;
-    ce = cudaMalloc(&slab, 2 * per);
-    if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "state slab: " + msg); }
+    if ((rc = raw_alloc(e, &slab, 2 * per))) { smc_destroy(e); return rc; }
     cudaMemsetAsync(slab, 0, 2 * per, e->stream);
-    e->allocs.push_back(slab);
     e->state_slab = slab;
     char* q = (char*)slab;
     for (int b = 0; b < 2; b++) {
@@ -1142,7 +1178,9 @@ void smc_destroy(smc_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (void* p : e->peer_maps) cudaIpcCloseMemHandle(p);
   if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
-  for (void* p : e->allocs) cudaFree(p);
+  const bool shared = e->comm != nullptr;        // peers hold IPC mappings of this engine's slabs: really free them
+  for (size_t k = 0; k < e->allocs.size(); k++)
+    if (shared || !g_pool.give(e->cfg.device, e->alloc_bytes[k], e->allocs[k])) cudaFree(e->allocs[k]);
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
