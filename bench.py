@@ -388,7 +388,7 @@ def main():
     ap.add_argument("--particles", type=int, default=10000)
     ap.add_argument("--len-mb", type=float, default=100.0)
     ap.add_argument("--chunks", type=int, default=16, help="independent chunks swept concurrently (smc2 -chunks)")
-    ap.add_argument("--rows-per-turn", type=int, default=4)
+    ap.add_argument("--rows-per-turn", type=int, default=1)
     ap.add_argument("--ess", type=float, default=0.5, help="-ESS resampling threshold fraction (reference default 0.5)")
     ap.add_argument("--cpu-particles", type=int, default=1000)
     ap.add_argument("--cpu-chunk-mb", type=float, default=2.0)

@@ -206,7 +206,7 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     }
   } else {
     cout << " Particle filtering " << C << " chunks (" << Rtot << " segments) concurrently." << endl;
-    check(smc_sweep_many(eng.data(), (int32_t)C, 4));
+    check(smc_sweep_many(eng.data(), (int32_t)C, 1));
   }
   cout << "\r Particle filtering step 100% completed." << endl;
   vector<double> t(6 * E, 0.0);
