@@ -226,6 +226,39 @@ def parse_out(path):
     return rows
 
 
+# BASELINE.json configs[0] at full size: 4 haplotypes x 10 Mb simulated under a constant size, inferred with 8 log-spaced
+# epochs from all-ones sizes, 1000 particles, 3 EM iterations (4 sweeps), seeds 1..10; recombination excluded from the
+# EM for the reason given above
+C0_BASE = ("-nsam 4 -Np 1000 -N0 10000 -t 10000 -r 4000 10000000 -eN 0 1 -eN 0.01 1 -eN 0.02 1 -eN 0.04 1 -eN 0.08 1 "
+           "-eN 0.16 1 -eN 0.32 1 -eN 0.64 1 -xr 0-7 -EM 3 -seed {seed} -seg {seg} -o {out}")
+
+
+def golden_configs0(seeds=range(1, 11)):
+    """reference ensemble for tests/test_em_parity.py::test_configs0_full_size (about 5 core-minutes per seed)"""
+    import gzip
+    import json
+    import shutil
+    import subprocess
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+    segz = os.path.join(os.path.dirname(HERE), "data", "const_n4_10Mb_seed11.seg.gz")
+    binp = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref", "smcsmc")
+    out = {"base": C0_BASE, "seeds": list(seeds)}
+    with tempfile.TemporaryDirectory() as tmp:
+        seg = os.path.join(tmp, "c0.seg")
+        with gzip.open(segz, "rb") as f, open(seg, "wb") as g:
+            shutil.copyfileobj(f, g)
+
+        def run(seed):
+            o = os.path.join(tmp, "s%d" % seed)
+            subprocess.run([binp] + C0_BASE.format(seed=seed, seg=seg, out=o).split(), check=True,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            return parse_out(o + ".out")
+        with ThreadPoolExecutor(8) as ex:
+            out["runs"] = list(ex.map(run, seeds))
+    json.dump(out, open(os.path.join(HERE, "configs0_reference.json"), "w"))
+
+
 def golden_em(seeds=range(1, 13)):
     """End-to-end reference runs (the unmodified smcsmc binary, oracle/_ref/smcsmc) on tests/data/const_n4_2Mb_seed7.seg:
     12 seeds per command variant; stores every .out row per seed (tests/test_em_parity.py compares the B200 driver's

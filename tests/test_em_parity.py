@@ -69,7 +69,7 @@ def test_out_file_format(runs):
     assert "Lags set to:" in r.stderr and "survival distance" in r.stderr and "resampled" in r.stderr
 
 
-def _compare(ref_runs, mine_rows, skip=()):
+def _compare(ref_runs, mine_rows, skip=(), small=0.0):
     nrows = len(ref_runs[0])
     report = []
     for k in range(nrows):
@@ -89,7 +89,9 @@ def _compare(ref_runs, mine_rows, skip=()):
     print(msg)
     for it, ep, typ, col, ma, mb, z, rel in report:
         tol = 0.25 if (typ == "Coal" and ep == "0") else 0.10      # epoch 0 holds ~25 events per run
-        assert abs(z) < 4.5 and abs(rel) < tol, msg
+        assert abs(z) < 4.5, msg
+        if not (col == "Count" and abs(ma) < small):               # a handful of events per run: the z test is the test
+            assert abs(rel) < tol, msg
     return report
 
 
@@ -184,3 +186,37 @@ def test_chunks_extension_adds_up(tmp_path):
             assert float(b["Count"]) == pytest.approx(float(a["Count"]), rel=0.02), (a, b)
     r = subprocess.run([BIN, "-Np", "10", "-t", "10", "-r", "10", "1000", "-chunks", "0", "-seg", SEG], capture_output=True, text=True)
     assert r.returncode == 1 and "Out of range: -chunks" in r.stderr
+
+
+def test_configs0_full_size(tmp_path):
+    """BASELINE.json configs[0] at full size -- 4 haplotypes x 10 Mb (18.6 k rows), 1000 particles, 8 inference epochs,
+    3 EM iterations, seeds 1..10 -- against the unmodified reference binary's ensemble on the same .seg and command
+    lines (tests/golden/configs0_reference.json, make_golden.py::golden_configs0): every per-epoch coalescent
+    opportunity / count and the log-likelihood of every iteration within Monte-Carlo error, and the final Ne estimates
+    of both programs around the simulated truth."""
+    import gzip
+    import shutil
+    ref = json.load(open(os.path.join(ROOT, "tests", "golden", "configs0_reference.json")))
+    seg = str(tmp_path / "c0.seg")
+    with gzip.open(os.path.join(ROOT, "tests", "data", "const_n4_10Mb_seed11.seg.gz"), "rb") as f, open(seg, "wb") as g:
+        shutil.copyfileobj(f, g)
+    procs = []
+    for seed in ref["seeds"]:          # the ten runs share the GPU (time-sliced); launch them together
+        out = str(tmp_path / ("s%d" % seed))
+        cmd = [BIN] + ref["base"].format(seed=seed, seg=seg, out=out).split()
+        procs.append((out, subprocess.Popen(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)))
+    mine = []
+    for out, p in procs:
+        err = p.communicate()[1]
+        assert p.returncode == 0, err[-2000:]
+        mine.append(parse_out(out + ".out")[1])
+    _compare(ref["runs"], mine, skip={("Recomb", "Opp"), ("Recomb", "Count")}, small=30.0)
+    ref0 = ref["runs"][0]
+    for k in range(len(ref0)):
+        # epochs 0-2 (< 1600 generations) see a handful of coalescences in 10 Mb of 4 haplotypes: both programs
+        # overestimate there (reference: 5e8, 3.2e4, 1.4e4); from epoch 3 on both sit on the simulated 10 000
+        if ref0[k]["Type"] == "Coal" and ref0[k]["Iter"] == "3" and int(ref0[k]["Epoch"]) >= 3:
+            ne = np.array([float(r[k]["Ne"]) for r in mine])
+            ne_ref = np.array([float(r[k]["Ne"]) for r in ref["runs"]])
+            assert 8500 < ne.mean() < 11500, (ref0[k]["Epoch"], ne.mean())
+            assert ne.mean() == pytest.approx(ne_ref.mean(), rel=0.05), (ref0[k]["Epoch"], ne.mean(), ne_ref.mean())
