@@ -1,0 +1,95 @@
+"""CPU tests of the drop-in `smcsmc` driver's host logic (smcsmc_b200/host): command-line parsing with the reference's
+messages and exit codes (pfparam.cpp:51-180, smcsmc.cpp:46-103), rejection of what the engine does not support yet,
+.seg validation (segdata.cpp:55-166), and the loud failure without a GPU (no CPU fallback)."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "smcsmc_b200", "bin", "smcsmc")
+SEG = os.path.join(ROOT, "tests", "data", "const_n4_2Mb_seed7.seg")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    if not os.path.exists(BIN):
+        import __graft_entry__ as g
+        g.build()
+    assert os.path.exists(BIN)
+
+
+def run(*args):
+    return subprocess.run([BIN] + list(args), capture_output=True, text=True)
+
+
+def test_help_and_version():
+    r = run("-v")
+    assert r.returncode == 0 and "smcsmc version" in r.stdout and "B200 engine" in r.stdout
+    for a in ((), ("-h",), ("-help",)):
+        r = run(*a)
+        assert r.returncode == 0
+        for flag in ("-Np", "-ESS", "-EM", "-seg", "-lag", "-calibrate_lag", "-xr", "-xc", "-cap", "-tmax", "-chunks"):
+            assert flag in r.stdout, flag
+
+
+@pytest.mark.parametrize("args, message", [
+    (["-Np", "10", "-t", "10"], "The option -r is required"),
+    (["-Np", "10", "-r", "10", "1000"], "The option -t is required"),
+    (["-Np"], "Not enough parameters when parsing options: -Np"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-ESS", "1.5"], "Out of range: -ESS"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-startpos", "0"], "Out of range: -startpos"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-calibrate_lag", "-1"], "Out of range: -calibrate_lag"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-chunks", "0"], "Out of range: -chunks"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-xr", "3-1"], "Out of range: -xr/-xc"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-xr", "5"], "epochs specified in -xr/-xc options out of range"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-bogus"], "unknown/unexpected argument: -bogus"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1", ], "Locus length must be at least two"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-eN", "0.1", "1", "-vb"], "-vb must occur before"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-nsam", "40"], "-nsam must be between 2 and 32"),
+])
+def test_parse_errors(args, message):
+    r = run(*args)
+    assert r.returncode == 1, (r.stdout, r.stderr)
+    assert r.stderr.strip().splitlines()[-1].startswith("Error: "), r.stderr
+    assert message in r.stderr
+
+
+@pytest.mark.parametrize("args", [
+    ["-I", "2", "2", "2"], ["-ej", "0.5", "2", "1"], ["-em", "0", "2", "1", "1"], ["-eM", "0", "1"], ["-eG", "0", "1"],
+    ["-guide", "x.gz"], ["-bias_heights", "400"], ["-apf", "1"], ["-dephase"], ["-arg"], ["-sr", "100", "2"],
+])
+def test_unsupported_features_are_rejected_not_ignored(args):
+    r = run("-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", "-seg", SEG, *args)
+    assert r.returncode == 1 and "is not supported by the B200 engine yet" in r.stderr, r.stderr
+
+
+def test_seg_validation(tmp_path):
+    base = ["-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "100000"]
+    r = run(*base, "-seg", "/nonexistent.seg")
+    assert r.returncode == 1 and "Invalid input file" in r.stderr
+    r = run(*base)
+    assert r.returncode == 1 and "a .seg file is required" in r.stderr
+    cases = {
+        "1\t10\tT\tF\t1\t01\n": "Number of variant site is wrong",
+        "1\t10\tT\tF\t1\t01x0\n": "Unknown character found in .seg file",
+        "1\t10\tT\tF\t1\t0.00\n": "inconsistent unphased heterozygous marks",
+        "1\t10\tT\tF\t1\t0100\n20\t5\tT\tF\t1\t0100\n": "Segments are not consecutive",
+        "1\t10\n": "Require 3 or 6 columns",
+        "1\t10\tT\tX\t1\t0100\n": "Expected T or F in .seg file column 3 and 4",
+        "200000\t10\tT\tF\t1\t0100\n": "No data found in file",
+    }
+    for k, (text, msg) in enumerate(cases.items()):
+        f = tmp_path / ("c%d.seg" % k)
+        f.write_text(text)
+        r = run(*base, "-seg", str(f))
+        assert r.returncode == 1 and msg in r.stderr, (text, r.stderr)
+
+
+def test_fails_loudly_without_a_gpu(tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    r = run("-nsam", "4", "-Np", "10", "-t", "2000", "-r", "800", "2000000", "-seg", SEG, "-o", str(tmp_path / "x"))
+    assert r.returncode == 1
+    assert "no CUDA device available" in r.stderr and "no CPU fallback" in r.stderr
