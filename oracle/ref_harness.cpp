@@ -115,6 +115,40 @@ extern "C" void ref_epoch_table(void* hv, double* t_start, double* inv2N /*[E][P
   m.resetTime();
 }
 
+// Structured models: populations, sample populations, migration rates and fixed-time moves per epoch.
+extern "C" int ref_num_pops(void* hv) { return (int)((RefHandle*)hv)->pf->model.population_number(); }
+extern "C" void ref_sample_pops(void* hv, int* pops) {
+  Model& m = ((RefHandle*)hv)->pf->model;
+  for (size_t i = 0; i < m.sample_size(); i++) pops[i] = (int)m.sample_population(i);
+}
+extern "C" void ref_mig_table(void* hv, double* mig /*[E][P][P]*/, double* single /*[E][P][P]*/) {
+  Model& m = ((RefHandle*)hv)->pf->model;
+  size_t E = m.change_times_.size(), P = m.population_number();
+  m.resetTime();
+  for (size_t e = 0; e < E; e++) {
+    if (e > 0) m.increaseTime();
+    for (size_t i = 0; i < P; i++)
+      for (size_t j = 0; j < P; j++) {
+        mig[(e * P + i) * P + j] = i == j ? 0.0 : m.migration_rate(i, j);
+        single[(e * P + i) * P + j] = i == j ? 0.0 : m.single_mig_pop(i, j);
+      }
+  }
+  m.resetTime();
+}
+// Prior trees of any model (migration nodes allowed): height of the local root and local tree length only.
+extern "C" int ref_prior_stats(void* hv, int count, double* tmrca, double* tree_len) {
+  RefHandle* h = (RefHandle*)hv;
+  try {
+    for (int t = 0; t < count; t++) {
+      Forest f(&h->pf->model, h->rng);
+      f.buildInitialTree(false);
+      tmrca[t] = f.local_root()->height();
+      tree_len[t] = f.getLocalTreeLength();
+    }
+    return 0;
+  } catch (std::exception& e) { g_err = e.what(); return 1; }
+}
+
 // Build the flat tree (n leaves = slots 0..n-1 with label slot+1, internal slots n..nn-1, parent[root] = -1) inside a
 // Forest using the reference's own node API, the way Forest::createExampleTree does (forest-debug.cc:57-121).
 static void build_tree(Forest* f, int n, int nn, const int* parent, const double* height) {

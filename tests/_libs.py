@@ -241,3 +241,43 @@ def ref_model(h, n, seqlen):
     inv = np.zeros(E)
     L.ref_epoch_table(h, P(t), P(inv))
     return make_model(n, list(t), list(inv), L.ref_mutation_rate(h), L.ref_recombination_rate(h), seqlen)
+
+
+# ---- structured-population oracle (oracle/smc_struct_oracle.h) -----------------------------------------------------
+ORC_MAXP, ORC_MAXMARKS = 4, 256
+
+
+class OrcSModel(ctypes.Structure):
+    _fields_ = [("base", OrcModel), ("P", ctypes.c_int),
+                ("inv2N", (ctypes.c_double * ORC_MAXP) * 64),
+                ("mig", ((ctypes.c_double * ORC_MAXP) * ORC_MAXP) * 64),
+                ("single_mig", ((ctypes.c_double * ORC_MAXP) * ORC_MAXP) * 64),
+                ("leaf_pop", ctypes.c_int * 64)]
+
+
+class OrcSParticle(ctypes.Structure):
+    _fields_ = [("tree", OrcParticle), ("pop", ctypes.c_int * 127), ("nmarks", ctypes.c_int),
+                ("mark_branch", ctypes.c_int * ORC_MAXMARKS), ("mark_time", ctypes.c_double * ORC_MAXMARKS),
+                ("mark_pop", ctypes.c_int * ORC_MAXMARKS), ("overflow", ctypes.c_int)]
+
+
+def make_smodel(n, t_start, inv2N, mig, single, leaf_pop, mu, rho, seqlen):
+    """inv2N [E][P], mig / single [E][P][P] (backward rates per generation / fixed-time move probabilities)"""
+    import numpy as np
+    inv2N, mig, single = np.asarray(inv2N), np.asarray(mig), np.asarray(single)
+    E, Pn = inv2N.shape
+    m = OrcSModel()
+    m.base.n, m.base.E, m.base.mu, m.base.rho, m.base.seqlen = n, E, mu, rho, seqlen
+    m.P = Pn
+    for e in range(E):
+        m.base.t_start[e] = t_start[e]
+        m.base.inv2N[e] = inv2N[e][0]
+        m.base.rec_mask[e] = 3
+        for i in range(Pn):
+            m.inv2N[e][i] = inv2N[e][i]
+            for j in range(Pn):
+                m.mig[e][i][j] = mig[e][i][j]
+                m.single_mig[e][i][j] = single[e][i][j]
+    for i in range(n):
+        m.leaf_pop[i] = int(leaf_pop[i])
+    return m

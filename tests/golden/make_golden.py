@@ -150,6 +150,51 @@ MOMENT_MODELS = {
 }
 
 
+STRUCT_MODELS = {
+    # name: (n, scrm flags) -- structured models (SURVEY.md 8d config 3 and simpler ones around it)
+    "island2": (4, "-I 2 2 2 1.0"),
+    "split2": (4, "-I 2 2 2 -ej 0.5 2 1"),
+    "config3": (8, "-I 2 4 4 -em 0 2 1 1 -ej 0.5 2 1"),
+    "island2_epochs": (6, "-I 2 3 3 0.5 -en 0.05 1 0.3 -en 0.05 2 2 -eM 0.2 3.0 -eN 0.6 1.5"),
+    "three": (6, "-I 3 2 2 2 -em 0.1 2 1 2.0 -ej 0.3 3 2 -ej 0.8 2 1"),
+}
+
+
+def golden_struct_moments(count=40000, walk=20000):
+    """the reference's prior trees and ARG walks under structured models: TMRCA, local tree length, recombination
+    heights, gaps -- mean / standard error (batch means for the autocorrelated walk) for tests/test_struct_oracle.py;
+    the model tables the oracle needs are stored alongside"""
+    R = _libs.ref()
+    out = {}
+    for name, (n, dem) in STRUCT_MODELS.items():
+        h = open_ref(n, dem, L=100000000)
+        E, Pn = R.ref_num_epochs(h), R.ref_num_pops(h)
+        ts, inv = np.zeros(E), np.zeros((E, Pn))
+        R.ref_epoch_table(h, P(ts), P(inv))
+        mig, single = np.zeros((E, Pn, Pn)), np.zeros((E, Pn, Pn))
+        R.ref_mig_table(h, P(mig), P(single))
+        pops = np.zeros(n, dtype=np.int32)
+        R.ref_sample_pops(h, P(pops))
+        tm, tl = np.zeros(count), np.zeros(count)
+        assert R.ref_prior_stats(h, count, P(tm), P(tl)) == 0, R.ref_last_error()
+        out[f"{name}_n"] = np.array(n); out[f"{name}_t_start"] = ts; out[f"{name}_inv2N"] = inv
+        out[f"{name}_mig"] = mig; out[f"{name}_single"] = single; out[f"{name}_leaf_pop"] = pops
+        out[f"{name}_prior"] = np.array([[x.mean(), x.std(ddof=1) / np.sqrt(count)] for x in (tm, tl, tm ** 2, tl ** 2)])
+        pos = np.zeros(walk); rech = np.zeros(walk); tmr = np.zeros(walk); tln = np.zeros(walk)
+        got = R.ref_arg_walk(h, walk, P(pos), P(rech), P(tmr), P(tln))
+        assert got > 1000, got
+        pos, rech, tmr, tln = pos[:got], rech[:got], tmr[:got], tln[:got]
+
+        def bm(x):
+            b = np.array_split(x, 50)
+            mm = np.array([c.mean() for c in b])
+            return [x.mean(), mm.std(ddof=1) / np.sqrt(len(mm))]
+        out[f"{name}_walk"] = np.array([bm(np.diff(pos)), bm(rech), bm(tmr[1:]), bm(tln[1:])])
+        out[f"{name}_rho"] = np.array(R.ref_recombination_rate(h)); out[f"{name}_mu"] = np.array(R.ref_mutation_rate(h))
+        R.ref_close(h)
+    np.savez_compressed(os.path.join(HERE, "struct_moments.npz"), **out)
+
+
 def golden_moments(count=40000, reps=40000):
     """Sample moments of the reference's stochastic pieces (its own mt19937_64 stream): prior trees
     (Forest::buildInitialTree), one SMC' move from a fixed start tree (Forest::sampleNextGenealogy) and the prior ARG
