@@ -21,6 +21,7 @@ extern "C" {
 
 #define SMC_MAX_HAPLOTYPES 32   /* n: local trees are flat arrays of 2n-1 nodes */
 #define SMC_MAX_EPOCHS 64
+#define SMC_MAX_POPULATIONS 4
 
 typedef enum {
   SMC_OK = 0,
@@ -63,6 +64,36 @@ int smc_create(const smc_config* cfg, smc_engine** out);   /* ParticleContainer 
 void smc_destroy(smc_engine* e);
 const char* smc_last_error(void);
 const char* smc_version(void);
+
+/* Structured populations (scrm -I / -ej / -em / -eM / -ema / -en; Model::population_number() > 1).  Call after
+ * smc_create and before smc_upload_rows; calling it again between sweeps (after smc_reset) replaces the rates, which is
+ * what the M-step does.  With it the engine runs the structured transition: the floating lineage coalesces with the
+ * contemporaries of its own population, migrates at rate sum_j mig[e][i][j], is moved by the fixed-time events at epoch
+ * starts, and above the old root both lineages float (forest.cc:496-756, 1100-1175).
+ *   npop                 2..SMC_MAX_POPULATIONS
+ *   inv2N[E][npop]       Model::inv_double_pop_size(pop, t) per epoch   (cfg.inv2N is ignored from here on)
+ *   mig[E][npop][npop]   Model::migration_rate(i, j): per-generation rate of a lineage in i moving to j, backwards in
+ *                        time; diagonal ignored; NULL = no migration
+ *   single_mig[E][npop][npop]  Model::single_mig_pop(i, j): probability that a lineage in i is moved to j at the START
+ *                        of the epoch (-ej t i j sets [i][j] = 1); NULL = none
+ *   leaf_pop[n]          Model::sample_population
+ *   max_marks            capacity of the per-particle pool of migration marks (<= 120), 0 = 2n + 8; a particle that
+ *                        needs more makes smc_get_lnZ fail
+ * Tallies then have 2Q rows, Q = 2 + 3*npop + npop^2 (smc_tally_rows): rows [0,Q) are sums of w * cell, rows [Q,2Q)
+ * sums of w^2 * cell (the reference's *_weight arrays, count.cpp:519-526), cells in the order
+ *   0 recombination count, 1 recombination opportunity, 2+3p coalescence count in p, 3+3p coalescence opportunity in p,
+ *   4+3p migration opportunity in p, 2+3*npop + p*npop + q migration count p -> q
+ * (CountModel::total_coal_count / total_coal_opportunity / total_mig_count / total_mig_opportunity, count.hpp).
+ * Not yet combinable with smc_shard_attach; -vb factors are not applied to structured moves. */
+int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const double* mig, const double* single_mig,
+                        const int32_t* leaf_pop, int32_t max_marks);
+/* rows of the array smc_get_tallies fills: 6 for a single population, 2Q after smc_set_populations */
+int smc_tally_rows(smc_engine* e);
+/* populations and migration marks of the current particles (tests): pop[N][2n-1] population at the bottom of the branch
+ * above each node, nmarks[N], and per particle max_marks entries (branch, time, population above the mark), unused
+ * entries -1 / 0 / -1.  Any pointer may be NULL. */
+int smc_get_population_state(smc_engine* e, int32_t* pop, int32_t* nmarks, int32_t* mark_branch, double* mark_time,
+                             int32_t* mark_pop);
 
 /* Upload the rows of the .seg chunk (Segment, segdata.cpp:55-223) and derive the lagged-tally schedule
  * (CountModel::extract_and_update_count's per-epoch update positions, count.cpp:363-385).

@@ -65,6 +65,13 @@ typedef struct {
   int overflow;
 } orc_events;
 
+/* A tally record in channel form (smc_tally_oracle.c: orc_channel_tallies): POINT (rect = 0) adds val at position x0,
+ * RECT (rect = 1) adds val per bp over [x0, x1). */
+typedef struct { int row, slot, epoch, chan, rect; double x0, x1, val; } orc_chan_event;
+void orc_channel_tallies(int E, int Q, const double* lags, int R, int N, const double* row_end, const double* weights,
+                         const int* anc, const double* w_final, double seq_end, const orc_chan_event* evs, long nev,
+                         double* out);
+
 /* ---- deterministic pieces ---- */
 double orc_fastexp(double x);                                               /* particle.cpp:30-40 */
 double orc_exp_digamma(double x);                                           /* particle.cpp:65-74 */

@@ -2,6 +2,7 @@
 #include "smc_struct_oracle.h"
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 /* ---- marks ------------------------------------------------------------------------------------------------- */
@@ -44,8 +45,8 @@ static double mig_total(const orc_smodel* m, int e, int i) {
 }
 
 /* a lineage's path of population changes while it floats */
-typedef struct { int n; double t[64]; int pop[64]; } spath;
-static void path_add(spath* a, double t, int pop) { if (a->n < 64) { a->t[a->n] = t; a->pop[a->n] = pop; a->n++; } }
+typedef struct { int n; double t[256]; int pop[256]; } spath;
+static void path_add(spath* a, double t, int pop) { if (a->n < 256) { a->t[a->n] = t; a->pop[a->n] = pop; a->n++; } }
 
 static void srecord(orc_srecords* recs, int who, int epoch, int pop, int weight, double dt, int event, int to_pop) {
   if (!recs || recs->count >= recs->cap) return;
@@ -350,4 +351,144 @@ int orc_sarg_walk(const orc_smodel* m, uint64_t seed, int count, double* pos, do
     if (marks) marks[i] = p.nmarks;
   }
   return count;
+}
+
+/* ---- the structured particle filter (test-side mirror of the engine with populations) --------------------------- */
+/* channel layout of the per-epoch tallies with P populations, Q = 2 + 3P + P*P:
+ *   0 recombination count, 1 recombination opportunity, 2+3p coalescence count in p, 3+3p coalescence opportunity in p,
+ *   4+3p migration opportunity in p, 2+3P + p*P + q migration count p -> q (backwards in time) */
+int orc_schannels(int P) { return 2 + 3 * P + P * P; }
+
+typedef struct { orc_chan_event* ev; long count, cap; } chan_buf;
+static void chan_emit(chan_buf* b, int row, int slot, int epoch, int chan, int rect, double x0, double x1, double val) {
+  if (b->count >= b->cap) {
+    b->cap = b->cap * 2 + 1024;
+    b->ev = (orc_chan_event*)realloc(b->ev, sizeof(orc_chan_event) * (size_t)b->cap);
+  }
+  orc_chan_event* e = &b->ev[b->count++];
+  e->row = row; e->slot = slot; e->epoch = epoch; e->chan = chan; e->rect = rect; e->x0 = x0; e->x1 = x1; e->val = val;
+}
+
+/* ForestState::extend_ARG for one row with populations: orc_extend_row with orc_ssmc_move as the transition and the
+ * records of particle.cpp:251-300 (coalescence AND migration opportunity of the floating lineages) as channel events.
+ * Returns the number of recombinations. */
+static int sextend_row(const orc_smodel* m, orc_sparticle* p, orc_rng* r, double x1, const int* data, int is_site,
+                       int ancestral_aware, int max_rec_epoch, chan_buf* out, int row, int slot) {
+  const orc_model* b = &m->base;
+  const int n = b->n, P = m->P;
+  orc_particle* t = &p->tree;
+  int nmiss = 0, nrec = 0;
+  for (int i = 0; i < n; i++) nmiss += data[i] == -1;
+  int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);
+  double L_obs = leaf_status == -1 ? 0.0
+               : leaf_status == 1 ? orc_tree_length(n, t->parent, t->height)
+                                  : orc_branch_length_with_data(n, t->parent, t->height, data);
+  double len_e[ORC_MAXE];
+  orc_srecord rbuf[512];
+  orc_epoch_tree_length(b, t->parent, t->height, len_e);
+  while (t->updated_to < x1) {
+    double new_to = x1 < t->next_base ? x1 : t->next_base;
+    t->logw += log(orc_fastexp(-b->mu * L_obs * (new_to - t->updated_to)));
+    for (int e = 0; e < b->E; e++)
+      if (len_e[e] > 0.0 && (b->rec_mask[e] & 1) && e <= max_rec_epoch)
+        chan_emit(out, row, slot, e, 1, 1, t->updated_to, new_to, len_e[e]);
+    t->updated_to = new_to;
+    if (t->updated_to < x1) {
+      t->cur_base = t->updated_to;
+      orc_srecords recs = { rbuf, 0, 512 };
+      double hh = 0.0;
+      orc_ssmc_move(m, p, r, &recs, &hh);
+      nrec++;
+      int e = sepoch_of(m, hh);
+      if ((b->rec_mask[e] & 1) && e <= max_rec_epoch) chan_emit(out, row, slot, e, 0, 0, t->cur_base, t->cur_base, 1.0);
+      for (int k = 0; k < recs.count; k++) {
+        const orc_srecord* q = &recs.rec[k];
+        if (!((b->rec_mask[q->epoch] & 2) && q->epoch <= max_rec_epoch)) continue;
+        const double x = t->cur_base;
+        if (q->event == 1) chan_emit(out, row, slot, q->epoch, 2 + 3 * q->pop, 0, x, x, 1.0);
+        if (q->weight > 0) chan_emit(out, row, slot, q->epoch, 3 + 3 * q->pop, 0, x, x, q->weight * q->dt);
+        chan_emit(out, row, slot, q->epoch, 4 + 3 * q->pop, 0, x, x, q->dt);
+        if (q->event == 2) chan_emit(out, row, slot, q->epoch, 2 + 3 * P + q->pop * P + q->to_pop, 0, x, x, 1.0);
+      }
+      if (leaf_status == 0) L_obs = orc_branch_length_with_data(n, t->parent, t->height, data);
+      if (leaf_status == 1) L_obs = orc_tree_length(n, t->parent, t->height);
+      orc_epoch_tree_length(b, t->parent, t->height, len_e);
+      sdraw_next_base(m, p, r, t->cur_base);
+    }
+    t->cur_base = t->updated_to;
+  }
+  if (is_site) t->logw += log(orc_site_likelihood(n, t->parent, t->height, data, b->mu, ancestral_aware, 0));
+  return nrec;
+}
+
+/* orc_particle_filter (smc_filter_oracle.c) with populations: same streams, same resampling, channel tallies
+ * out [2][Q][E].  Returns 0, 1 on zero total weight, 2 when a particle failed orc_scheck. */
+int orc_sparticle_filter(const orc_smodel* m, int N, uint64_t seed, uint32_t chunk, uint32_t slot_offset,
+                         double start_pos, double ess_fraction, int ancestral_aware, const double* lags, int R,
+                         const double* row_end, const int* data, const int* is_site, const int* max_rec,
+                         orc_sparticle* parts, double* lnZ_out, double* tallies, int* n_resample_out, int* last_anc,
+                         long* n_recomb_out) {
+  const int n = m->base.n, E = m->base.E, Q = orc_schannels(m->P);
+  orc_rng r;
+  orc_sparticle* next = (orc_sparticle*)malloc(sizeof(orc_sparticle) * (size_t)N);
+  double* weights = (double*)malloc(sizeof(double) * (size_t)R * N);
+  int* anc = (int*)malloc(sizeof(int) * (size_t)R * N);
+  double* lw = (double*)malloc(sizeof(double) * (size_t)N);
+  double* ps = (double*)malloc(sizeof(double) * (size_t)(N + 1));
+  int* counts = (int*)malloc(sizeof(int) * (size_t)N);
+  chan_buf evs = { 0, 0, 0 };
+  int rc = 0, n_resample = 0;
+  long n_recomb = 0;
+  double lnZ = 0.0;
+  for (int i = 0; i < N; i++) {
+    orc_rng_init(&r, seed, slot_offset + (uint32_t)i, 0, chunk, 1);
+    orc_sinit_particle(m, &parts[i], &r, start_pos);
+    parts[i].tree.logw = -log((double)N);
+    if (last_anc) last_anc[i] = -1;
+  }
+  for (int row = 0; row < R; row++) {
+    for (int i = 0; i < N; i++) {
+      orc_rng_init(&r, seed, slot_offset + (uint32_t)i, (uint32_t)row, chunk, 2);
+      n_recomb += sextend_row(m, &parts[i], &r, row_end[row], data + (size_t)row * n, is_site[row], ancestral_aware,
+                              max_rec ? max_rec[row] : E - 1, &evs, row, i);
+      if (orc_scheck(m, &parts[i])) { rc = 2; goto done; }
+    }
+    for (int i = 0; i < N; i++) lw[i] = parts[i].tree.logw;
+    double lse = orc_normalize_log(lw, N);
+    if (!isfinite(lse)) { rc = 1; goto done; }
+    lnZ += lse;
+    for (int i = 0; i < N; i++) { parts[i].tree.logw = lw[i]; weights[(size_t)row * N + i] = exp(lw[i]); }
+    double ess = orc_ess_partial_sums(weights + (size_t)row * N, N, ps);
+    anc[(size_t)row * N] = -1;
+    if (ess < N * ess_fraction - 1e-6) {
+      n_resample++;
+      if (row + 1 == R) break;
+      orc_rng_init(&r, seed, 0, (uint32_t)row, chunk, 3);
+      double u = orc_rng_uniform(&r);
+      orc_systematic_resampling(ps, N, N, u, counts);
+      int j = 0;
+      for (int i = 0; i < N; i++)
+        for (int k = 0; k < counts[i]; k++) {
+          next[j] = parts[i];
+          next[j].tree.logw = log(ps[N] / (double)N);
+          anc[(size_t)row * N + j] = i;
+          if (counts[i] > 1) {
+            orc_rng_init(&r, seed, slot_offset + (uint32_t)j, (uint32_t)row, chunk, 4);
+            sdraw_next_base(m, &next[j], &r, next[j].tree.cur_base);
+          }
+          j++;
+        }
+      memcpy(parts, next, sizeof(orc_sparticle) * (size_t)N);
+      if (last_anc) memcpy(last_anc, anc + (size_t)row * N, sizeof(int) * (size_t)N);
+    }
+  }
+  if (tallies)
+    orc_channel_tallies(E, Q, lags, R, N, row_end, weights, anc, weights + (size_t)(R - 1) * N, m->base.seqlen, evs.ev,
+                        evs.count, tallies);
+done:
+  *lnZ_out = lnZ;
+  if (n_resample_out) *n_resample_out = n_resample;
+  if (n_recomb_out) *n_recomb_out = n_recomb;
+  free(next); free(weights); free(anc); free(lw); free(ps); free(counts); free(evs.ev);
+  return rc;
 }

@@ -62,6 +62,14 @@ int orc_sprior_stats(const orc_smodel* m, uint64_t seed, int count, double* tmrc
 int orc_sarg_walk(const orc_smodel* m, uint64_t seed, int count, double* pos, double* rec_h, double* tmrca, double* tlen,
                   double* marks);
 
+/* the whole filter with populations (mirror of orc_particle_filter); tallies [2][Q][E], Q = orc_schannels(P) */
+int orc_schannels(int P);
+int orc_sparticle_filter(const orc_smodel* m, int N, uint64_t seed, uint32_t chunk, uint32_t slot_offset,
+                         double start_pos, double ess_fraction, int ancestral_aware, const double* lags, int R,
+                         const double* row_end, const int* data, const int* is_site, const int* max_rec,
+                         orc_sparticle* parts, double* lnZ_out, double* tallies, int* n_resample_out, int* last_anc,
+                         long* n_recomb_out);
+
 #ifdef __cplusplus
 }
 #endif

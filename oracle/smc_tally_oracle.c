@@ -41,18 +41,17 @@ int orc_max_epoch_to_record(int E, const double* lags, double distance_to_mutati
 
 typedef struct { int row, slot; orc_event ev; } orc_rec_event;
 
-/* out: [6][E] = coal_count, coal_opp, coal_weight(w^2), rec_count, rec_opp, rec_weight(w^2) -- WITHOUT the initial
- * pseudo-counts of count.cpp:161-193.
- * rows 0..R-1: row_end[r], weights[r*N+i] = normalised posterior weight of slot i when row r's update runs
- * (after normalize_probability, before resampling); anc[r*N+i] = slot (in row r's indexing) that slot i of row r+1 was
- * copied from, or anc[r*N] = -1 when no resampling followed row r.  w_final = weights for the end-of-data flush
- * (smcsmc.cpp:371-373), in the indexing after the last row's resampling. */
-void orc_lagged_tallies(int E, const double* lags, int R, int N, const double* row_end, const double* weights,
-                        const int* anc, const double* w_final, double seq_end, const orc_rec_event* evs, long nev,
-                        double* out) {
+/* The same rule for any number of tallied quantities ("channels", Q per epoch): a POINT record adds val to its channel
+ * when the update window [counted_to, update_to) passes its position x0; a RECT record adds val * |[x0,x1) n window|.
+ * out: [2][Q][E] = sum of w * amount, then sum of w^2 * amount (the latter feeds the ESS column for the opportunity
+ * channels).  orc_lagged_tallies below is this function with the single-population channel map; the structured
+ * filter (smc_struct_oracle.c) uses it with per-population coalescence / migration channels. */
+void orc_channel_tallies(int E, int Q, const double* lags, int R, int N, const double* row_end, const double* weights,
+                         const int* anc, const double* w_final, double seq_end, const orc_chan_event* evs, long nev,
+                         double* out) {
   double counted_to[ORC_MAXE], update_to[ORC_MAXE];
   for (int e = 0; e < E; e++) counted_to[e] = 0.0;
-  memset(out, 0, sizeof(double) * 6 * E);
+  memset(out, 0, sizeof(double) * 2 * (size_t)Q * E);
   double* W = (double*)malloc(sizeof(double) * (size_t)(R + 1) * N);   /* W[r][s] descendant weight */
   for (int step = 0; step <= R; step++) {
     int end_data = step == R;
@@ -71,34 +70,64 @@ void orc_lagged_tallies(int E, const double* lags, int R, int N, const double* r
         for (int i = 0; i < N; i++) dst[anc[(size_t)r * N + i]] += src[i];
       }
       for (long k = 0; k < nev; k++) {
-        const orc_rec_event* re = &evs[k];
-        int e = re->ev.epoch;
+        const orc_chan_event* re = &evs[k];
+        int e = re->epoch;
         if (e < first) continue;
         if (re->row > top) continue;
         if (!end_data && re->row > step) continue;
         double w = W[(size_t)re->row * N + re->slot];
         double xs = counted_to[e], xe = update_to[e];
-        if (re->ev.type == ORC_EV_COAL) {
-          double x = re->ev.x0;
-          if (xs <= x && x < xe) {            /* count.cpp:464,512: counted once, when update_to passes it */
-            out[0 * E + e] += w * re->ev.cnt;
-            out[1 * E + e] += w * re->ev.opp;
-            out[2 * E + e] += w * w * re->ev.opp;
-          }
-        } else if (re->ev.type == ORC_EV_RECOPP) {
-          double a = re->ev.x0 > xs ? re->ev.x0 : xs, b = re->ev.x1 < xe ? re->ev.x1 : xe;
-          if (b > a) {                        /* coalevent.hpp:224-226 clipped rectangle */
-            double opp = re->ev.opp * (b - a);
-            out[4 * E + e] += w * opp;
-            out[5 * E + e] += w * w * opp;
-          }
+        double amount;
+        if (re->rect) {
+          double a = re->x0 > xs ? re->x0 : xs, b = re->x1 < xe ? re->x1 : xe;
+          if (!(b > a)) continue;             /* coalevent.hpp:224-226 clipped rectangle */
+          amount = re->val * (b - a);
         } else {
-          double x = re->ev.x0;
-          if (xs <= x && x < xe) out[3 * E + e] += w * re->ev.cnt;   /* coalevent.hpp:231-235 */
+          if (!(xs <= re->x0 && re->x0 < xe)) continue;   /* count.cpp:464,512: counted once, when update_to passes it */
+          amount = re->val;
         }
+        out[((size_t)0 * Q + re->chan) * E + e] += w * amount;
+        out[((size_t)1 * Q + re->chan) * E + e] += w * w * amount;
       }
     }
     for (int e = 0; e < E; e++) counted_to[e] = update_to[e];
   }
   free(W);
+}
+
+/* out: [6][E] = coal_count, coal_opp, coal_weight(w^2), rec_count, rec_opp, rec_weight(w^2) -- WITHOUT the initial
+ * pseudo-counts of count.cpp:161-193.
+ * rows 0..R-1: row_end[r], weights[r*N+i] = normalised posterior weight of slot i when row r's update runs
+ * (after normalize_probability, before resampling); anc[r*N+i] = slot (in row r's indexing) that slot i of row r+1 was
+ * copied from, or anc[r*N] = -1 when no resampling followed row r.  w_final = weights for the end-of-data flush
+ * (smcsmc.cpp:371-373), in the indexing after the last row's resampling.
+ * Channels: 0 coalescence count, 1 coalescence opportunity, 2 recombination count, 3 recombination opportunity. */
+void orc_lagged_tallies(int E, const double* lags, int R, int N, const double* row_end, const double* weights,
+                        const int* anc, const double* w_final, double seq_end, const orc_rec_event* evs, long nev,
+                        double* out) {
+  orc_chan_event* g = (orc_chan_event*)malloc(sizeof(orc_chan_event) * (size_t)(2 * nev + 1));
+  long ng = 0;
+  for (long k = 0; k < nev; k++) {
+    const orc_rec_event* re = &evs[k];
+    orc_chan_event c = { re->row, re->slot, re->ev.epoch, 0, 0, re->ev.x0, re->ev.x1, 0.0 };
+    if (re->ev.type == ORC_EV_COAL) {
+      c.chan = 0; c.val = re->ev.cnt; g[ng++] = c;
+      c.chan = 1; c.val = re->ev.opp; g[ng++] = c;
+    } else if (re->ev.type == ORC_EV_RECOPP) {
+      c.chan = 3; c.rect = 1; c.val = re->ev.opp; g[ng++] = c;
+    } else {
+      c.chan = 2; c.val = re->ev.cnt; g[ng++] = c;
+    }
+  }
+  double* o = (double*)malloc(sizeof(double) * 2 * 4 * (size_t)E);
+  orc_channel_tallies(E, 4, lags, R, N, row_end, weights, anc, w_final, seq_end, g, ng, o);
+  for (int e = 0; e < E; e++) {
+    out[0 * E + e] = o[(0 * 4 + 0) * E + e];
+    out[1 * E + e] = o[(0 * 4 + 1) * E + e];
+    out[2 * E + e] = o[(1 * 4 + 1) * E + e];
+    out[3 * E + e] = o[(0 * 4 + 2) * E + e];
+    out[4 * E + e] = o[(0 * 4 + 3) * E + e];
+    out[5 * E + e] = o[(1 * 4 + 3) * E + e];
+  }
+  free(g); free(o);
 }

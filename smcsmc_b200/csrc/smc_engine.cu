@@ -36,6 +36,7 @@
 #include <vector>
 #include "../../include/smcsmc_b200.h"
 #include "smc_device.cuh"
+#include "smc_struct_device.cuh"
 
 using namespace smc;
 
@@ -65,6 +66,7 @@ struct Ctrl {
   long long cons_done;      // row whose leading tally consumption has already been done (by a materialise pass)
   unsigned int ticket;
   int err;
+  int sflags;               // SFLAG_* raised by any particle (structured populations)
   long long n_resample, n_recomb;
   int nseg;
   USeg seg[MAXSEG];
@@ -75,12 +77,19 @@ struct StateBuf {
   signed char* parent;  // [nn][N]
   double* logw;
   double* next_base;
-  double* open;         // [E][N][4]
+  double* open;         // [E][N][Q]   Q = 4 cells per epoch (2 + 3P + P*P with P > 1 populations)
   int* map;             // [E][B][N] global slot of the ancestor's frozen record
+  // structured populations only (smc_struct_device.cuh)
+  signed char* pop;     // [nn][N]
+  double* mtime;        // [K][N]
+  signed char* mbranch; // [K][N]
+  signed char* mpop;    // [K][N]
+  signed char* nmarks;  // [N]
 };
 
 struct Params {
   ModelDev m;
+  SModelDev sm;            // sm.P > 1: structured populations (the <.., true> kernels)
   int N, B, parity_scan, nblocks;
   uint64_t seed;
   uint32_t chunk, slot_offset;
@@ -97,7 +106,7 @@ struct Params {
   const int* kslot;        // [R+1][E] kstart modulo the ring depth B
   const int* kfirst;       // [R+1][E] oldest bucket still pending once the row's own hand-over is done
   const unsigned long long* closes;   // [R] bit e: the bucket open at the row's left end closes by the row end
-  double* frozen;          // [E][B][N][4]
+  double* frozen;          // [E][B][N][Q]
   const int* ub_off;       // [E+1]
   const double* ub;        // bucket upper bounds per epoch (last = +inf: the end-of-data bucket)
   const int* cons_off;     // [R+1]
@@ -110,7 +119,7 @@ struct Params {
   double* boff[2];         // [nblocks+1] exclusive prefix of normalised block totals
   double* bscale[2];
   double* psum;            // [N+1] parity-mode sequential partial sums
-  double* tallies;         // [6][E]
+  double* tallies;         // [6][E]; structured: [2][Q][E] (sum of w * cell, sum of w^2 * cell)
   int* anc;                // [N] ancestry of the last resampling (global particle index when sharded)
   double* rs_pos; double* rs_ess; long long rs_cap;
   // particle sharding over ranks: this engine owns particles [base, base + N) of Ntot.  What a
@@ -148,7 +157,7 @@ __device__ __forceinline__ void load_frozen(const Params& P, const int* map, int
 // Recombination opportunity (the dense record: every epoch, every stretch) is summed in shared memory over the row and
 // written once per epoch at the row end, unless a bucket bound of that epoch falls inside the row (then each stretch
 // is split at the bound and written directly).
-template <int BS>
+template <int BS, bool ST = false>
 struct RingSink {
   const Params* P;
   double* open;    // destination copy of the open cells
@@ -159,6 +168,9 @@ struct RingSink {
   double* ACC;     // [E][BS] shared
   int t;
   unsigned long long split;   // bit e: a bound of epoch e lies inside this row
+  // cells per epoch and where the recombination cells sit (single population: coal cnt, coal opp, rec cnt, rec opp)
+  __device__ __forceinline__ int Q() const { return ST ? P->sm.Q : 4; }
+  static constexpr int REC_CNT = ST ? 0 : 2, REC_OPP = ST ? 1 : 3;
   __device__ __forceinline__ int bucket(int e, double x) const {
     int k = ks[e];
     const double* ub = P->ub + P->ub_off[e];
@@ -166,10 +178,10 @@ struct RingSink {
     return k;
   }
   __device__ __forceinline__ double* cell(int e, int k, int q) const {
-    if (k == kn[e]) return open + ((size_t)e * P->N + i) * 4 + q;
+    if (k == kn[e]) return open + ((size_t)e * P->N + i) * Q() + q;
     int s = ksl[e] + (k - ks[e]);
     if (s >= P->B) s -= P->B;
-    return P->frozen + ((size_t)(e * P->B + s) * P->N + i) * 4 + q;
+    return P->frozen + ((size_t)(e * P->B + s) * P->N + i) * Q() + q;
   }
   __device__ void row_begin(double x1) {
     split = 0ull;
@@ -188,7 +200,7 @@ struct RingSink {
       for (int j = 0; j < 4; j++) {
         int e = e0 + j;
         a[j] = e < E ? ACC[e * BS + t] : 0.0;
-        cp[j] = cell(e < E ? e : 0, ks[e < E ? e : 0], 3);
+        cp[j] = cell(e < E ? e : 0, ks[e < E ? e : 0], REC_OPP);
         v[j] = a[j] != 0.0 ? *cp[j] : 0.0;
       }
 #pragma unroll
@@ -200,9 +212,21 @@ struct RingSink {
     if (cnt) *cell(e, k, 0) += 1.0;
     *cell(e, k, 1) += opp;
   }
+  // structured records (particle.cpp:251-300): coalescence opportunity / event of a floating lineage in population p,
+  // and its migration opportunity dt / event p -> to
+  __device__ void scoal(int e, int p, double x, int cnt, double opp) const {
+    int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
+    if (cnt) *cell(e, k, cell_coal_cnt(p)) += 1.0;
+    if (opp != 0.0) *cell(e, k, cell_coal_opp(p)) += opp;
+  }
+  __device__ void smig(int e, int p, double x, int to, double dt) const {
+    int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
+    *cell(e, k, cell_mig_opp(p)) += dt;
+    if (to >= 0) *cell(e, k, cell_mig_cnt(P->sm.P, p, to)) += 1.0;
+  }
   __device__ void rec_event(int e, double x) const {
     int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
-    *cell(e, k, 2) += 1.0;
+    *cell(e, k, REC_CNT) += 1.0;
   }
   __device__ void rec_opp(int e, double xa, double xb, double rate) const {
     if (!((split >> e) & 1ull)) { ACC[e * BS + t] += rate * (xb - xa); return; }
@@ -210,7 +234,7 @@ struct RingSink {
     const double* ub = P->ub + P->ub_off[e];
     while (xa < xb) {
       double bend = ub[k] < xb ? ub[k] : xb;
-      *cell(e, k, 3) += rate * (bend - xa);
+      *cell(e, k, REC_OPP) += rate * (bend - xa);
       xa = bend;
       k++;
     }
@@ -353,13 +377,33 @@ __device__ void commit_row(const Params& P, Ctrl* c, long long row, double new_l
 // ---------------------------------------------------------------------------------------------------------------
 // mode 0: one row; mode 1: materialise only (apply pending normalisation / resampling, no extension, no finalise)
 template <int BS>
+__device__ __forceinline__ TreeViewT<BS> tree_view_of(const Params& P, unsigned char* smem, int t, std::false_type) {
+  return make_tree_view<BS>(smem, P.m.n, P.m.nn, P.m.E, t);
+}
+template <int BS>
+__device__ __forceinline__ STreeViewT<BS> tree_view_of(const Params& P, unsigned char* smem, int t, std::true_type) {
+  return make_stree_view<BS>(smem, P.m.n, P.m.nn, P.m.E, t, &P.sm);
+}
+
+// pointer to the frozen record (Q doubles) of closed bucket (e, slot s) that belongs to particle i's ancestor
+__device__ __forceinline__ const double* frozen_record(const Params& P, const int* map, int e, int s, long long i, int Q) {
+  const size_t es = (size_t)(e * P.B + s);
+  const int m = map[es * P.N + i];
+  const double* f = P.frozen;
+  long long l = m;
+  if (P.world > 1) { const int r = m / P.N; l = m - r * P.N; f = at_peer(f, P.peer_tally[r]); }
+  return f + (es * P.N + l) * Q;
+}
+
+template <int BS, bool ST>
 __global__ void __launch_bounds__(BS)
 smc_row_kernel(const __grid_constant__ Params P, int mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int t = threadIdx.x;
   const ModelDev& m = P.m;
   const int n = m.n, nn = m.nn, E = m.E;
-  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, n, nn, E, t);
+  auto T = tree_view_of<BS>(P, smem_raw, t, std::integral_constant<bool, ST>());
+  const int QC = ST ? P.sm.Q : 4;      // tally cells per epoch
   __shared__ double red[3][4];
   __shared__ bool is_last;
 
@@ -384,28 +428,50 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   if (c1 > c0) {
     // at most one bucket per epoch falls due per row; the per-warp sums of all of them are staged in the (still
     // unused) tree area and handed to the global tallies with one pass
-    double* scr = reinterpret_cast<double*>(smem_raw);           // [c1 - c0][6][nwarp]
+    double* scr = reinterpret_cast<double*>(smem_raw);           // [c1 - c0][6][nwarp]  (structured: [..][2Q][nwarp])
     const double w = live ? exp(src.logw[i] - lse) : 0.0;
     const double w2 = w * w;
-    for (int q = c0; q < c1; q++) {
-      int2 ek = P.cons[q];
-      double v[6] = {0, 0, 0, 0, 0, 0};
-      if (live) {
-        double f[4];
-        load_frozen(P, src.map, ek.x, ek.y % P.B, i, f);
-        v[0] = w * f[0]; v[1] = w * f[1]; v[2] = w2 * f[1]; v[3] = w * f[2]; v[4] = w * f[3]; v[5] = w2 * f[3];
+    if constexpr (ST) {
+      // every cell is summed with w and with w^2: rows [0, QC) and [QC, 2Q) of the tallies
+      for (int q = c0; q < c1; q++) {
+        int2 ek = P.cons[q];
+        const double* fr = live ? frozen_record(P, src.map, ek.x, ek.y % P.B, i, QC) : nullptr;
+        for (int a = 0; a < QC; a++) {
+          const double f = live ? fr[a] : 0.0;
+          const double v0 = warp_sum(w * f), v1 = warp_sum(w2 * f);
+          if (lane == 0) {
+            scr[((q - c0) * 2 * QC + a) * nwarp + warp] = v0;
+            scr[((q - c0) * 2 * QC + QC + a) * nwarp + warp] = v1;
+          }
+        }
       }
+      __syncthreads();
+      for (int idx = t; idx < (c1 - c0) * 2 * QC; idx += BS) {
+        double s = 0;
+        for (int w_ = 0; w_ < nwarp; w_++) s += scr[idx * nwarp + w_];
+        if (s != 0.0) atomicAdd(P.tallies + (idx % (2 * QC)) * E + P.cons[c0 + idx / (2 * QC)].x, s);
+      }
+    } else {
+      for (int q = c0; q < c1; q++) {
+        int2 ek = P.cons[q];
+        double v[6] = {0, 0, 0, 0, 0, 0};
+        if (live) {
+          double f[4];
+          load_frozen(P, src.map, ek.x, ek.y % P.B, i, f);
+          v[0] = w * f[0]; v[1] = w * f[1]; v[2] = w2 * f[1]; v[3] = w * f[2]; v[4] = w * f[3]; v[5] = w2 * f[3];
+        }
 #pragma unroll
-      for (int a = 0; a < 6; a++) {
-        v[a] = warp_sum(v[a]);
-        if (lane == 0) scr[((q - c0) * 6 + a) * nwarp + warp] = v[a];
+        for (int a = 0; a < 6; a++) {
+          v[a] = warp_sum(v[a]);
+          if (lane == 0) scr[((q - c0) * 6 + a) * nwarp + warp] = v[a];
+        }
       }
-    }
-    __syncthreads();
-    for (int idx = t; idx < (c1 - c0) * 6; idx += BS) {
-      double s = 0;
-      for (int w_ = 0; w_ < nwarp; w_++) s += scr[idx * nwarp + w_];
-      if (s != 0.0) atomicAdd(P.tallies + (idx % 6) * E + P.cons[c0 + idx / 6].x, s);
+      __syncthreads();
+      for (int idx = t; idx < (c1 - c0) * 6; idx += BS) {
+        double s = 0;
+        for (int w_ = 0; w_ < nwarp; w_++) s += scr[idx * nwarp + w_];
+        if (s != 0.0) atomicAdd(P.tallies + (idx % 6) * E + P.cons[c0 + idx / 6].x, s);
+      }
     }
     __syncthreads();
   }
@@ -460,6 +526,21 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       const signed char* __restrict__ sp_ = at_peer(src.parent, dS);
       for (int v = n; v < nn; v++) T.hw(v) = sh_[(size_t)(v - n) * P.N + a];
       for (int v = 0; v < nn; v++) T.par(v) = sp_[(size_t)v * P.N + a];
+      if constexpr (ST) {
+        const signed char* __restrict__ spop = at_peer(src.pop, dS);
+        for (int v = 0; v < nn; v++) T.pop(v) = spop[(size_t)v * P.N + a];
+        const int nm = at_peer(src.nmarks, dS)[a];
+        T.nm() = (signed char)nm;
+        T.FLAG[t] = 0;
+        const double* __restrict__ smt = at_peer(src.mtime, dS);
+        const signed char* __restrict__ smb = at_peer(src.mbranch, dS);
+        const signed char* __restrict__ smp = at_peer(src.mpop, dS);
+        for (int k = 0; k < nm; k++) {
+          T.mt(k) = smt[(size_t)k * P.N + a];
+          T.mb(k) = smb[(size_t)k * P.N + a];
+          T.mp(k) = smp[(size_t)k * P.N + a];
+        }
+      }
     }
     // tallies: the open cells travel by value, closed buckets by reference (4-byte slot ids); a bucket that closes
     // during this row is frozen now -- its carried value moves to this particle's own frozen cell and the buckets born
@@ -476,7 +557,30 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       const size_t NN = (size_t)P.N;
       for (int e = 0; e < E; e++) {
         const bool closing = (closes >> e) & 1ull;
-        if (resampled || closing) {
+        if constexpr (ST) {
+          if (resampled || closing) {
+            const double2* o2 = reinterpret_cast<const double2*>(osrc + ((size_t)e * NN + a) * QC);
+            double2* d2 = reinterpret_cast<double2*>(dst.open + ((size_t)e * NN + i) * QC);
+            const int QC2 = QC >> 1;                       // QC = 2 + P(P+3) is even
+            const double2 zero = make_double2(0.0, 0.0);
+            if (closing) {
+              int s = ksl[e];
+              double2* f2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * QC);
+              for (int c2 = 0; c2 < QC2; c2++) { f2[c2] = o2[c2]; }
+              dst.map[(size_t)(e * P.B + s) * NN + i] = self;
+              const int kn = P.kstart[(row + 1) * E + e];
+              for (int k = ks[e] + 1; k < kn; k++) {
+                if (++s >= P.B) s = 0;
+                double2* z2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * QC);
+                for (int c2 = 0; c2 < QC2; c2++) z2[c2] = zero;
+                dst.map[(size_t)(e * P.B + s) * NN + i] = self;
+              }
+              for (int c2 = 0; c2 < QC2; c2++) d2[c2] = zero;
+            } else {
+              for (int c2 = 0; c2 < QC2; c2++) d2[c2] = o2[c2];
+            }
+          }
+        } else if (resampled || closing) {
           const double2* o2 = reinterpret_cast<const double2*>(osrc + ((size_t)e * NN + a) * 4);
           double2 o0 = o2[0], o1 = o2[1];
           double2* d2 = reinterpret_cast<double2*>(dst.open + ((size_t)e * NN + i) * 4);
@@ -522,7 +626,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
-    RingSink<BS> sink{&P, dst.open, (int)i, P.kstart + row * E, P.kslot + row * E, P.kstart + (row + 1) * E, T.ACC, t, 0ull};
+    RingSink<BS, ST> sink{&P, dst.open, (int)i, P.kstart + row * E, P.kslot + row * E, P.kstart + (row + 1) * E, T.ACC, t, 0ull};
     nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
   }
 
@@ -533,6 +637,17 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     if (resampled || mode == 0) {
       for (int v = n; v < nn; v++) dst.height[(size_t)(v - n) * P.N + i] = T.h(v);
       for (int v = 0; v < nn; v++) dst.parent[(size_t)v * P.N + i] = T.par(v);
+      if constexpr (ST) {
+        for (int v = 0; v < nn; v++) dst.pop[(size_t)v * P.N + i] = T.pop(v);
+        const int nm = T.nm();
+        dst.nmarks[i] = (signed char)nm;
+        for (int k = 0; k < nm; k++) {
+          dst.mtime[(size_t)k * P.N + i] = T.mt(k);
+          dst.mbranch[(size_t)k * P.N + i] = T.mb(k);
+          dst.mpop[(size_t)k * P.N + i] = T.mp(k);
+        }
+        if (T.FLAG[t]) atomicOr(&c->sflags, (int)T.FLAG[t]);
+      }
     }
   }
   if (mode != 0) return;
@@ -722,23 +837,66 @@ __global__ void __launch_bounds__(128) smc_flush_kernel(const __grid_constant__ 
   }
 }
 
+// structured populations: the end-of-data flush over all Q cells, with w and with w^2
+__global__ void __launch_bounds__(128) smc_flush_struct_kernel(const __grid_constant__ Params P, const int* first_pending) {
+  __shared__ double tal[2][4];
+  Ctrl* c = P.ctrl;
+  const int BS = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarp = BS >> 5;
+  const long long i = (long long)blockIdx.x * BS + t;
+  const bool live = i < P.N;
+  const StateBuf& src = P.buf[c->cur];
+  const int E = P.m.E, Q = P.sm.Q;
+  const double w = live ? exp(src.logw[i] - c->lse) : 0.0;
+  for (int e = 0; e < E; e++) {
+    const int nbk = P.ub_off[e + 1] - P.ub_off[e];
+    for (int a = 0; a < Q; a++) {
+      double f = 0.0;
+      if (live)
+        for (int k = first_pending[e]; k < nbk; k++)
+          f += k < nbk - 1 ? frozen_record(P, src.map, e, k % P.B, i, Q)[a] : src.open[((size_t)e * P.N + i) * Q + a];
+      const double v0 = warp_sum(w * f), v1 = warp_sum(w * w * f);
+      if (lane == 0) { tal[0][warp] = v0; tal[1][warp] = v1; }
+      __syncthreads();
+      if (t < 2) {
+        double s = 0;
+        for (int ww = 0; ww < nwarp; ww++) s += tal[t][ww];
+        if (s != 0.0) atomicAdd(P.tallies + ((size_t)t * Q + a) * E + e, s);
+      }
+      __syncthreads();
+    }
+  }
+}
+
 // prior trees + first recombination position + weight 1/N (particleContainer.cpp:33-65)
+template <bool ST>
 __global__ void __launch_bounds__(128) smc_init_kernel(const __grid_constant__ Params P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int BS = AUX_BS;
   const int t = threadIdx.x;
   const ModelDev& m = P.m;
   const int n = m.n, nn = m.nn;
-  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
+  auto T = tree_view_of<BS>(P, smem_raw, t, std::integral_constant<bool, ST>());
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= P.N) return;
   Rng r;
   rng_init(r, P.seed, P.slot_offset + (uint32_t)i, 0, P.chunk, RNG_INIT);
+  if constexpr (ST) T.FLAG[t] = 0;
   init_tree(m, T, r);
   double nb = draw_next_base(m, tree_length(m, T), r, P.start_pos);
   const StateBuf& d = P.buf[0];
   for (int v = n; v < nn; v++) d.height[(size_t)(v - n) * P.N + i] = T.h(v);
   for (int v = 0; v < nn; v++) d.parent[(size_t)v * P.N + i] = T.par(v);
+  if constexpr (ST) {
+    for (int v = 0; v < nn; v++) d.pop[(size_t)v * P.N + i] = T.pop(v);
+    const int nm = T.nm();
+    d.nmarks[i] = (signed char)nm;
+    for (int k = 0; k < nm; k++) {
+      d.mtime[(size_t)k * P.N + i] = T.mt(k);
+      d.mbranch[(size_t)k * P.N + i] = T.mb(k);
+      d.mpop[(size_t)k * P.N + i] = T.mp(k);
+    }
+    if (T.FLAG[t]) atomicOr(&P.ctrl->sflags, (int)T.FLAG[t]);
+  }
   d.logw[i] = -log((double)P.Ntot);
   d.next_base[i] = nb;
 }
@@ -925,6 +1083,8 @@ struct smc_engine {
   // particle sharding
   void* state_slab = nullptr;
   void* ring_slab = nullptr;            // tally slab: open[2], map[2], frozen
+  int Q = 4;                            // tally cells per epoch
+  int tally_rows = 6;                   // rows of the tallies array: 6, or 2Q with structured populations
   size_t open_bytes = 0;
   ncclComm_t comm = nullptr;
   std::vector<void*> peer_maps;         // cudaIpcOpenMemHandle results, closed in smc_destroy
@@ -1024,6 +1184,7 @@ int use_device(int device) {
 }
 
 size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * smc::tree_bytes_per_thread(nn, E) + 16; }
+size_t stree_smem(int nn, int E, int K, int BS) { return (size_t)BS * smc::stree_bytes_per_thread(nn, E, K) + 16; }
 
 int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, int aa, const double* t_start,
                const double* inv2N, const double* vb, const uint8_t* mask) {
@@ -1069,10 +1230,18 @@ int exchange_slab(smc_engine* e, void* slab, long long* delta) {
 
 int launch_row(smc_engine* e, int mode) {
   int nb = e->P.nblocks;
-  switch (e->BS) {
-    case 32: smc_row_kernel<32><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
-    case 64: smc_row_kernel<64><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
-    default: smc_row_kernel<128><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+  if (e->P.sm.P > 1) {
+    switch (e->BS) {
+      case 32: smc_row_kernel<32, true><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
+      case 64: smc_row_kernel<64, true><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+      default: smc_row_kernel<128, true><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+    }
+  } else {
+    switch (e->BS) {
+      case 32: smc_row_kernel<32, false><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
+      case 64: smc_row_kernel<64, false><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+      default: smc_row_kernel<128, false><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+    }
   }
   e->launches++;
   return 0;
@@ -1089,6 +1258,8 @@ int materialise(smc_engine* e) {
 }  // namespace
 
 extern "C" {
+
+static int read_ctrl(smc_engine* e, Ctrl* c);
 
 const char* smc_last_error(void) { return g_err.c_str(); }
 const char* smc_version(void) { return "smcsmc_b200 0.1 (sm_100a)"; }
@@ -1121,10 +1292,14 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   cudaEventCreate(&e->ev0); cudaEventCreate(&e->ev1);
   // opt in to the full 227 KB once (the attribute is per function, not per engine)
   if (e->smem > 230400) { smc_destroy(e); return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has"); }
-  ce = cudaFuncSetAttribute(smc_row_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  ce = cudaFuncSetAttribute(smc_row_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
   const size_t N = cfg->N;
   const int n = cfg->n, nn = 2 * n - 1;
@@ -1203,6 +1378,7 @@ int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t i
   if (world < 2 || world > SMC_MAX_RANKS || rank < 0 || rank >= world) return fail(SMC_ERR_ARG, "rank/world out of range (2..8 ranks)");
   if (e->rows_ready || e->inited) return fail(SMC_ERR_STATE, "attach the shard before uploading rows");
   if (e->P.world > 1) return fail(SMC_ERR_STATE, "engine is already sharded");
+  if (e->P.sm.P > 1) return fail(SMC_ERR_STATE, "structured populations cannot be combined with particle sharding yet");
   if (e->cfg.parity_scan) return fail(SMC_ERR_ARG, "parity_scan is a single-rank mode");
   if ((long long)e->cfg.N * world > 0x7fffffffLL) return fail(SMC_ERR_ARG, "more than 2^31 particles in total");
   int rc = nccl_load();
@@ -1220,6 +1396,117 @@ int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t i
   for (int b = 0; b < 2; b++)
     if ((rc = dev_alloc(e, &P.rank_off[b], world + 1)) || (rc = dev_alloc(e, &P.rank_fac[b], world))) return rc;
   return exchange_slab(e, e->state_slab, P.peer_state);
+}
+
+int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const double* mig, const double* single_mig,
+                        const int32_t* leaf_pop, int32_t max_marks) {
+  if (!e || !inv2N || !leaf_pop) return fail(SMC_ERR_ARG, "null argument");
+  if (npop < 2 || npop > SMC_MAX_POPULATIONS) return fail(SMC_ERR_ARG, "populations must be in 2..4");
+  Params& P = e->P;
+  if (P.world > 1) return fail(SMC_ERR_STATE, "structured populations cannot be combined with particle sharding yet");
+  const bool update = P.sm.P > 1;
+  if (update && P.sm.P != npop) return fail(SMC_ERR_STATE, "the number of populations cannot change");
+  if (!update && e->rows_ready) return fail(SMC_ERR_STATE, "set the populations before uploading rows");
+  if (e->inited && e->swept > 0) return fail(SMC_ERR_STATE, "populations cannot change during a sweep");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  const int E = e->cfg.E, n = e->cfg.n, nn = 2 * n - 1, Pp = npop;
+  std::vector<double> h_inv((size_t)E * Pp), h_mig((size_t)E * Pp * Pp, 0.0), h_tot((size_t)E * Pp, 0.0), h_single((size_t)E * Pp * Pp, 0.0);
+  std::vector<unsigned char> h_fixed(E, 0);
+  std::vector<signed char> h_leaf(n);
+  for (int ep = 0; ep < E; ep++)
+    for (int i = 0; i < Pp; i++) {
+      h_inv[(size_t)ep * Pp + i] = inv2N[(size_t)ep * Pp + i];
+      if (!(h_inv[(size_t)ep * Pp + i] > 0)) return fail(SMC_ERR_ARG, "inv2N must be positive");
+      double tot = 0.0, stot = 0.0;
+      for (int j = 0; j < Pp; j++) {
+        const size_t at = ((size_t)ep * Pp + i) * Pp + j;
+        double mr = (mig && j != i) ? mig[at] : 0.0;
+        double sm = single_mig ? single_mig[at] : 0.0;
+        if (!(mr >= 0)) return fail(SMC_ERR_ARG, "migration rates must be non-negative");
+        if (!(sm >= 0 && sm <= 1)) return fail(SMC_ERR_ARG, "single_mig entries are probabilities");
+        h_mig[at] = mr; h_single[at] = sm;
+        if (j != i) tot += mr;
+        stot += sm;
+        if (sm > 0) h_fixed[ep] = 1;
+      }
+      if (stot > 1.0 + 1e-12) return fail(SMC_ERR_ARG, "single_mig rows must sum to at most 1");
+      h_tot[(size_t)ep * Pp + i] = tot;
+    }
+  for (int i = 0; i < n; i++) {
+    if (leaf_pop[i] < 0 || leaf_pop[i] >= Pp) return fail(SMC_ERR_ARG, "leaf population out of range");
+    h_leaf[i] = (signed char)leaf_pop[i];
+  }
+  int rc;
+  if (!update) {
+    const int K = max_marks > 0 ? max_marks : 2 * n + 8;
+    if (K > 120) return fail(SMC_ERR_ARG, "max_marks must be at most 120");
+    const int Q = 2 + 3 * Pp + Pp * Pp;
+    size_t smem = stree_smem(nn, E, K, e->BS);
+    smem = std::max(smem, (size_t)E * 2 * Q * (e->BS / 32) * sizeof(double) + 16);   // hand-over staging of phase 0
+    if (smem > 230400 || stree_smem(nn, E, K, AUX_BS) > 230400)
+      return fail(SMC_ERR_ARG, "n, E and max_marks need more shared memory than one SM has (fewer particles per block: SMC_BLOCK=32)");
+    double *d_inv, *d_mig, *d_tot, *d_single; unsigned char* d_fixed; signed char* d_leaf;
+    if ((rc = dev_alloc(e, &d_inv, h_inv.size(), false)) || (rc = dev_alloc(e, &d_mig, h_mig.size(), false)) ||
+        (rc = dev_alloc(e, &d_tot, h_tot.size(), false)) || (rc = dev_alloc(e, &d_single, h_single.size(), false)) ||
+        (rc = dev_alloc(e, &d_fixed, (size_t)E, false)) || (rc = dev_alloc(e, &d_leaf, (size_t)n, false)))
+      return rc;
+    const size_t N = e->cfg.N;
+    for (int b = 0; b < 2; b++) {
+      if ((rc = dev_alloc(e, &P.buf[b].pop, (size_t)nn * N)) || (rc = dev_alloc(e, &P.buf[b].mtime, (size_t)K * N)) ||
+          (rc = dev_alloc(e, &P.buf[b].mbranch, (size_t)K * N)) || (rc = dev_alloc(e, &P.buf[b].mpop, (size_t)K * N)) ||
+          (rc = dev_alloc(e, &P.buf[b].nmarks, N)))
+        return rc;
+    }
+    if ((rc = dev_alloc(e, &P.tallies, 2 * (size_t)Q * E))) return rc;
+    P.sm.K = K; P.sm.Q = Q;
+    P.sm.inv2N = d_inv; P.sm.mig = d_mig; P.sm.migtot = d_tot; P.sm.single_mig = d_single; P.sm.fixed = d_fixed;
+    P.sm.leaf_pop = d_leaf;
+    e->Q = Q; e->tally_rows = 2 * Q; e->smem = smem;
+  }
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.inv2N, h_inv.data(), h_inv.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.mig, h_mig.data(), h_mig.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.migtot, h_tot.data(), h_tot.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.single_mig, h_single.data(), h_single.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.fixed, h_fixed.data(), h_fixed.size(), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.leaf_pop, h_leaf.data(), h_leaf.size(), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  P.sm.P = Pp;
+  return 0;
+}
+
+int smc_tally_rows(smc_engine* e) { return e ? e->tally_rows : 0; }
+
+int smc_get_population_state(smc_engine* e, int32_t* pop, int32_t* nmarks, int32_t* mark_branch, double* mark_time,
+                             int32_t* mark_pop) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  if (e->P.sm.P < 2) return fail(SMC_ERR_STATE, "the engine has a single population");
+  if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  if (!e->finished) { int rc = materialise(e); if (rc) return rc; }
+  Ctrl c;
+  int rc = read_ctrl(e, &c);
+  if (rc) return rc;
+  const size_t N = e->cfg.N;
+  const int nn = 2 * e->cfg.n - 1, K = e->P.sm.K;
+  const StateBuf& s = e->P.buf[c.cur];
+  std::vector<signed char> hp((size_t)nn * N), hn(N), hb((size_t)K * N), hq((size_t)K * N);
+  std::vector<double> ht((size_t)K * N);
+  CUDA_TRY(cudaMemcpy(hp.data(), s.pop, hp.size(), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(hn.data(), s.nmarks, hn.size(), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(hb.data(), s.mbranch, hb.size(), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(hq.data(), s.mpop, hq.size(), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(ht.data(), s.mtime, ht.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; i++) {
+    if (pop) for (int v = 0; v < nn; v++) pop[i * nn + v] = hp[(size_t)v * N + i];
+    if (nmarks) nmarks[i] = hn[i];
+    for (int k = 0; k < K; k++) {
+      const bool used = k < hn[i];
+      if (mark_branch) mark_branch[i * K + k] = used ? hb[(size_t)k * N + i] : -1;
+      if (mark_time) mark_time[i * K + k] = used ? ht[(size_t)k * N + i] : 0.0;
+      if (mark_pop) mark_pop[i * K + k] = used ? hq[(size_t)k * N + i] : -1;
+    }
+  }
+  return 0;
 }
 
 int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, const uint8_t* is_site,
@@ -1336,8 +1623,9 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
   {
     auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
     const size_t NN = (size_t)e->cfg.N;
-    const size_t s_open = up((size_t)E * NN * 4 * sizeof(double)), s_map = up((size_t)E * B * NN * sizeof(int)),
-                 s_frozen = up((size_t)E * B * NN * 4 * sizeof(double));
+    const size_t QQ = (size_t)e->Q;
+    const size_t s_open = up((size_t)E * NN * QQ * sizeof(double)), s_map = up((size_t)E * B * NN * sizeof(int)),
+                 s_frozen = up((size_t)E * B * NN * QQ * sizeof(double));
     char* slab = nullptr;
     if ((rc = dev_alloc(e, &slab, 2 * s_open + 2 * s_map + s_frozen))) return rc;
     e->ring_slab = slab;
@@ -1359,7 +1647,11 @@ int smc_init_particles(smc_engine* e) {
   if (!e) return fail(SMC_ERR_ARG, "null engine");
   if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows before initialising particles");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
-  smc_init_kernel<<<(unsigned)((e->cfg.N + AUX_BS - 1) / AUX_BS), AUX_BS, tree_smem(e->P.m.nn, e->P.m.E, AUX_BS), e->stream>>>(e->P);
+  const unsigned init_blocks = (unsigned)((e->cfg.N + AUX_BS - 1) / AUX_BS);
+  if (e->P.sm.P > 1)
+    smc_init_kernel<true><<<init_blocks, AUX_BS, stree_smem(e->P.m.nn, e->P.m.E, e->P.sm.K, AUX_BS), e->stream>>>(e->P);
+  else
+    smc_init_kernel<false><<<init_blocks, AUX_BS, tree_smem(e->P.m.nn, e->P.m.E, AUX_BS), e->stream>>>(e->P);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   e->inited = true;
@@ -1466,7 +1758,7 @@ int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_l
   P.seed = seed;
   // frozen records and maps are (re)initialised when their bucket is born; only the open cells start from zero
   for (int b = 0; b < 2; b++) CUDA_TRY(cudaMemsetAsync(P.buf[b].open, 0, e->open_bytes, e->stream));
-  CUDA_TRY(cudaMemsetAsync(P.tallies, 0, 6 * (size_t)E * sizeof(double), e->stream));
+  CUDA_TRY(cudaMemsetAsync(P.tallies, 0, (size_t)e->tally_rows * E * sizeof(double), e->stream));
   CUDA_TRY(cudaMemsetAsync(P.anc, 0xff, (size_t)P.N * sizeof(int), e->stream));
   Ctrl init;
   memset(&init, 0, sizeof(init));
@@ -1497,11 +1789,12 @@ int smc_finish(smc_engine* e) {
   }
   CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, fp.data(), fp.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   cudaEventRecord(e->ev0, e->stream);
-  smc_flush_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
+  if (e->P.sm.P > 1) smc_flush_struct_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
+  else smc_flush_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
   e->launches++;
   if (e->P.world > 1) {
     // the ranks' tallies and recombination counts add up (the ln normaliser and the resampling log are already global)
-    NCCL_TRY(g_nccl.AllReduce(e->P.tallies, e->P.tallies, 6 * (size_t)e->cfg.E, ncclDouble, ncclSum, e->comm, e->stream));
+    NCCL_TRY(g_nccl.AllReduce(e->P.tallies, e->P.tallies, (size_t)e->tally_rows * e->cfg.E, ncclDouble, ncclSum, e->comm, e->stream));
     NCCL_TRY(g_nccl.AllReduce(&e->P.ctrl->n_recomb, &e->P.ctrl->n_recomb, 1, ncclUint64, ncclSum, e->comm, e->stream));
   }
   cudaEventRecord(e->ev1, e->stream);
@@ -1518,7 +1811,7 @@ int smc_get_tallies(smc_engine* e, double* out) {
   if (!e || !out) return fail(SMC_ERR_ARG, "null argument");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
-  CUDA_TRY(cudaMemcpy(out, e->P.tallies, 6 * (size_t)e->cfg.E * sizeof(double), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(out, e->P.tallies, (size_t)e->tally_rows * e->cfg.E * sizeof(double), cudaMemcpyDeviceToHost));
   return 0;
 }
 
@@ -1535,6 +1828,8 @@ int smc_get_lnZ(smc_engine* e, double* lnZ) {
   int rc = read_ctrl(e, &c);
   if (rc) return rc;
   *lnZ = c.lnZ;
+  if (c.sflags & SFLAG_NOCOAL) return fail(SMC_ERR_NUMERIC, "Lines did not coalescence: the populations of the model never join and do not exchange migrants");
+  if (c.sflags & SFLAG_MARKS) return fail(SMC_ERR_NUMERIC, "a particle needed more migration marks than max_marks (smc_set_populations)");
   if (c.err) return fail(SMC_ERR_NUMERIC, "Zero or negative probabilities");
   return 0;
 }
@@ -1594,6 +1889,7 @@ int smc_set_particles(smc_engine* e, const int32_t* parent, const double* height
   if (!e || !parent || !height || !logw || !next_base) return fail(SMC_ERR_ARG, "null argument");
   if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows first");
   if (e->swept != 0) return fail(SMC_ERR_STATE, "set_particles only before the first row");
+  if (e->P.sm.P > 1) return fail(SMC_ERR_STATE, "set_particles is not available with structured populations");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   const size_t N = e->cfg.N;
   const int n = e->cfg.n, nn = 2 * n - 1;

@@ -26,8 +26,10 @@ def shard_unique_id():
 class ParticleFilter:
     def __init__(self, n, N, t_start, inv2N, mu, rho, seqlen, lags, seed=1, chunk=0, start_pos=0.0, ess_fraction=0.5,
                  ancestral_aware=False, parity_scan=False, vb_logfac=None, rec_mask=None, device=0, slot_offset=0,
-                 shard=None):
-        """N is the number of particles THIS engine holds.  shard = (rank, world, unique_id) splits a population of
+                 shard=None, populations=None):
+        """N is the number of particles THIS engine holds.  populations = dict(inv2N[E][P], mig[E][P][P] or None,
+        single_mig[E][P][P] or None, leaf_pop[n], max_marks=0) switches the structured transition on
+        (smc_set_populations; scrm -I / -ej / -em); the argument inv2N is then ignored.  shard = (rank, world, unique_id) splits a population of
         world * N particles over `world` engines, one per process and GPU (smc_shard_attach); unique_id comes from
         shard_unique_id() on rank 0 and is handed to the other ranks by the caller (smcsmc_b200.sharding)."""
         self.n, self.N, self.E = int(n), int(N), len(t_start)
@@ -46,6 +48,9 @@ class ParticleFilter:
         check(lib().smc_create(ctypes.byref(c), ctypes.byref(self._h)))
         self.R = 0
         self.shard = None
+        self.P, self.max_marks = 1, 0
+        if populations is not None:
+            self.set_populations(**populations)
         if shard is not None:
             rank, world, uid = shard
             uid = np.ascontiguousarray(np.frombuffer(bytes(uid), dtype=np.uint8))
@@ -63,6 +68,31 @@ class ParticleFilter:
             self.close()
         except Exception:
             pass
+
+    def set_populations(self, inv2N, leaf_pop, mig=None, single_mig=None, max_marks=0):
+        """Model with several populations; call again after reset() to replace the rates (M-step)"""
+        inv = _f64(inv2N)
+        E, P = inv.shape
+        assert E == self.E
+        m = None if mig is None else _f64(mig).reshape(E, P, P)
+        sm = None if single_mig is None else _f64(single_mig).reshape(E, P, P)
+        lp = np.ascontiguousarray(leaf_pop, dtype=np.int32)
+        assert lp.shape == (self.n,)
+        check(lib().smc_set_populations(self._h, P, _P(inv), None if m is None else _P(m),
+                                        None if sm is None else _P(sm), _P(lp), int(max_marks)))
+        self.P = P
+        self.max_marks = int(max_marks) if max_marks > 0 else 2 * self.n + 8
+
+    def population_state(self):
+        """(pop[N][2n-1], marks) with marks[i] = list of (branch, time, population above) of particle i"""
+        nn, K = 2 * self.n - 1, self.max_marks
+        pop = np.zeros((self.N, nn), dtype=np.int32)
+        nm = np.zeros(self.N, dtype=np.int32)
+        mb, mp = np.zeros((self.N, K), dtype=np.int32), np.zeros((self.N, K), dtype=np.int32)
+        mt = np.zeros((self.N, K))
+        check(lib().smc_get_population_state(self._h, _P(pop), _P(nm), _P(mb), _P(mt), _P(mp)))
+        marks = [[(int(mb[i, k]), float(mt[i, k]), int(mp[i, k])) for k in range(nm[i])] for i in range(self.N)]
+        return pop, marks
 
     # --- Segment rows ---
     def upload_rows(self, x_end, alleles, is_site, max_rec_epoch=None):
@@ -110,9 +140,11 @@ class ParticleFilter:
         return v.value
 
     def tallies(self):
-        out = np.zeros((6, self.E))
+        """[6][E] (coal count, opp, w^2-opp, rec count, opp, w^2-opp); with populations [2][Q][E] (see the header)"""
+        rows = lib().smc_tally_rows(self._h)
+        out = np.zeros((rows, self.E))
         check(lib().smc_get_tallies(self._h, _P(out)))
-        return out
+        return out if self.P == 1 else out.reshape(2, rows // 2, self.E)
 
     def counters(self):
         c = np.zeros(4, dtype=np.int64)

@@ -281,3 +281,49 @@ def make_smodel(n, t_start, inv2N, mig, single, leaf_pop, mu, rho, seqlen):
     for i in range(n):
         m.leaf_pop[i] = int(leaf_pop[i])
     return m
+
+
+def oracle_sfilter(smodel, N, seed, chunk, start_pos, ess_fraction, lags, row_end, data, is_site, max_rec=None,
+                   ancestral_aware=0, slot_offset=0):
+    """The CPU restatement of the whole filter with populations (oracle/smc_struct_oracle.c: orc_sparticle_filter).
+    Returns parent, height, pop [N,2n-1], marks (per particle: sorted list of (branch, time, pop)), logw, next_base,
+    lnZ, tallies [2,Q,E], n_resample, last_anc, n_recomb."""
+    L = oracle()
+    L.orc_schannels.restype = ctypes.c_int
+    n, E = smodel.base.n, smodel.base.E
+    nn = 2 * n - 1
+    Q = L.orc_schannels(smodel.P)
+    R = len(row_end)
+    lags = np.ascontiguousarray(lags, dtype=np.float64)
+    parts = (OrcSParticle * N)()
+    row_end = np.ascontiguousarray(row_end, dtype=np.float64)
+    data = np.ascontiguousarray(data, dtype=np.int32)
+    is_site = np.ascontiguousarray(is_site, dtype=np.int32)
+    mr = None if max_rec is None else np.ascontiguousarray(max_rec, dtype=np.int32)
+    lnZ = ctypes.c_double()
+    tallies = np.zeros(2 * Q * E)
+    nres = ctypes.c_int()
+    nrec = ctypes.c_long()
+    last_anc = np.zeros(N, dtype=np.int32)
+    rc = L.orc_sparticle_filter(ctypes.byref(smodel), N, ctypes.c_uint64(seed), ctypes.c_uint32(chunk),
+                                ctypes.c_uint32(slot_offset), ctypes.c_double(start_pos), ctypes.c_double(ess_fraction),
+                                ancestral_aware, P(lags), R, P(row_end), P(data), P(is_site),
+                                None if mr is None else P(mr), parts, ctypes.byref(lnZ), P(tallies), ctypes.byref(nres),
+                                P(last_anc), ctypes.byref(nrec))
+    if rc:
+        raise RuntimeError("structured oracle filter failed: %d" % rc)
+    parent = np.zeros((N, nn), dtype=np.int32)
+    height = np.zeros((N, nn))
+    pop = np.zeros((N, nn), dtype=np.int32)
+    logw, nb = np.zeros(N), np.zeros(N)
+    marks = []
+    for i in range(N):
+        parent[i] = np.ctypeslib.as_array(parts[i].tree.parent)[:nn]
+        height[i] = np.ctypeslib.as_array(parts[i].tree.height)[:nn]
+        pop[i] = np.ctypeslib.as_array(parts[i].pop)[:nn]
+        logw[i], nb[i] = parts[i].tree.logw, parts[i].tree.next_base
+        k = parts[i].nmarks
+        marks.append(sorted((int(parts[i].mark_branch[q]), float(parts[i].mark_time[q]), int(parts[i].mark_pop[q]))
+                            for q in range(k)))
+    return dict(parent=parent, height=height, pop=pop, marks=marks, logw=logw, next_base=nb, lnZ=lnZ.value,
+                tallies=tallies.reshape(2, Q, E), n_resample=nres.value, last_anc=last_anc, n_recomb=nrec.value)
