@@ -182,6 +182,12 @@ int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* 
  * fall-backs for sparsely sampled epochs).  CountModel::reset_lag then sets lag = lag_fraction * median. */
 int smc_calibrate_survival(int device, int32_t n, int32_t E, const double* t_start, const double* inv2N, double rho,
                            double seqlen, uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events);
+/* The same calibration under a structured model (tables as in smc_set_populations): the reference forward-simulates with
+ * whatever Model the command line describes (smcsmc.cpp:169-189), populations and migration included. */
+int smc_calibrate_survival_struct(int device, int32_t n, int32_t E, const double* t_start, int32_t npop,
+                                  const double* inv2N, const double* mig, const double* single_mig,
+                                  const int32_t* leaf_pop, double rho, double seqlen, uint64_t seed, int64_t n_args,
+                                  double* median_survival, int64_t* n_events);
 /* fastexp (particle.cpp:30-40) evaluated on the device, for the 1e-12 no-mutation-factor parity test */
 int smc_fastexp(int device, const double* x, int64_t count, double* out);
 

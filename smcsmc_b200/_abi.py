@@ -57,6 +57,8 @@ SYMBOLS = {
     "smc_normalize_log": (_I, [_I, _V, _I64, c_dp, c_dp]),
     "smc_fastexp": (_I, [_I, _V, _I64, _V]),
     "smc_calibrate_survival": (_I, [_I, ctypes.c_int32, ctypes.c_int32, _V, _V, _D, _D, ctypes.c_uint64, _I64, _V, _V]),
+    "smc_calibrate_survival_struct": (_I, [_I, ctypes.c_int32, ctypes.c_int32, _V, ctypes.c_int32, _V, _V, _V, _V, _D, _D,
+                                           ctypes.c_uint64, _I64, _V, _V]),
 }
 
 

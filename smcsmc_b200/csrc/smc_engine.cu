@@ -932,16 +932,23 @@ __global__ void __launch_bounds__(128) k_tree_functions(ModelDev m, long long co
 // ARG from the prior -- prior tree, then SMC' moves along the sequence -- and reports, for every internal node of the
 // initial tree, the position at which a node of exactly that height is no longer in the local tree (or -1 if it
 // survived to 0.6 * seqlen).  The host takes per-epoch medians.
-__global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, uint64_t seed, double* dist, int* epoch) {
+struct SurvivalSink : NullSink, SNullSink {};
+template <bool ST>
+__global__ void __launch_bounds__(128) k_survival(const __grid_constant__ ModelDev m, const __grid_constant__ SModelDev sm,
+                                                  long long count, uint64_t seed, double* dist, int* epoch, int* flags) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int BS = AUX_BS;
   const int t = threadIdx.x;
   const int n = m.n, nn = m.nn;
-  TreeViewT<BS> T = make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
+  auto T = [&]() {
+    if constexpr (ST) return make_stree_view<BS>(smem_raw, m.n, nn, m.E, t, &sm);
+    else return make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
+  }();
   const long long i = (long long)blockIdx.x * BS + t;
   if (i >= count) return;
   Rng r;
   rng_init(r, seed, (uint32_t)i, 0, 0xCA11B, RNG_INIT);
+  if constexpr (ST) T.FLAG[t] = 0;
   init_tree(m, T, r);
   // original heights live in the L0 scratch column; L1 marks them alive (1) / gone (0)
   int alive = n - 1;
@@ -951,13 +958,16 @@ __global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, u
     dist[i * (n - 1) + j] = -1.0;
     epoch[i * (n - 1) + j] = epoch_of(m, h);
   }
-  NullSink sink;
+  SurvivalSink sink;
   double logw = 0.0;
   double tl = tree_length(m, T);
   double next = draw_next_base(m, tl, r, 0.0);
   const double stop = m.seqlen * 0.6;
-  while (alive > 0 && next < stop) {
+  bool ok = true;
+  if constexpr (ST) ok = T.FLAG[t] == 0;
+  while (ok && alive > 0 && next < stop) {
     smc_move(m, T, r, next, m.E, sink, logw, tl);
+    if constexpr (ST) ok = T.FLAG[t] == 0;
     tl = tree_length(m, T);
     double pos = next;
     next = draw_next_base(m, tl, r, pos);
@@ -970,6 +980,7 @@ __global__ void __launch_bounds__(128) k_survival(ModelDev m, long long count, u
       if (!present) { dist[i * (n - 1) + j] = pos; T.l1(n + j) = 0.0; alive--; break; }
     }
   }
+  if constexpr (ST) { if (T.FLAG[t]) atomicOr(flags, (int)T.FLAG[t]); }
 }
 
 __global__ void k_fastexp(const double* x, long long count, double* out) {
@@ -2044,25 +2055,86 @@ int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* 
   return 0;
 }
 
-int smc_calibrate_survival(int device, int32_t n, int32_t E, const double* t_start, const double* inv2N, double rho,
-                           double seqlen, uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events) {
+// shared by the two calibration entry points; npop <= 1: single population (inv2N[E]), else structured tables
+static int calibrate_impl(int device, int32_t n, int32_t E, const double* t_start, int32_t npop, const double* inv2N,
+                          const double* mig, const double* single_mig, const int32_t* leaf_pop, double rho, double seqlen,
+                          uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events) {
   if (!t_start || !inv2N || !median_survival) return fail(SMC_ERR_ARG, "null argument");
   if (n_args < 1) return fail(SMC_ERR_ARG, "n_args must be >= 1");
   int rc = use_device(device);
   if (rc) return rc;
+  const bool st = npop > 1;
+  if (st && (npop > SMC_MAX_POPULATIONS || !leaf_pop)) return fail(SMC_ERR_ARG, "populations must be in 2..4 with leaf_pop given");
   ModelDev m;
-  if ((rc = fill_model(m, n, E, 0.0, rho, seqlen, 0, t_start, inv2N, nullptr, nullptr))) return rc;
-  const int BS = 64, per = n - 1;
-  DevBuf dd, de;
-  if ((rc = dd.alloc(n_args * per * sizeof(double))) || (rc = de.alloc(n_args * per * sizeof(int)))) return rc;
+  std::vector<double> inv0(E);
+  for (int e = 0; e < E; e++) inv0[e] = st ? inv2N[(size_t)e * npop] : inv2N[e];
+  if ((rc = fill_model(m, n, E, 0.0, rho, seqlen, 0, t_start, inv0.data(), nullptr, nullptr))) return rc;
+  const int BS = AUX_BS, per = n - 1;
+  DevBuf dd, de, df, t_inv, t_mig, t_tot, t_single, t_fixed, t_leaf;
+  if ((rc = dd.alloc(n_args * per * sizeof(double))) || (rc = de.alloc(n_args * per * sizeof(int))) || (rc = df.alloc(sizeof(int))))
+    return rc;
+  CUDA_TRY(cudaMemset(df.p, 0, sizeof(int)));
+  SModelDev sm;
+  memset(&sm, 0, sizeof(sm));
+  sm.P = 1;
   size_t smem = tree_smem(m.nn, E, BS);
-  CUDA_TRY(cudaFuncSetAttribute(k_survival, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
-  k_survival<<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, n_args, seed, (double*)dd.p, (int*)de.p);
+  if (st) {
+    const int Pp = npop;
+    std::vector<double> h_inv((size_t)E * Pp), h_mig((size_t)E * Pp * Pp, 0.0), h_tot((size_t)E * Pp, 0.0), h_single((size_t)E * Pp * Pp, 0.0);
+    std::vector<unsigned char> h_fixed(E, 0);
+    std::vector<signed char> h_leaf(n);
+    for (int ep = 0; ep < E; ep++)
+      for (int i = 0; i < Pp; i++) {
+        h_inv[(size_t)ep * Pp + i] = inv2N[(size_t)ep * Pp + i];
+        if (!(h_inv[(size_t)ep * Pp + i] > 0)) return fail(SMC_ERR_ARG, "inv2N must be positive");
+        double tot = 0.0;
+        for (int j = 0; j < Pp; j++) {
+          const size_t at = ((size_t)ep * Pp + i) * Pp + j;
+          double mr = (mig && j != i) ? mig[at] : 0.0;
+          double s1 = single_mig ? single_mig[at] : 0.0;
+          if (!(mr >= 0)) return fail(SMC_ERR_ARG, "migration rates must be non-negative");
+          if (!(s1 >= 0 && s1 <= 1)) return fail(SMC_ERR_ARG, "single_mig entries are probabilities");
+          h_mig[at] = mr; h_single[at] = s1;
+          if (j != i) tot += mr;
+          if (s1 > 0) h_fixed[ep] = 1;
+        }
+        h_tot[(size_t)ep * Pp + i] = tot;
+      }
+    for (int i = 0; i < n; i++) {
+      if (leaf_pop[i] < 0 || leaf_pop[i] >= Pp) return fail(SMC_ERR_ARG, "leaf population out of range");
+      h_leaf[i] = (signed char)leaf_pop[i];
+    }
+    auto up = [&](DevBuf& d, const void* src, size_t bytes) -> int {
+      int r2 = d.alloc(bytes);
+      if (r2) return r2;
+      CUDA_TRY(cudaMemcpy(d.p, src, bytes, cudaMemcpyHostToDevice));
+      return 0;
+    };
+    if ((rc = up(t_inv, h_inv.data(), h_inv.size() * 8)) || (rc = up(t_mig, h_mig.data(), h_mig.size() * 8)) ||
+        (rc = up(t_tot, h_tot.data(), h_tot.size() * 8)) || (rc = up(t_single, h_single.data(), h_single.size() * 8)) ||
+        (rc = up(t_fixed, h_fixed.data(), h_fixed.size())) || (rc = up(t_leaf, h_leaf.data(), h_leaf.size())))
+      return rc;
+    sm.P = Pp; sm.K = 120; sm.Q = 2 + 3 * Pp + Pp * Pp;
+    sm.inv2N = (const double*)t_inv.p; sm.mig = (const double*)t_mig.p; sm.migtot = (const double*)t_tot.p;
+    sm.single_mig = (const double*)t_single.p; sm.fixed = (const unsigned char*)t_fixed.p;
+    sm.leaf_pop = (const signed char*)t_leaf.p;
+    smem = stree_smem(m.nn, E, sm.K, BS);
+    if (smem > 230400) { sm.K = 2 * n + 8; smem = stree_smem(m.nn, E, sm.K, BS); }
+    if (smem > 230400) return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has");
+    CUDA_TRY(cudaFuncSetAttribute(k_survival<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+    k_survival<true><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
+  } else {
+    CUDA_TRY(cudaFuncSetAttribute(k_survival<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+    k_survival<false><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
+  }
   CUDA_TRY(cudaGetLastError());
   std::vector<double> dist(n_args * per);
   std::vector<int> ep(n_args * per);
+  int flags = 0;
   CUDA_TRY(cudaMemcpy(dist.data(), dd.p, dist.size() * sizeof(double), cudaMemcpyDeviceToHost));
   CUDA_TRY(cudaMemcpy(ep.data(), de.p, ep.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(&flags, df.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (flags & SFLAG_NOCOAL) return fail(SMC_ERR_NUMERIC, "Lines did not coalescence: the populations of the model never join and do not exchange migrants");
   std::vector<std::vector<double>> by(E);
   for (size_t k = 0; k < dist.size(); k++) if (dist[k] >= 0.0) by[ep[k]].push_back(dist[k]);
   // medians with the reference's fall-backs for sparsely sampled epochs (smcsmc.cpp:238-262)
@@ -2079,6 +2151,21 @@ int smc_calibrate_survival(int device, int32_t n, int32_t E, const double* t_sta
     if (median_survival[e] < 0) median_survival[e] = e > 0 ? median_survival[e - 1] : earliest;
   if (median_survival[0] < 0) return fail(SMC_ERR_NUMERIC, "no node survival distances could be sampled; check the model");
   return 0;
+}
+
+int smc_calibrate_survival(int device, int32_t n, int32_t E, const double* t_start, const double* inv2N, double rho,
+                           double seqlen, uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events) {
+  return calibrate_impl(device, n, E, t_start, 1, inv2N, nullptr, nullptr, nullptr, rho, seqlen, seed, n_args,
+                        median_survival, n_events);
+}
+
+int smc_calibrate_survival_struct(int device, int32_t n, int32_t E, const double* t_start, int32_t npop,
+                                  const double* inv2N, const double* mig, const double* single_mig,
+                                  const int32_t* leaf_pop, double rho, double seqlen, uint64_t seed, int64_t n_args,
+                                  double* median_survival, int64_t* n_events) {
+  if (npop < 2) return fail(SMC_ERR_ARG, "populations must be in 2..4");
+  return calibrate_impl(device, n, E, t_start, npop, inv2N, mig, single_mig, leaf_pop, rho, seqlen, seed, n_args,
+                        median_survival, n_events);
 }
 
 int smc_fastexp(int device, const double* x, int64_t count, double* out) {

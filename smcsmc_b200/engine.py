@@ -237,3 +237,19 @@ def calibrate_survival(n, t_start, inv2N, rho, seqlen, seed=1, n_args=8192, devi
     cnt = np.zeros(E, dtype=np.int64)
     check(lib().smc_calibrate_survival(device, n, E, _P(ts), _P(iv), rho, seqlen, seed, n_args, _P(med), _P(cnt)))
     return med, cnt
+
+
+def calibrate_survival_struct(n, t_start, inv2N, mig, single_mig, leaf_pop, rho, seqlen, seed=1, n_args=8192, device=0):
+    """the same under a structured model: inv2N[E][P], mig / single_mig [E][P][P] (or None), leaf_pop[n]"""
+    ts, iv = _f64(t_start), _f64(inv2N)
+    E, npop = iv.shape
+    mg = None if mig is None else _f64(mig)
+    sg = None if single_mig is None else _f64(single_mig)
+    lp = np.ascontiguousarray(leaf_pop, dtype=np.int32)
+    med = np.zeros(E)
+    cnt = np.zeros(E, dtype=np.int64)
+    check(lib().smc_calibrate_survival_struct(device, n, E, _P(ts), npop, _P(iv), None if mg is None else _P(mg),
+                                              None if sg is None else _P(sg), _P(lp), rho, seqlen, seed, n_args,
+                                              _P(med), _P(cnt)))
+    return med, cnt
+

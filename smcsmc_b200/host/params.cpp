@@ -1,5 +1,5 @@
 // Command-line parser: PfParam::parse (pfparam.cpp:51-169) + the subset of scrm's Param::parse (param.cc:37-520) that
-// the single-population, piecewise-constant engine supports.
+// the piecewise-constant engine supports: sizes per epoch and population, migration matrices, joins (-ej / -eps).
 #include "params.hpp"
 #include <algorithm>
 #include <cstdio>
@@ -34,14 +34,57 @@ int read_range(const std::string& s, int& last) {
   return first;
 }
 
-void add_size_change(Params& P, double t_scaled, double rel_size, double count) {
-  double t = t_scaled * 4 * P.N0;
-  for (auto& e : P.epochs)
-    if (e.t_start == t) { e.pop_size = rel_size * P.N0; e.vb_count = count; return; }
-  // a new change time inherits nothing: scrm's addPopulationSizes sets the size from this time onwards until the
-  // next explicit change; sizes of later, already-declared epochs stay as declared
-  P.epochs.push_back({t, rel_size * P.N0, count});
-  std::sort(P.epochs.begin(), P.epochs.end(), [](const Epoch& a, const Epoch& b) { return a.t_start < b.t_start; });
+const double kNaN = std::nan("");
+
+// Model::addChangeTime (model.cc:96-130): position of the epoch starting at `t` generations, inserted if new
+Epoch& epoch_at(Params& P, double t) {
+  size_t pos = 0;
+  for (; pos < P.epochs.size(); pos++) {
+    if (P.epochs[pos].t_start == t) return P.epochs[pos];
+    if (P.epochs[pos].t_start > t) break;
+  }
+  Epoch e;
+  e.t_start = t;
+  P.epochs.insert(P.epochs.begin() + pos, e);
+  return P.epochs[pos];
+}
+
+void check_pop(const Params& P, int pop, const std::string& flag) {
+  if (pop < 0 || pop >= P.npop) throw std::invalid_argument("Invalid population in option " + flag);
+}
+
+// Model::addPopulationSizes / addPopulationSize (model.cc:202-281); pop < 0: all populations
+void add_size_change(Params& P, double t_scaled, int pop, double rel_size, double count) {
+  if (!(rel_size * P.N0 > 0.0)) throw std::invalid_argument("population size <= 0");
+  Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
+  if (pop < 0) {
+    e.pop_size.assign(P.npop, rel_size * P.N0);
+    e.vb_count.assign(P.npop, count);
+  } else {
+    if (e.pop_size.empty()) { e.pop_size.assign(P.npop, kNaN); e.vb_count.assign(P.npop, kNaN); }
+    e.pop_size[pop] = rel_size * P.N0;
+    e.vb_count[pop] = count;
+  }
+}
+
+// Model::addMigrationRates / addMigrationRate / addSymmetricMigration (model.cc:370-459); M = 4 N0 m
+void add_mig_all(Params& P, double t_scaled, double M) {
+  Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
+  e.mig.assign((size_t)P.npop * P.npop, std::isnan(M) ? kNaN : M / (4 * P.N0));
+}
+void add_mig_one(Params& P, double t_scaled, int i, int j, double M) {
+  Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
+  if (e.mig.empty()) e.mig.assign((size_t)P.npop * P.npop, kNaN);
+  e.mig[(size_t)i * P.npop + j] = M / (4 * P.N0);
+}
+// Model::addSingleMigrationEvent (model.cc:461-480)
+void add_single_mig(Params& P, double t_scaled, int i, int j, double fraction) {
+  if (t_scaled < 0.0) throw std::invalid_argument("Single migration event: Negative time");
+  if (fraction < 0.0 || fraction > 1.0) throw std::invalid_argument("Single migration event: Fraction out of range");
+  Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
+  if (e.single_mig.empty()) e.single_mig.assign((size_t)P.npop * P.npop, 0.0);
+  e.single_mig[(size_t)i * P.npop + j] = fraction;
+  P.has_migration = true;
 }
 
 }  // namespace
@@ -96,6 +139,7 @@ void parse(int argc, char** argv, Params& P) {
     else if (f == "-o") P.out_prefix = a.next(f);
     else if (f == "-log") {}
     else if (f == "-record_ess") P.record_resample_file = true;
+    else if (f == "-dump_model") P.dump_model = true;
     else if (f == "-h" || f == "-help") P.help = true;
     else if (f == "-v" || f == "-version") P.version = true;
     else scrm.push_back(f);
@@ -105,7 +149,18 @@ void parse(int argc, char** argv, Params& P) {
   // ---- the scrm part (param.cc): two passes so that -N0 applies wherever it stands ----
   for (size_t k = 0; k + 1 < scrm.size(); k++)
     if (scrm[k] == "-N0") P.N0 = to_double(scrm[k + 1], "-N0");
-  P.epochs.push_back({0.0, P.N0, 1e10});
+  // -I fixes the number of populations; every table row is sized by it, so it is read ahead of the other options
+  // (scrm itself needs -I to come first for the same reason, param.cc:148-160)
+  for (size_t k = 0; k + 1 < scrm.size(); k++)
+    if (scrm[k] == "-I") {
+      P.npop = (int)to_double(scrm[k + 1], "-I");
+      if (P.npop < 1 || P.npop > 4) throw std::invalid_argument("-I: the B200 engine takes 1 to 4 populations");
+    }
+  {
+    Epoch e0;
+    e0.t_start = 0.0;
+    P.epochs.push_back(e0);
+  }
   if (!P.pattern.empty())
     for (double t : expand_pattern(P.pattern, P.top_t)) {
       char buf[64];
@@ -115,6 +170,18 @@ void parse(int argc, char** argv, Params& P) {
   Args s;
   s.v = scrm;
   bool have_t = false, have_r = false;
+  double min_time = 0.0;
+  auto time_of = [&](const std::string& f, bool timed) {
+    double t = timed ? s.next_double(f) : 0.0;
+    if (t < min_time)
+      throw std::invalid_argument("If you use '" + f + "' in a model with population merges ('-es'), then you need to sort both arguments by time.");
+    return t;
+  };
+  auto next_pop = [&](const std::string& f) {
+    int pop = (int)s.next_double(f) - 1;
+    check_pop(P, pop, f);
+    return pop;
+  };
   for (; s.more(); s.i++) {
     const std::string f = s.cur();
     if (f == "-t") { P.theta = s.next_double(f); have_t = true; }
@@ -125,18 +192,17 @@ void parse(int argc, char** argv, Params& P) {
       P.vb = true;
     }
     else if (f == "-eN" || f == "-N") {
-      double t = f == "-eN" ? s.next_double(f) : 0.0;
+      double t = time_of(f, f == "-eN");
       double size = s.next_double(f);
       double count = P.vb ? s.next_double(f) : 1e10;
-      add_size_change(P, t, size, count);
+      add_size_change(P, t, -1, size, count);
     }
     else if (f == "-en" || f == "-n") {
       double t = f == "-en" ? s.next_double(f) : 0.0;
-      int pop = (int)s.next_double(f);
-      if (pop != 1) unsupported(f, "more than one population");
+      int pop = next_pop(f);
       double size = s.next_double(f);
       double count = P.vb ? s.next_double(f) : 1e10;
-      add_size_change(P, t, size, count);
+      add_size_change(P, t, pop, size, count);
     }
     else if (f == "-seed" || f == "--seed" || f == "-seeds" || f == "--seeds") {
       P.seed = (uint64_t)s.next_double(f); P.seed_set = true;
@@ -148,12 +214,71 @@ void parse(int argc, char** argv, Params& P) {
     }
     else if (f == "-l") { (void)s.next(f); }                    // exact window: the driver always uses 0 (pfparam.cpp:315)
     else if (f == "-I") {
-      int npop = (int)s.next_double(f);
-      if (npop != 1) unsupported(f, "structured populations");
       (void)s.next(f);
+      P.leaf_pop.clear();
+      for (int p = 0; p < P.npop; p++) {
+        int cnt = (int)s.next_double(f);
+        if (cnt < 0) throw std::invalid_argument("Failed to parse option: -I");
+        for (int k = 0; k < cnt; k++) P.leaf_pop.push_back(p);
+      }
+      // an optional symmetric migration rate may follow (param.cc:156-160)
+      if (s.i + 1 < s.v.size()) {
+        char* end = nullptr;
+        double M = std::strtod(s.v[s.i + 1].c_str(), &end);
+        if (end != s.v[s.i + 1].c_str() && *end == '\0') {
+          s.i++;
+          if (P.npop > 1) { add_mig_all(P, 0.0, M / (P.npop - 1)); if (M > 0) P.has_migration = true; }
+        }
+      }
     }
-    else if (f == "-eI" || f == "-M" || f == "-eM" || f == "-m" || f == "-em" || f == "-ma" || f == "-ema" ||
-             f == "-es" || f == "-ej" || f == "-eps") unsupported(f, "migration / population splits");
+    else if (f == "-ma" || f == "-ema") {
+      double t = time_of(f, f == "-ema");
+      std::vector<double> M((size_t)P.npop * P.npop, 0.0);
+      for (int i = 0; i < P.npop; i++)
+        for (int j = 0; j < P.npop; j++) {
+          if (i == j) { (void)s.next(f); if (P.vb) (void)s.next(f); continue; }
+          M[(size_t)i * P.npop + j] = s.next_double(f);
+          if (P.vb) (void)s.next_double(f);
+        }
+      add_mig_all(P, t, 0.0);
+      for (int i = 0; i < P.npop; i++)
+        for (int j = 0; j < P.npop; j++)
+          if (i != j) { add_mig_one(P, t, i, j, M[(size_t)i * P.npop + j]); if (M[(size_t)i * P.npop + j] > 0) P.has_migration = true; }
+    }
+    else if (f == "-m" || f == "-em") {
+      double t = time_of(f, f == "-em");
+      int i = next_pop(f), j = next_pop(f);
+      double M = s.next_double(f);
+      add_mig_one(P, t, i, j, M);
+      if (M > 0) P.has_migration = true;
+    }
+    else if (f == "-M" || f == "-eM") {
+      double t = time_of(f, f == "-eM");
+      if (P.npop < 2) throw std::invalid_argument(f + " needs more than one population (-I)");
+      double M = s.next_double(f) / (P.npop - 1);
+      if (P.vb) (void)s.next_double(f);
+      add_mig_all(P, t, M);
+      if (M > 0) P.has_migration = true;
+    }
+    else if (f == "-ej") {
+      double t = time_of(f, true);
+      min_time = t;
+      int i = next_pop(f), j = next_pop(f);
+      add_single_mig(P, t, i, j, 1.0);
+      for (int k = 0; k < P.npop; k++)
+        if (k != i) add_mig_one(P, t, k, i, 0.0);               // nobody migrates into the dissolved population
+    }
+    else if (f == "-eps") {
+      double t = time_of(f, true);
+      min_time = t;
+      int i = next_pop(f), j = next_pop(f);
+      double fraction = s.next_double(f);
+      if (fraction < 0.0) throw std::invalid_argument("Probability in `-eps` argument is negative.");
+      if (fraction > 1.0) throw std::invalid_argument("Probability in `-eps` argument greater than one.");
+      add_single_mig(P, t, i, j, 1 - fraction);
+    }
+    else if (f == "-es") unsupported(f, "admixture into a new population");
+    else if (f == "-eI") unsupported(f, "ancient samples");
     else if (f == "-G" || f == "-eG" || f == "-g" || f == "-eg") unsupported(f, "exponential growth");
     else if (f == "-bias_heights" || f == "-bias_strengths") unsupported(f, "biased recombination sampling");
     else if (f == "-sr" || f == "-st") unsupported(f, "position-dependent rates");
@@ -169,7 +294,38 @@ void parse(int argc, char** argv, Params& P) {
     throw std::invalid_argument("Problem: epochs specified in -xr/-xc options out of range");
   if (P.nsam < 2 || P.nsam > 32) throw std::invalid_argument("-nsam must be between 2 and 32 for the B200 engine");
   if (!P.seed_set) { P.seed = (uint64_t)time(nullptr); }
+  if (P.leaf_pop.empty()) P.leaf_pop.assign(P.nsam, 0);
+  if (P.leaf_pop.size() != P.nsam)
+    throw std::invalid_argument("-I: the sample sizes of the populations do not add up to -nsam");
+  if (P.npop > 1 && P.vb) unsupported("-vb", "variational Bayes factors with structured populations");
+  finalize_model(P);
+  if (P.npop > 1 && !P.has_migration)      // Model::check (model.cc:630-633)
+    throw std::invalid_argument("Model has multiple populations but no migration. Coalescence impossible");
   finalize_rates(P);
+}
+
+// Model::finalize (model.cc:553-670): sizes not given at a change time continue from the epoch before (default N0),
+// migration rates likewise (default 0); fixed-time moves hold for their own epoch start only
+void finalize_model(Params& P) {
+  const size_t np = (size_t)P.npop;
+  const std::vector<double>* last_mig = nullptr;
+  for (size_t e = 0; e < P.epochs.size(); e++) {
+    Epoch& ep = P.epochs[e];
+    if (ep.pop_size.empty()) { ep.pop_size.assign(np, kNaN); ep.vb_count.assign(np, kNaN); }
+    for (size_t p = 0; p < np; p++) {
+      if (std::isnan(ep.pop_size[p])) ep.pop_size[p] = e == 0 ? P.N0 : P.epochs[e - 1].pop_size[p];
+      if (std::isnan(ep.vb_count[p])) ep.vb_count[p] = 1e10;
+    }
+    if (ep.mig.empty()) {
+      if (last_mig) ep.mig = *last_mig; else ep.mig.assign(np * np, 0.0);
+    } else {
+      for (size_t k = 0; k < np * np; k++)
+        if (std::isnan(ep.mig[k])) ep.mig[k] = last_mig ? (*last_mig)[k] : 0.0;
+    }
+    for (size_t p = 0; p < np; p++) ep.mig[p * np + p] = 0.0;
+    last_mig = &ep.mig;
+    if (ep.single_mig.empty()) ep.single_mig.assign(np * np, 0.0);
+  }
 }
 
 void finalize_rates(Params& P) {

@@ -14,10 +14,15 @@
 
 namespace host {
 
+// One row of scrm's Model tables (model.h:55: change_times_, pop_sizes_list_, mig_rates_list_, single_mig_probs_list_).
+// While the command line is parsed NaN means "as in the previous epoch" and an empty vector "not mentioned at this
+// time"; finalize_model() resolves both the way Model::finalize does (model.cc:553-670).
 struct Epoch {
-  double t_start;     // generations
-  double pop_size;    // absolute N_e
-  double vb_count;    // -vb event count (1e10 = no correction)
+  double t_start;                  // generations
+  std::vector<double> pop_size;    // [P] absolute N_e
+  std::vector<double> vb_count;    // [P] -vb event counts (1e10 = no correction)
+  std::vector<double> mig;         // [P*P] per-generation rate of a lineage in i moving to j (backwards in time)
+  std::vector<double> single_mig;  // [P*P] probability of being moved i -> j at the START of the epoch (-ej / -eps)
 };
 
 struct Params {
@@ -50,6 +55,10 @@ struct Params {
   bool seed_set = false;
   bool vb = false;
   std::vector<Epoch> epochs;                // sorted by time, epochs[0].t_start == 0
+  int npop = 1;                             // -I
+  std::vector<int> leaf_pop;                // [nsam] Model::sample_population (0-based)
+  bool has_migration = false;               // Model::has_migration()
+  bool dump_model = false;                  // -dump_model (extension): print the flattened tables and exit
   std::vector<std::string> argv;
   // derived
   double mutation_rate = 0, recombination_rate = 0, original_recombination_rate = 0;
@@ -101,5 +110,6 @@ inline std::vector<double> expand_pattern(const std::string& pattern, double top
 
 void parse(int argc, char** argv, Params& P);      // params.cpp
 void finalize_rates(Params& P);
+void finalize_model(Params& P);                    // Model::finalize (model.cc:553-670)
 
 }  // namespace host

@@ -90,7 +90,22 @@ void write_log(ostream& w, const Params& P, const Out& o) {   // PfParam::writeL
   w << setw(17) << "recomb rate =" << setw(10) << P.original_recombination_rate << "\n";
   w << setw(17) << "inferred recomb rate = " << setw(10) << P.recombination_rate << "\n";
   w << setw(17) << "Pop size (at Generation):\n";
-  for (const auto& e : P.epochs) w << setw(3) << "(" << setw(8) << e.t_start << " )" << " | " << setw(10) << e.pop_size << "\n";
+  for (const auto& e : P.epochs) {
+    w << setw(3) << "(" << setw(8) << e.t_start << " )";
+    for (double sz : e.pop_size) w << " | " << setw(10) << sz;
+    w << "\n";
+  }
+  if (P.npop > 1) {
+    w << setw(17) << "Migration rate (per generation, backwards in time; at Generation):\n";
+    for (const auto& e : P.epochs) {
+      w << setw(3) << "(" << setw(8) << e.t_start << " )";
+      for (int i = 0; i < P.npop; i++) {
+        w << " |";
+        for (int j = 0; j < P.npop; j++) w << " " << setw(10) << e.mig[(size_t)i * P.npop + j];
+      }
+      w << "\n";
+    }
+  }
   w << "Out file is saved in file: " << o.out_name << "\n";
 }
 
@@ -120,27 +135,59 @@ void print_help(const Params& P) {
   opt("-cap", "FLT", "Cap on inferred population sizes");
   opt("-ancestral_aware", " ", "Alleles are polarised (0 = ancestral)");
   opt("-record_ess", " ", "Generate *.resample file");
-  cout << endl << "Model (scrm syntax): -t THETA  -r RHO LENGTH  -N0 N  -eN T SIZE  -en T 1 SIZE  -vb  -seed S" << endl;
-  cout << "Not supported by this engine yet (rejected with an error): -I/-ej/-em/-eM/-ema/-es (structure), -eG (growth),"
-       << endl << "  -guide, -bias_heights/-bias_strengths, -apf > 0, -dephase, -arg" << endl;
+  cout << endl << "Model (scrm syntax): -t THETA  -r RHO LENGTH  -N0 N  -eN T SIZE  -en T POP SIZE  -vb  -seed S" << endl;
+  cout << "  -I NPOP n1..nP [M]  -eM T M  -em T i j M  -ema T M11..  -ej T i j  -eps T i j f   (up to 4 populations)" << endl;
+  cout << "Not supported by this engine yet (rejected with an error): -es, -eI, -eG (growth), -guide," << endl
+       << "  -bias_heights/-bias_strengths, -apf > 0, -dephase, -arg, -vb together with -I" << endl;
 }
 
-struct Tallies {   // CountModel totals incl. the initial pseudo-counts (count.cpp:161-193)
-  vector<double> coal_count, coal_opp, coal_weight, rec_count, rec_opp, rec_weight;
-  double resample_count = 0, delayed_opp = 0;
+// the flattened Model the engine takes: [E] times, [E][P] 1/(2N), [E][P][P] migration rates and fixed-time moves
+struct FlatModel {
+  int E, np;
+  vector<double> t_start, inv2N, mig, single_mig;
+  vector<int32_t> leaf_pop;
+  explicit FlatModel(const Params& P) : E(P.num_epochs()), np(P.npop) {
+    for (const auto& e : P.epochs) {
+      t_start.push_back(e.t_start);
+      for (int p = 0; p < np; p++) inv2N.push_back(1.0 / (2.0 * e.pop_size[p]));
+      mig.insert(mig.end(), e.mig.begin(), e.mig.end());
+      single_mig.insert(single_mig.end(), e.single_mig.begin(), e.single_mig.end());
+    }
+    for (int v : P.leaf_pop) leaf_pop.push_back(v);
+  }
 };
+
+// -dump_model (extension, used by the CPU tests): the tables exactly as they are handed to the engine
+void dump_model(const Params& P) {
+  FlatModel M(P);
+  cout << setprecision(17);
+  cout << "npop " << M.np << "\nepochs " << M.E << "\nmutation_rate " << P.mutation_rate << "\nrecombination_rate "
+       << P.recombination_rate << "\nloci_length " << P.loci_length << "\nleaf_pop";
+  for (int v : M.leaf_pop) cout << " " << v;
+  cout << "\n";
+  for (int e = 0; e < M.E; e++) {
+    cout << "epoch " << e << " t_start " << M.t_start[e] << " inv2N";
+    for (int p = 0; p < M.np; p++) cout << " " << M.inv2N[(size_t)e * M.np + p];
+    cout << " mig";
+    for (int k = 0; k < M.np * M.np; k++) cout << " " << M.mig[(size_t)e * M.np * M.np + k];
+    cout << " single_mig";
+    for (int k = 0; k < M.np * M.np; k++) cout << " " << M.single_mig[(size_t)e * M.np * M.np + k];
+    cout << "\n";
+  }
+}
 
 // one EM iteration: pfARG_core (smcsmc.cpp:278-400)
 void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<double>& chunk_start, double chunk_len,
                 const Out& out, int em, const vector<int>& devices) {
   const int device = devices[0];
-  const int E = P.num_epochs(), n = (int)P.nsam;
-  vector<double> t_start(E), inv2N(E), vb(E), lags(E);
+  const int E = P.num_epochs(), n = (int)P.nsam, np = P.npop;
+  const FlatModel M(P);
+  const vector<double>& t_start = M.t_start;
+  vector<double> inv2N0(E), vb(E), lags(E);
   vector<uint8_t> mask(E);
   for (int e = 0; e < E; e++) {
-    t_start[e] = P.epochs[e].t_start;
-    inv2N[e] = 1.0 / (2.0 * P.epochs[e].pop_size);
-    vb[e] = P.vb ? log(exp_digamma(P.epochs[e].vb_count) / P.epochs[e].vb_count) : 0.0;
+    inv2N0[e] = M.inv2N[(size_t)e * np];
+    vb[e] = P.vb ? log(exp_digamma(P.epochs[e].vb_count[0]) / P.epochs[e].vb_count[0]) : 0.0;
     mask[e] = (uint8_t)(P.record_event_in_epoch[e] & 3);
   }
   // CountModel::init_lags (count.cpp:230-249), then reset_lag from the calibration (smcsmc.cpp:314-316)
@@ -154,8 +201,13 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
   if (P.calibrate_lag) {
     vector<double> surv(E);
     vector<int64_t> cnt(E);
-    check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N.data(), P.recombination_rate, chunk_len, 1,
-                                 8192, surv.data(), cnt.data()));
+    if (np > 1)
+      check(smc_calibrate_survival_struct(device, n, E, t_start.data(), np, M.inv2N.data(), M.mig.data(),
+                                          M.single_mig.data(), M.leaf_pop.data(), P.recombination_rate, chunk_len, 1,
+                                          8192, surv.data(), cnt.data()));
+    else
+      check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N0.data(), P.recombination_rate, chunk_len, 1,
+                                   8192, surv.data(), cnt.data()));
     for (int e = 0; e < E; e++) {
       clog << " Epoch " << e << " (" << cnt[e] << " events): survival distance " << surv[e] << endl;
       lags[e] = surv[e] * P.lag_fraction;
@@ -190,8 +242,10 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     c.chunk = (uint32_t)(((long long)chunk_start[k]) & 0xFFFFFF);
     c.mu = P.mutation_rate; c.rho = P.recombination_rate; c.seqlen = chunk_len; c.start_pos = 0.0;
     c.ess_fraction = P.ESS_fraction; c.ancestral_aware = P.ancestral_aware; c.parity_scan = 0;
-    c.t_start = t_start.data(); c.inv2N = inv2N.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
+    c.t_start = t_start.data(); c.inv2N = inv2N0.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
     check(smc_create(&c, &eng[k]));
+    if (np > 1)
+      check(smc_set_populations(eng[k], np, M.inv2N.data(), M.mig.data(), M.single_mig.data(), M.leaf_pop.data(), 0));
     check(smc_upload_rows(eng[k], rows.x_end.data(), rows.alleles.data(), rows.is_site.data(), max_rec.data(), (int64_t)R));
     check(smc_init_particles(eng[k]));
   }
@@ -209,20 +263,22 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     check(smc_sweep_many(eng.data(), (int32_t)C, 1));
   }
   cout << "\r Particle filtering step 100% completed." << endl;
-  vector<double> t(6 * E, 0.0);
+  const int rows_t = smc_tally_rows(eng[0]);           // 6 for one population, 2Q with structure
+  vector<double> t((size_t)rows_t * E, 0.0);
   double lnZ = 0;
   int64_t counters[4] = {0, 0, 0, 0};
   for (size_t k = 0; k < C; k++) {
     check(smc_finish(eng[k]));
-    vector<double> tk(6 * E);
+    vector<double> tk((size_t)rows_t * E);
     double lz = 0;
     int64_t ck[4];
     check(smc_get_tallies(eng[k], tk.data()));
     int rc = smc_get_lnZ(eng[k], &lz);
-    if (rc == SMC_ERR_NUMERIC) throw runtime_error("Zero or negative probabilities");
+    if (rc == SMC_ERR_NUMERIC) throw runtime_error(string(smc_last_error()).find("probabilit") != string::npos
+                                                       ? string("Zero or negative probabilities") : string(smc_last_error()));
     check(rc);
     check(smc_get_counters(eng[k], ck));
-    for (int q = 0; q < 6 * E; q++) t[q] += tk[q];
+    for (size_t q = 0; q < tk.size(); q++) t[q] += tk[q];
     lnZ += lz;
     for (int q = 0; q < 4; q++) counters[q] += ck[q];
     if (P.record_resample_file) {
@@ -236,17 +292,40 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
   clog << "Got to end of sequence; resampled " << counters[1] << " times" << endl;
   clog << " Inference step completed." << endl;
 
-  Tallies T;
-  for (int e = 0; e < E; e++) {
-    T.coal_count.push_back(t[0 * E + e] + inv2N[e]);       // initial value: the rate, with opportunity 1
-    T.coal_opp.push_back(t[1 * E + e] + 1.0);
-    T.coal_weight.push_back(t[2 * E + e] + 1.0);
-    T.rec_count.push_back(t[3 * E + e] + P.recombination_rate);
-    T.rec_opp.push_back(t[4 * E + e] + 1.0);
-    T.rec_weight.push_back(t[5 * E + e] + 1.0);
+  // CountModel totals incl. the initial pseudo-counts (count.cpp:161-226): count = the rate, opportunity = weight = 1
+  vector<double> coal_count((size_t)E * np), coal_opp((size_t)E * np), coal_weight((size_t)E * np);
+  vector<double> rec_count(E), rec_opp(E), rec_weight(E);
+  vector<double> mig_count((size_t)E * np * np, 0.0), mig_opp((size_t)E * np, 1.0), mig_weight((size_t)E * np, 1.0);
+  if (np == 1) {
+    for (int e = 0; e < E; e++) {
+      coal_count[e] = t[0 * E + e] + inv2N0[e];
+      coal_opp[e] = t[1 * E + e] + 1.0;
+      coal_weight[e] = t[2 * E + e] + 1.0;
+      rec_count[e] = t[3 * E + e] + P.recombination_rate;
+      rec_opp[e] = t[4 * E + e] + 1.0;
+      rec_weight[e] = t[5 * E + e] + 1.0;
+    }
+  } else {
+    // cells of smc_set_populations: rows [0,Q) sums of w * cell, rows [Q,2Q) sums of w^2 * cell
+    const int Q = rows_t / 2;
+    auto W = [&](int cell, int e) { return t[(size_t)cell * E + e]; };
+    auto W2 = [&](int cell, int e) { return t[(size_t)(Q + cell) * E + e]; };
+    for (int e = 0; e < E; e++) {
+      rec_count[e] = W(0, e) + P.recombination_rate;
+      rec_opp[e] = W(1, e) + 1.0;
+      rec_weight[e] = W2(1, e) + 1.0;
+      for (int p = 0; p < np; p++) {
+        coal_count[(size_t)e * np + p] = W(2 + 3 * p, e) + M.inv2N[(size_t)e * np + p];
+        coal_opp[(size_t)e * np + p] = W(3 + 3 * p, e) + 1.0;
+        coal_weight[(size_t)e * np + p] = W2(3 + 3 * p, e) + 1.0;
+        mig_opp[(size_t)e * np + p] = W(4 + 3 * p, e) + 1.0;
+        mig_weight[(size_t)e * np + p] = W2(4 + 3 * p, e) + 1.0;
+        for (int q = 0; q < np; q++)
+          mig_count[((size_t)e * np + p) * np + q] = W(2 + 3 * np + p * np + q, e) + M.mig[((size_t)e * np + p) * np + q];
+      }
+    }
   }
-  T.resample_count = (double)counters[1];
-  T.delayed_opp = P.loci_length;
+  const double resample_count = (double)counters[1], delayed_opp = P.loci_length;
 
   {   // <prefix>.recomb.gz: header of CountModel::dump_local_recomb_logs (count.cpp:616-628); the per-100-bp table is
       // row f2 of the scope table and is left empty
@@ -260,29 +339,44 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     if (g) gzclose(g);
   }
 
-  // reset_model_parameters(force_update = true): the in-binary M-step (count.cpp:44-63,267-325)
+  // reset_model_parameters(force_update = true): the in-binary M-step (count.cpp:44-63,267-352)
   clog << " MODEL IS RESET at base " << P.loci_length << endl;
   double ro = 0, rc_ = 0, rw = 0;
-  for (int e = 0; e < E; e++) { ro += T.rec_opp[e]; rc_ += T.rec_count[e]; rw += T.rec_weight[e]; }
+  for (int e = 0; e < E; e++) { ro += rec_opp[e]; rc_ += rec_count[e]; rw += rec_weight[e]; }
   P.recombination_rate = rc_ / ro;
   clog << " Setting recombination rate to " << P.recombination_rate << " ( " << rc_ << " / " << ro << "; post-lag ESS "
        << 1.0 / (rw / ro) << " )" << endl;
-  for (int e = 0; e < E; e++) {
-    double rate = T.coal_count[e] / T.coal_opp[e];
-    double pop = 1.0 / (2.0 * rate);
-    P.epochs[e].pop_size = (P.useCap && pop >= P.Ne_cap) ? P.Ne_cap : pop;
-    clog << " Setting size of population 0 @ " << setw(8) << t_start[e] << " to " << setw(8) << pop << " ( 0.5 * "
-         << T.coal_opp[e] << " / " << T.coal_count[e] << "; post-lag ESS " << 1.0 / (T.coal_weight[e] / T.coal_opp[e])
-         << " )" << endl;
-  }
+  for (int e = 0; e < E; e++)
+    for (int p = 0; p < np; p++) {
+      const size_t at = (size_t)e * np + p;
+      double rate = coal_count[at] / coal_opp[at];
+      double pop = 1.0 / (2.0 * rate);
+      P.epochs[e].pop_size[p] = (P.useCap && pop >= P.Ne_cap) ? P.Ne_cap : pop;
+      clog << " Setting size of population " << p << " @ " << setw(8) << t_start[e] << " to " << setw(8) << pop
+           << " ( 0.5 * " << coal_opp[at] << " / " << coal_count[at] << "; post-lag ESS "
+           << 1.0 / (coal_weight[at] / coal_opp[at]) << " )" << endl;
+    }
+  if (P.has_migration && np > 1)   // CountModel::reset_mig_rate (count.cpp:327-352)
+    for (int e = 0; e < E; e++)
+      for (int p = 0; p < np; p++)
+        for (int q = 0; q < np; q++)
+          if (p != q) P.epochs[e].mig[(size_t)p * np + q] = mig_count[((size_t)e * np + p) * np + q] / mig_opp[(size_t)e * np + p];
 
   // CountModel::log_counts (count.cpp:66-158) and the LogL row (smcsmc.cpp:391)
+  auto t_end = [&](int e) { return e == E - 1 ? 1e+99 : t_start[e + 1]; };
   for (int e = 0; e < E; e++)
-    out.row(em, e, t_start[e], e == E - 1 ? 1e+99 : t_start[e + 1], "Coal", 0, -1, T.coal_opp[e], T.coal_count[e],
-            T.coal_weight[e]);
+    for (int p = 0; p < np; p++)
+      out.row(em, e, t_start[e], t_end(e), "Coal", p, -1, coal_opp[(size_t)e * np + p], coal_count[(size_t)e * np + p],
+              coal_weight[(size_t)e * np + p]);
   out.row(em, -1, 0.0, 1e+99, "Recomb", -1, -1, ro, rc_, rw);
-  out.row(em, -1, 0.0, 1e+99, "Delay", -1, -1, T.delayed_opp, 0.0 / (double)P.N, T.delayed_opp);
-  out.row(em, -1, 0.0, 1e+99, "Resamp", -1, -1, T.delayed_opp, T.resample_count, T.delayed_opp);
+  for (int e = 0; e < E; e++)
+    for (int p = 0; p < np; p++)
+      for (int q = 0; q < np; q++)
+        if (p != q)
+          out.row(em, e, t_start[e], t_end(e), "Migr", p, q, mig_opp[(size_t)e * np + p],
+                  mig_count[((size_t)e * np + p) * np + q], mig_weight[(size_t)e * np + p]);
+  out.row(em, -1, 0.0, 1e+99, "Delay", -1, -1, delayed_opp, 0.0 / (double)P.N, delayed_opp);
+  out.row(em, -1, 0.0, 1e+99, "Resamp", -1, -1, delayed_opp, resample_count, delayed_opp);
   out.row(em, -1, 0, 1e+99, "LogL", -1, -1, 1.0, lnZ, 1.0);
   clog << " Estimated log likelihood: " << lnZ << endl;
 }
@@ -301,6 +395,7 @@ int main(int argc, char* argv[]) {
       return EXIT_SUCCESS;
     }
     if (P.help) { print_help(P); return EXIT_SUCCESS; }
+    if (P.dump_model) { dump_model(P); return EXIT_SUCCESS; }
     Out out{P.out_prefix + ".out", P.out_prefix + ".log", P.out_prefix + ".recomb.gz", P.out_prefix + ".resample"};
     remove(out.out_name.c_str());
     remove(out.log_name.c_str());

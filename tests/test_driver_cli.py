@@ -56,12 +56,72 @@ def test_parse_errors(args, message):
 
 
 @pytest.mark.parametrize("args", [
-    ["-I", "2", "2", "2"], ["-ej", "0.5", "2", "1"], ["-em", "0", "2", "1", "1"], ["-eM", "0", "1"], ["-eG", "0", "1"],
+    ["-es", "0.5", "1", "0.3"], ["-eI", "0.1", "1"], ["-eG", "0", "1"], ["-vb", "-I", "2", "2", "2", "1.0"],
     ["-guide", "x.gz"], ["-bias_heights", "400"], ["-apf", "1"], ["-dephase"], ["-arg"], ["-sr", "100", "2"],
 ])
 def test_unsupported_features_are_rejected_not_ignored(args):
     r = run("-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", "-seg", SEG, *args)
     assert r.returncode == 1 and "is not supported by the B200 engine yet" in r.stderr, r.stderr
+
+
+def _dump(*args):
+    r = run(*args, "-dump_model")
+    assert r.returncode == 0, r.stderr
+    d = {"rows": []}
+    for line in r.stdout.splitlines():
+        w = line.split()
+        if w[0] == "epoch":
+            i, j, k = w.index("inv2N"), w.index("mig"), w.index("single_mig")
+            d["rows"].append((float(w[3]), [float(x) for x in w[i + 1:j]], [float(x) for x in w[j + 1:k]],
+                                [float(x) for x in w[k + 1:]]))
+        elif w[0] == "leaf_pop":
+            d["leaf_pop"] = [int(x) for x in w[1:]]
+        else:
+            d[w[0]] = float(w[1])
+    return d
+
+
+def test_structured_models_parse_like_scrm():
+    """-I / -en / -eM / -em / -ej: the flattened tables the driver hands to the engine against the tables of the
+    reference's own parsed Model (scrm Param::parse + Model::finalize), stored with the structured fixtures
+    (tests/golden/struct_moments.npz, make_golden.py::golden_struct_moments, same command lines)"""
+    import numpy as np
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    G = np.load(os.path.join(ROOT, "tests", "golden", "struct_moments.npz"))
+    models = {   # the flags of make_golden.py::STRUCT_MODELS
+        "island2": (4, "-I 2 2 2 1.0"),
+        "split2": (4, "-I 2 2 2 -ej 0.5 2 1"),
+        "config3": (8, "-I 2 4 4 -em 0 2 1 1 -ej 0.5 2 1"),
+        "island2_epochs": (6, "-I 2 3 3 0.5 -en 0.05 1 0.3 -en 0.05 2 2 -eM 0.2 3.0 -eN 0.6 1.5"),
+        "three": (6, "-I 3 2 2 2 -em 0.1 2 1 2.0 -ej 0.3 3 2 -ej 0.8 2 1"),
+    }
+    L = 100000000
+    for name, (n, flags) in models.items():
+        d = _dump("-nsam", str(n), "-Np", "10", "-t", repr(4e4 * 2.5e-8 * L), "-r", repr(4e4 * 1e-8 * L), str(L),
+                  "-seed", "1", *flags.split())
+        ts, inv, mig, single, leaf = (G[name + k] for k in ("_t_start", "_inv2N", "_mig", "_single", "_leaf_pop"))
+        E, P = inv.shape
+        assert d["npop"] == P and d["epochs"] == E and len(d["rows"]) == E, name
+        assert d["leaf_pop"] == list(leaf), name
+        np.testing.assert_allclose([e[0] for e in d["rows"]], ts, rtol=1e-14)
+        np.testing.assert_allclose([e[1] for e in d["rows"]], inv, rtol=1e-14)
+        np.testing.assert_allclose(np.array([e[2] for e in d["rows"]]).reshape(E, P, P), mig, rtol=1e-14)
+        np.testing.assert_allclose(np.array([e[3] for e in d["rows"]]).reshape(E, P, P), single, rtol=1e-14)
+        assert d["mutation_rate"] == pytest.approx(float(G[name + "_mu"]), rel=1e-14)
+        assert d["recombination_rate"] == pytest.approx(float(G[name + "_rho"]), rel=1e-14)
+
+
+@pytest.mark.parametrize("args, message", [
+    (["-I", "2", "2", "2"], "Model has multiple populations but no migration"),
+    (["-I", "2", "2", "3", "1.0"], "do not add up to -nsam"),
+    (["-I", "2", "2", "2", "-ej", "0.5", "2", "1", "-em", "0", "2", "1", "1"], "sort both arguments by time"),
+    (["-I", "2", "2", "2", "1.0", "-en", "0.1", "3", "1"], "Invalid population"),
+    (["-I", "5", "1", "1", "1", "1", "0", "1.0"], "1 to 4 populations"),
+])
+def test_structured_parse_errors(args, message):
+    r = run("-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", *args)
+    assert r.returncode == 1 and message in r.stderr, r.stderr
 
 
 def test_seg_validation(tmp_path):
