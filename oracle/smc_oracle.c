@@ -348,6 +348,9 @@ void orc_smc_move(const orc_model* m, orc_particle* p, orc_rng* r, int max_rec_e
   double hroot = height[root];
   double tt = hh, tc = 0.0;
   int k = 0, above_root = 0;
+  /* one unit exponential for the whole float, used up at rate * length per interval (memoryless; the reference's
+     sampleExpoExpoLimit re-uses its unit exponential across intervals the same way, random_generator.cc:32-78) */
+  double ex = -log(orc_rng_uniform(r));
   for (;;) {
     double tnode = DBL_MAX;
     above_root = !(tt < hroot);
@@ -361,12 +364,13 @@ void orc_smc_move(const orc_model* m, orc_particle* p, orc_rng* r, int max_rec_e
     double tep = e + 1 < m->E ? m->t_start[e + 1] : DBL_MAX;
     double tend = tnode < tep ? tnode : tep;
     double rate = k * m->inv2N[e];
-    double w = -log(orc_rng_uniform(r)) / rate;
-    tc = tt + w;
-    int coal = tc < tend;
+    double need = rate * (tend - tt);
+    int coal = ex < need;
+    if (coal) { tc = tt + ex / rate; if (!(tc < tend)) tc = nextafter(tend, 0.0); }
     double dt = (coal ? tc : tend) - tt;
     if ((m->rec_mask[e] & 2) && e <= max_rec_epoch) emit(t, ORC_EV_COAL, e, coal, x, x, k * dt);
     if (coal) break;
+    ex -= need;
     tt = tend;
     if (tend == tep) e++;
   }

@@ -302,6 +302,10 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
   // coalescence opportunity of consecutive intervals inside one epoch is summed in a register and recorded once
   double opp = 0.0;
   bool rec_on = (m.rec_mask[e] & 2) && e <= max_rec_epoch;
+  // ONE unit exponential for the whole float: an interval of length d at rate r uses up r * d of it, the lineage
+  // coalesces in the interval in which it runs out (memoryless, the same law as a fresh draw per interval; the reference
+  // re-uses its unit exponential the same way, random_generator.cc:32-78)
+  double ex = -log(rng_uniform(r));
   for (;;) {
     double tnode = DBL_MAX;
     above_root = !(tt < hroot);
@@ -310,12 +314,13 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
     double tep = e + 1 < m.E ? m.t_start[e + 1] : DBL_MAX;
     double tend = tnode < tep ? tnode : tep;
     double rate = k * m.inv2N[e];
-    double w = -log(rng_uniform(r)) / rate;
-    tc = tt + w;
-    bool coal = tc < tend;
+    double need = rate * (tend - tt);
+    bool coal = ex < need;
+    if (coal) { tc = tt + ex / rate; if (!(tc < tend)) tc = nextafter(tend, 0.0); }
     double dt = (coal ? tc : tend) - tt;
     opp += k * dt;
     if (coal) break;
+    ex -= need;
     tt = tend;
     if (tend == tep) {
       if (rec_on) sink.coal(e, x, 0, opp);

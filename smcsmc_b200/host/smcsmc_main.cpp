@@ -244,8 +244,20 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     c.ess_fraction = P.ESS_fraction; c.ancestral_aware = P.ancestral_aware; c.parity_scan = 0;
     c.t_start = t_start.data(); c.inv2N = inv2N0.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
     check(smc_create(&c, &eng[k]));
-    if (np > 1)
-      check(smc_set_populations(eng[k], np, M.inv2N.data(), M.mig.data(), M.single_mig.data(), M.leaf_pop.data(), 0));
+    if (np > 1) {
+      // capacity of the per-particle pool of migration marks: a local tree of n leaves is ~ 4 N0 * 2 * H(n-1) generations
+      // long and collects marks at the summed migration rate; room for several times the expectation, engine maximum 120
+      // (a particle that still overflows makes the run fail loudly at the end, smc_get_lnZ)
+      double msum = 0;
+      for (int e = 0; e < E; e++) {
+        double s = 0;
+        for (int q = 0; q < np * np; q++) s += M.mig[(size_t)e * np * np + q];
+        msum = max(msum, s * 4 * P.N0);
+      }
+      int marks = min(120, 2 * n + 8 + 10 * (int)ceil(msum));
+      if (const char* mm = getenv("SMCSMC_MAX_MARKS")) marks = atoi(mm);
+      check(smc_set_populations(eng[k], np, M.inv2N.data(), M.mig.data(), M.single_mig.data(), M.leaf_pop.data(), marks));
+    }
     check(smc_upload_rows(eng[k], rows.x_end.data(), rows.alleles.data(), rows.is_site.data(), max_rec.data(), (int64_t)R));
     check(smc_init_particles(eng[k]));
   }

@@ -304,6 +304,39 @@ def golden_configs0(seeds=range(1, 11)):
     json.dump(out, open(os.path.join(HERE, "configs0_reference.json"), "w"))
 
 
+EM_STRUCT_BASE = ("-nsam 8 -Np 500 -N0 10000 -t 2000 -r 800 2000000 -I 2 4 4 -em 0 2 1 1 -eN 0.1 1 -ej 0.5 2 1 {extra} "
+                  "-seed {seed} -seg {seg} -o {out}")
+EM_STRUCT_VARIANTS = {
+    # BASELINE.json configs[2] in small: two populations of 4 haplotypes, migration 2 -> 1 backwards in time, joined at
+    # 0.5 * 4N0; inference epochs {0, 0.1, 0.5}; one sweep with everything recorded
+    "sweep": "-EM 0",
+    # three in-binary EM iterations on population sizes AND migration rates (recombination excluded)
+    "em": "-xr 0-2 -EM 2",
+}
+
+
+def golden_em_struct(seeds=range(1, 13)):
+    """The same for a structured model (tests/data/split_mig_n8_2Mb_seed13.seg, simulated by the reference's scrm under
+    `-I 2 4 4 -em 0 2 1 1 -ej 0.5 2 1`): per-population Coal rows and the Migr rows of the unmodified binary."""
+    import json
+    import subprocess
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+    seg = os.path.join(os.path.dirname(HERE), "data", "split_mig_n8_2Mb_seed13.seg")
+    binp = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref", "smcsmc")
+    out = {"base": EM_STRUCT_BASE, "variants": EM_STRUCT_VARIANTS, "seeds": list(seeds), "runs": {}}
+    with tempfile.TemporaryDirectory() as tmp:
+        for name, extra in EM_STRUCT_VARIANTS.items():
+            def run(seed):
+                o = os.path.join(tmp, "%s_s%d" % (name, seed))
+                subprocess.run([binp] + EM_STRUCT_BASE.format(extra=extra, seed=seed, seg=seg, out=o).split(), check=True,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                return parse_out(o + ".out")
+            with ThreadPoolExecutor(8) as ex:
+                out["runs"][name] = list(ex.map(run, seeds))
+    json.dump(out, open(os.path.join(HERE, "em_struct_reference.json"), "w"))
+
+
 def golden_em(seeds=range(1, 13)):
     """End-to-end reference runs (the unmodified smcsmc binary, oracle/_ref/smcsmc) on tests/data/const_n4_2Mb_seed7.seg:
     12 seeds per command variant; stores every .out row per seed (tests/test_em_parity.py compares the B200 driver's

@@ -134,7 +134,7 @@ def test_cli_errors_and_help():
     assert r.returncode == 0 and "-Np" in r.stdout
     r = subprocess.run([BIN, "-Np", "10", "-t", "10"], capture_output=True, text=True)
     assert r.returncode == 1 and r.stderr.strip().endswith("Error: The option -r is required")
-    r = subprocess.run([BIN, "-Np", "10", "-t", "10", "-r", "10", "1000", "-I", "2", "2", "2", "-seg", SEG],
+    r = subprocess.run([BIN, "-Np", "10", "-t", "10", "-r", "10", "1000", "-eG", "0.1", "2", "-seg", SEG],
                        capture_output=True, text=True)
     assert r.returncode == 1 and "not supported by the B200 engine yet" in r.stderr
     r = subprocess.run([BIN, "-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", "-seg", "/nonexistent.seg"],
