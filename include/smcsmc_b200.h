@@ -34,7 +34,7 @@ typedef enum {
 
 typedef struct smc_engine smc_engine;
 
-/* Flattened Model + PfParam of one sweep (single population; migration is a later row).
+/* Flattened Model + PfParam of one sweep (one population; smc_set_populations adds structure).
  * Replaces: Model (scrm/src/model.h:55), PfParam (pfparam.hpp), CountModel::lags (count.hpp). */
 typedef struct {
   int32_t n;                /* -nsam: haplotypes, 2..SMC_MAX_HAPLOTYPES */
