@@ -126,10 +126,14 @@ __device__ __forceinline__ TreeViewT<BS> make_tree_view(unsigned char* smem, int
 // forest.h:188 getLocalTreeLength: sum of branch lengths in slot order (the order the parity tests assume)
 template <class TV>
 __device__ inline double tree_length(const ModelDev& m, const TV& T) {
+  // leaves sit at height 0 and always have a parent: their term is h(parent) - 0.0 == h(parent) exactly, so splitting
+  // the loop changes no bit and spares the leaf test on every height access
   double len = 0.0;
-  for (int v = 0; v < m.nn; v++) {
+  const int n = m.n;
+  for (int v = 0; v < n; v++) len += T.hw(T.par(v));
+  for (int v = n; v < m.nn; v++) {
     int p = T.par(v);
-    if (p >= 0) len += T.h(p) - T.h(v);
+    if (p >= 0) len += T.hw(p) - T.hw(v);
   }
   return len;
 }
@@ -156,7 +160,7 @@ __device__ inline double branch_length_with_data(const ModelDev& m, const TV& T,
     int p = T.par(v);
     if (p >= 0) {
       double up = s;
-      if (up >= 0.0) up += T.h(p) - T.h(v);
+      if (up >= 0.0) up += T.hw(p) - T.h(v);
       if (T.l0(p) == -2.0) T.l0(p) = up; else T.l1(p) = up;
     }
   }
@@ -180,7 +184,7 @@ __device__ inline double prune_likelihood(const ModelDev& m, const TV& T, const 
     }
     int p = T.par(v);
     if (p < 0) { r0 = a0; r1 = a1; continue; }
-    double t = T.h(p) - T.h(v);
+    double t = T.hw(p) - T.h(v);
     double pr = fastexp(-t * m.mu);
     double q = 1 - pr;
     // 1.0 * x == x exactly, so the first child's factor is stored as is and the second multiplies it: (left)*(right)
@@ -226,7 +230,7 @@ __device__ inline void record_recomb_opportunity(const ModelDev& m, const TV& T,
   int e = 0, k = n;
   double lo = 0.0, len = 0.0;
   for (int j = n; j < m.nn; j++) {
-    double hi = T.h(j);
+    double hi = T.hw(j);
     while (e + 1 < E && m.t_start[e + 1] < hi) {
       double b = m.t_start[e + 1];
       if (b > lo) { len += k * (b - lo); lo = b; }
@@ -249,7 +253,7 @@ __device__ inline int epoch_of(const ModelDev& m, double t) {
 
 template <class TV>
 __device__ inline void swap_slots(const ModelDev& m, const TV& T, int a, int b) {
-  double th = T.h(a); T.hw(a) = T.h(b); T.hw(b) = th;
+  double th = T.hw(a); T.hw(a) = T.hw(b); T.hw(b) = th;     // internal slots only
   signed char tp = T.par(a); T.par(a) = T.par(b); T.par(b) = tp;
   for (int v = 0; v < m.nn; v++) {
     int p = T.par(v);
@@ -282,20 +286,20 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
     int p = T.par(v);
     if (p < 0) continue;
     double hv = T.h(v);
-    double bl = T.h(p) - hv;
+    double bl = T.hw(p) - hv;
     b = v; hh = hv + (target - cum);
     if (target < cum + bl) break;
     cum += bl;
   }
   int Pn = T.par(b);
-  if (hh > T.h(Pn)) hh = T.h(Pn);
+  if (hh > T.hw(Pn)) hh = T.hw(Pn);
   int e = epoch_of(m, hh);
   if ((m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_event(e, x);
   // 2. the cut lineage floats upwards (time_interval.cc:84-134, forest.cc:601-696)
   const int root = nn - 1;                 // internal slots are height-sorted
-  const double hroot = T.h(root);
+  const double hroot = T.hw(root);
   int c = n;                               // next internal slot above tt
-  while (c < nn && T.h(c) <= hh) c++;
+  while (c < nn && T.hw(c) <= hh) c++;
   double tt = hh, tc = 0.0;
   int k = 0;
   bool above_root = false;
@@ -309,7 +313,7 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
   for (;;) {
     double tnode = DBL_MAX;
     above_root = !(tt < hroot);
-    if (!above_root) { tnode = T.h(c); k = n - (c - n); }
+    if (!above_root) { tnode = T.hw(c); k = n - (c - n); }
     else k = 1;
     double tep = e + 1 < m.E ? m.t_start[e + 1] : DBL_MAX;
     double tend = tnode < tep ? tnode : tep;
@@ -349,7 +353,7 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
     int Tg = -1;
     for (int v = 0; v < nn; v++) {
       int p = T.par(v);
-      if (p >= 0 && T.h(v) <= tt && tt < T.h(p)) { if (idx == 0) { Tg = v; break; } idx--; }
+      if (p >= 0 && T.h(v) <= tt && tt < T.hw(p)) { if (idx == 0) { Tg = v; break; } idx--; }
     }
     if (Tg == b) {
       // back-coalescence into the stub: tree unchanged (SMC')
@@ -363,8 +367,8 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
     }
   }
   int s = Pn;
-  while (s + 1 < nn && T.h(s + 1) < T.h(s)) { swap_slots(m, T, s, s + 1); s++; }
-  while (s - 1 >= n && T.h(s - 1) > T.h(s)) { swap_slots(m, T, s, s - 1); s--; }
+  while (s + 1 < nn && T.hw(s + 1) < T.hw(s)) { swap_slots(m, T, s, s + 1); s++; }
+  while (s - 1 >= n && T.hw(s - 1) > T.hw(s)) { swap_slots(m, T, s, s - 1); s--; }
 }
 
 // particle.cpp:1195-1254 with multiplicity 1 and one rho segment; forest.h:140-151 for the re-draw after resampling

@@ -477,6 +477,34 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   }
 
   // ---- phase 1: load own state, or pull the parent's after a resampling ---------------------------------------
+  // After a resampling every particle copies its parent's ancestor slot of every pending closed bucket (~150 of them
+  // at the bench shape).  The (epoch, ring slot) pairs are the same for all particles of the launch: they are listed
+  // once per block in shared memory (the per-row accumulators of phase 2 are not in use yet), so that the copy below is
+  // a flat loop with eight independent gathers in flight instead of one dependent load -> store per bucket.
+  int npend = -1;                                             // -1: no list (not resampled, or it does not fit)
+  int* plist = reinterpret_cast<int*>(T.ACC);
+  if (resampled && (size_t)E * P.B * sizeof(int) <= (size_t)E * BS * sizeof(double)) {
+    __shared__ int pl_off[SMC_MAX_EPOCHS + 1];
+    const long long rowc = row < P.R ? row : P.R;
+    const int* ks = P.kstart + rowc * E;
+    const int* ksl = P.kslot + rowc * E;
+    const int* kf = P.kfirst + rowc * E;
+    if (t == 0) {
+      int acc = 0;
+      for (int e = 0; e < E; e++) { pl_off[e] = acc; int cnt = ks[e] - kf[e]; acc += cnt > 0 ? cnt : 0; }
+      pl_off[E] = acc;
+    }
+    __syncthreads();
+    for (int e = t; e < E; e += BS) {
+      int s = ksl[e], o = pl_off[e];
+      for (int k = ks[e] - 1; k >= kf[e]; k--) {
+        if (--s < 0) s = P.B - 1;
+        plist[o++] = e * P.B + s;
+      }
+    }
+    __syncthreads();
+    npend = pl_off[E];
+  }
   double logw = 0.0, next_base = 0.0;
   long long a = i;
   long long dS = 0, dR = 0;      // byte offsets to the parent's owner (0: this rank)
@@ -555,9 +583,9 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       const int* __restrict__ msrc = at_peer(src.map, dR);
       const int self = (int)(P.base + i);
       const size_t NN = (size_t)P.N;
-      for (int e = 0; e < E; e++) {
-        const bool closing = (closes >> e) & 1ull;
-        if constexpr (ST) {
+      if constexpr (ST) {
+        for (int e = 0; e < E; e++) {
+          const bool closing = (closes >> e) & 1ull;
           if (resampled || closing) {
             const double2* o2 = reinterpret_cast<const double2*>(osrc + ((size_t)e * NN + a) * QC);
             double2* d2 = reinterpret_cast<double2*>(dst.open + ((size_t)e * NN + i) * QC);
@@ -580,33 +608,63 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
               for (int c2 = 0; c2 < QC2; c2++) d2[c2] = o2[c2];
             }
           }
-        } else if (resampled || closing) {
-          const double2* o2 = reinterpret_cast<const double2*>(osrc + ((size_t)e * NN + a) * 4);
-          double2 o0 = o2[0], o1 = o2[1];
-          double2* d2 = reinterpret_cast<double2*>(dst.open + ((size_t)e * NN + i) * 4);
-          if (closing) {
-            int s = ksl[e];
-            double2* f2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * 4);
-            f2[0] = o0; f2[1] = o1;
-            dst.map[(size_t)(e * P.B + s) * NN + i] = self;
-            const int kn = P.kstart[(row + 1) * E + e];
-            for (int k = ks[e] + 1; k < kn; k++) {
-              if (++s >= P.B) s = 0;
-              double2* z2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * 4);
-              z2[0] = make_double2(0.0, 0.0); z2[1] = make_double2(0.0, 0.0);
-              dst.map[(size_t)(e * P.B + s) * NN + i] = self;
-            }
-            o0 = make_double2(0.0, 0.0); o1 = o0;
-          }
-          d2[0] = o0; d2[1] = o1;
         }
-        if (resampled) {
+      } else {
+        // four epochs at a time: the loads of a batch are all in flight before the first store
+        for (int e0 = 0; e0 < E; e0 += 4) {
+          double2 o0[4], o1[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const int e = e0 + j;
+            if (e < E && (resampled || ((closes >> e) & 1ull))) {
+              const double2* o2 = reinterpret_cast<const double2*>(osrc + ((size_t)e * NN + a) * 4);
+              o0[j] = o2[0]; o1[j] = o2[1];
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const int e = e0 + j;
+            if (e >= E) continue;
+            const bool closing = (closes >> e) & 1ull;
+            if (!(resampled || closing)) continue;
+            double2* d2 = reinterpret_cast<double2*>(dst.open + ((size_t)e * NN + i) * 4);
+            if (closing) {
+              int s = ksl[e];
+              double2* f2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * 4);
+              f2[0] = o0[j]; f2[1] = o1[j];
+              dst.map[(size_t)(e * P.B + s) * NN + i] = self;
+              const int kn = P.kstart[(row + 1) * E + e];
+              for (int k = ks[e] + 1; k < kn; k++) {
+                if (++s >= P.B) s = 0;
+                double2* z2 = reinterpret_cast<double2*>(P.frozen + ((size_t)(e * P.B + s) * NN + i) * 4);
+                z2[0] = make_double2(0.0, 0.0); z2[1] = make_double2(0.0, 0.0);
+                dst.map[(size_t)(e * P.B + s) * NN + i] = self;
+              }
+              o0[j] = make_double2(0.0, 0.0); o1[j] = o0[j];
+            }
+            d2[0] = o0[j]; d2[1] = o1[j];
+          }
+        }
+      }
+      if (resampled && npend < 0) {
+        for (int e = 0; e < E; e++) {
           int s = ksl[e];
           for (int k = ks[e] - 1; k >= kf[e]; k--) {
             if (--s < 0) s = P.B - 1;
             const size_t at = (size_t)(e * P.B + s) * NN;
             dst.map[at + i] = msrc[at + a];
           }
+        }
+      }
+      if (npend > 0) {
+        const int* __restrict__ ms = msrc + a;
+        int* __restrict__ md = dst.map + i;
+        for (int q0 = 0; q0 < npend; q0 += 8) {
+          int val[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) val[j] = q0 + j < npend ? ms[(size_t)plist[q0 + j] * NN] : 0;
+#pragma unroll
+          for (int j = 0; j < 8; j++) if (q0 + j < npend) md[(size_t)plist[q0 + j] * NN] = val[j];
         }
       }
     }
@@ -616,6 +674,8 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       next_base = draw_next_base(m, tree_length(m, T), rr, c->resample_pos);
     }
   }
+
+  if (npend >= 0) __syncthreads();   // the slot list shares its storage with the accumulators phase 2 is about to zero
 
   // ---- phase 2: the row ----------------------------------------------------------------------------------------
   int nrec = 0;

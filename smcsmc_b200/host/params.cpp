@@ -134,7 +134,7 @@ void parse(int argc, char** argv, Params& P) {
     else if (f == "-delay") { (void)a.next_double(f); }        // only used with -bias_* / -guide (not supported): no effect
     else if (f == "-delay_coal" || f == "-delay_migr") {}
     else if (f == "-ancestral_aware") P.ancestral_aware = true;
-    else if (f == "-dephase") unsupported(f, "dephasing");
+    else if (f == "-dephase") P.dephase = true;
     else if (f == "-apf") { if ((int)a.next_double(f) != 0) unsupported(f, "auxiliary particle filter"); }
     else if (f == "-o") P.out_prefix = a.next(f);
     else if (f == "-log") {}

@@ -37,6 +37,7 @@ struct Params {
   bool calibrate_lag = true;
   double lag_fraction = 2.0;
   bool ancestral_aware = false;
+  bool dephase = false;           // -dephase: heterozygous genotypes are summed over both phasings
   double Ne_cap = 200000;
   bool useCap = false;
   double top_t = 2.0;

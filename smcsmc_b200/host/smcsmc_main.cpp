@@ -134,11 +134,12 @@ void print_help(const Params& P) {
   opt("-xc", "INT", "Epoch or epoch range (e.g. 0-10) to exclude from coalescent EM");
   opt("-cap", "FLT", "Cap on inferred population sizes");
   opt("-ancestral_aware", " ", "Alleles are polarised (0 = ancestral)");
+  opt("-dephase", " ", "Dephase heterozygous sites");
   opt("-record_ess", " ", "Generate *.resample file");
   cout << endl << "Model (scrm syntax): -t THETA  -r RHO LENGTH  -N0 N  -eN T SIZE  -en T POP SIZE  -vb  -seed S" << endl;
   cout << "  -I NPOP n1..nP [M]  -eM T M  -em T i j M  -ema T M11..  -ej T i j  -eps T i j f   (up to 4 populations)" << endl;
   cout << "Not supported by this engine yet (rejected with an error): -es, -eI, -eG (growth), -guide," << endl
-       << "  -bias_heights/-bias_strengths, -apf > 0, -dephase, -arg, -vb together with -I" << endl;
+       << "  -bias_heights/-bias_strengths, -apf > 0, -arg, -vb together with -I" << endl;
 }
 
 // the flattened Model the engine takes: [E] times, [E][P] 1/(2N), [E][P][P] migration rates and fixed-time moves
@@ -427,6 +428,17 @@ int main(int argc, char* argv[]) {
       double s0 = P.start_position + c * chunk_len;
       chunk_start.push_back(s0);
       chunks.push_back(host::read_seg(P.seg_file, P.nsam, chunk_len, (long long)s0, max_seg_len));
+      if (P.dephase) {
+        // -dephase (particleContainer.cpp:138-181): a genotype whose two haplotypes differ is treated as an unphased
+        // heterozygote in the site likelihood, i.e. exactly like the pair "//" (code 2); nothing else reads the phase
+        vector<int8_t>& al = chunks.back().alleles;
+        for (size_t r = 0; r < chunks.back().rows(); r++)
+          for (size_t i = 0; i + 1 < P.nsam; i += 2) {
+            int8_t& a = al[r * P.nsam + i];
+            int8_t& b = al[r * P.nsam + i + 1];
+            if ((a == 0 && b == 1) || (a == 1 && b == 0)) a = b = 2;
+          }
+      }
     }
     // SMCSMC_DEVICE=3 selects one GPU; SMCSMC_DEVICES=0,1,2,3 spreads the chunks of -chunks over several
     vector<int> devices;

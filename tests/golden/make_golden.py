@@ -141,6 +141,29 @@ def golden_tallies():
     np.savez_compressed(os.path.join(HERE, "tallies.npz"), **out)
 
 
+def golden_dephase():
+    """-dephase (particleContainer.cpp:138-181): site likelihoods of the reference with dephase = true on PHASED data, on
+    the trees of prune.npz; the driver implements the flag by recoding differing pairs as unphased hets"""
+    R = _libs.ref()
+    g = np.load(os.path.join(HERE, "prune.npz"))
+    out = {}
+    for n in (4, 8, 16):
+        h = open_ref(n)
+        parent, height, phased = g[f"n{n}_parent"], g[f"n{n}_height"], g[f"n{n}_phased"]
+        nn = 2 * n - 1
+        site = np.zeros(len(parent)); site_aa = np.zeros(len(parent))
+        for t in range(len(parent)):
+            v = ctypes.c_double()
+            par, hei, d = (np.ascontiguousarray(x) for x in (parent[t], height[t], phased[t]))
+            assert R.ref_site_likelihood(h, n, nn, P(par), P(hei), P(d), 0, 1, ctypes.byref(v)) == 0
+            site[t] = v.value
+            assert R.ref_site_likelihood(h, n, nn, P(par), P(hei), P(d), 1, 1, ctypes.byref(v)) == 0
+            site_aa[t] = v.value
+        out[f"n{n}_site_dephase"] = site; out[f"n{n}_site_dephase_aa"] = site_aa
+        R.ref_close(h)
+    np.savez_compressed(os.path.join(HERE, "dephase.npz"), **out)
+
+
 MOMENT_MODELS = {
     # name: (n, scrm demography flags)
     "const4": (4, ""),

@@ -57,7 +57,7 @@ def test_parse_errors(args, message):
 
 @pytest.mark.parametrize("args", [
     ["-es", "0.5", "1", "0.3"], ["-eI", "0.1", "1"], ["-eG", "0", "1"], ["-vb", "-I", "2", "2", "2", "1.0"],
-    ["-guide", "x.gz"], ["-bias_heights", "400"], ["-apf", "1"], ["-dephase"], ["-arg"], ["-sr", "100", "2"],
+    ["-guide", "x.gz"], ["-bias_heights", "400"], ["-apf", "1"], ["-arg"], ["-sr", "100", "2"],
 ])
 def test_unsupported_features_are_rejected_not_ignored(args):
     r = run("-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", "-seg", SEG, *args)

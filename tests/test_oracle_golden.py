@@ -42,6 +42,30 @@ def test_prune_and_branch_lengths(L, n):
         assert nomut == pytest.approx(g[f"n{n}_nomut"][t], rel=1e-12, abs=0)
 
 
+def _dephased(data):
+    """what the driver does for -dephase: a genotype whose two haplotypes differ becomes the unphased pair (2, 2)"""
+    d = np.array(data, copy=True)
+    for i in range(0, len(d) - 1, 2):
+        if d[i] + d[i + 1] == 1 and min(d[i], d[i + 1]) == 0:
+            d[i] = d[i + 1] = 2
+    return d
+
+
+@pytest.mark.parametrize("n", [4, 8, 16])
+def test_dephase(L, n):
+    """-dephase: the reference's likelihoods with dephase = true on phased data (tests/golden/dephase.npz) equal the
+    restatement's with the flag, and equal the plain likelihood of the recoded data -- the driver's implementation"""
+    g, d = np.load(os.path.join(G, "prune.npz")), np.load(os.path.join(G, "dephase.npz"))
+    mu = float(g[f"n{n}_mu"])
+    for t in range(g[f"n{n}_parent"].shape[0]):
+        par, hei = np.ascontiguousarray(g[f"n{n}_parent"][t]), np.ascontiguousarray(g[f"n{n}_height"][t])
+        ph = np.ascontiguousarray(g[f"n{n}_phased"][t])
+        assert L.orc_site_likelihood(n, P(par), P(hei), P(ph), mu, 0, 1) == d[f"n{n}_site_dephase"][t]
+        assert L.orc_site_likelihood(n, P(par), P(hei), P(ph), mu, 1, 1) == d[f"n{n}_site_dephase_aa"][t]
+        re = np.ascontiguousarray(_dephased(ph))
+        assert L.orc_site_likelihood(n, P(par), P(hei), P(re), mu, 0, 0) == d[f"n{n}_site_dephase"][t]
+
+
 def test_reference_example_tree(L):
     """createExampleTree (forest-debug.cc:57): 7 local nodes, tree length 24; allele patterns of
     test/old/unittest/test_FroestState.cpp:135-199 (that test is stale and commented out in the reference; the values
