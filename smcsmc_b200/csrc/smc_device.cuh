@@ -126,11 +126,11 @@ __device__ __forceinline__ TreeViewT<BS> make_tree_view(unsigned char* smem, int
 // forest.h:188 getLocalTreeLength: sum of branch lengths in slot order (the order the parity tests assume)
 template <class TV>
 __device__ inline double tree_length(const ModelDev& m, const TV& T) {
-  // leaves sit at height 0 and always have a parent: their term is h(parent) - 0.0 == h(parent) exactly, so splitting
+  // leaves sit at height 0: their term is h(parent) - 0.0 == h(parent) exactly, so splitting
   // the loop changes no bit and spares the leaf test on every height access
   double len = 0.0;
   const int n = m.n;
-  for (int v = 0; v < n; v++) len += T.hw(T.par(v));
+  for (int v = 0; v < n; v++) { int p = T.par(v); if (p >= 0) len += T.hw(p); }   // p < 0: a tree that failed to join
   for (int v = n; v < m.nn; v++) {
     int p = T.par(v);
     if (p >= 0) len += T.hw(p) - T.hw(v);

@@ -90,7 +90,7 @@ struct StateBuf {
 struct Params {
   ModelDev m;
   SModelDev sm;            // sm.P > 1: structured populations (the <.., true> kernels)
-  int N, B, parity_scan, nblocks;
+  int N, B, parity_scan, nblocks, flat_search;
   uint64_t seed;
   uint32_t chunk, slot_offset;
   double ess_fraction, start_pos;
@@ -303,6 +303,27 @@ __device__ __forceinline__ double u_at(const Ctrl* c, long long j) {
 // parent of offspring j: the first interval i with c_i / norm > u_j (particleContainer.cpp:474-504)
 __device__ __forceinline__ long long parent_of(const Params& P, int p, double uj, double norm, int bs) {
   long long lo = 0, hi = P.N;   // count of i with c_i/norm <= uj
+  if (!P.parity_scan && !P.flat_search) {
+    // two levels: c is non-decreasing and capped by boff[b+1] inside block b, so the block that holds the answer is
+    // the first b with boff[b+1]/norm > uj -- found in the small (cache-resident) offset array -- and only the search
+    // inside that block touches the per-particle prefixes.  Same answer as the flat search.
+    int bl = 0, bh = P.nblocks;
+    while (bl < bh) {
+      int mid = (bl + bh) >> 1;
+      if (P.boff[p][mid + 1] / norm > uj) bh = mid; else bl = mid + 1;
+    }
+    if (bl >= P.nblocks) return P.N - 1;
+    // everything before block bl fails the test and the first element after it passes (its c is >= boff[bl+1]), so the
+    // flat search's answer lies in [start of bl, end of bl] -- the end itself only if rounding left the block's last
+    // prefix a hair under boff[bl+1]
+    lo = (long long)bl * bs;
+    hi = lo + bs < P.N ? lo + bs : P.N;
+    while (lo < hi) {
+      long long mid = (lo + hi) >> 1;
+      if (cum_at(P, p, mid, bs) / norm > uj) hi = mid; else lo = mid + 1;
+    }
+    return lo < P.N ? lo : P.N - 1;
+  }
   while (lo < hi) {
     long long mid = (lo + hi) >> 1;
     if (cum_at(P, p, mid, bs) / norm > uj) hi = mid; else lo = mid + 1;
@@ -1357,6 +1378,7 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   if (const char* s = getenv("SMC_BLOCK")) { int b = atoi(s); if (b == 32 || b == 64 || b == 128) e->BS = b; }   // tuning knob
   P.nblocks = (cfg->N + e->BS - 1) / e->BS;
   e->smem = tree_smem(P.m.nn, P.m.E, e->BS);
+  if (getenv("SMC_FLAT_SEARCH")) P.flat_search = 1;   // tests: the one-level parent search the two-level one must reproduce
   if (const char* s = getenv("SMC_EXTRA_SMEM")) e->smem += (size_t)atoi(s);                                       // occupancy experiments
   cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
   if (ce != cudaSuccess) { delete e; return fail(SMC_ERR_CUDA, cudaGetErrorString(ce)); }

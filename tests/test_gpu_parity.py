@@ -306,6 +306,30 @@ def test_blocked_scan_mode_matches_parity_mode(S):
     assert out[0][3] == out[1][3]
 
 
+def test_two_level_parent_search_equals_flat_search(S, monkeypatch):
+    """production mode finds an offspring's parent by a search over block offsets followed by a search inside one
+    block; SMC_FLAT_SEARCH=1 selects the plain binary search over all particles it must reproduce: identical
+    ancestry, trees and weights (20 000 particles = 157 blocks, many resampling events)"""
+    n, N = 4, 20000
+    t_start, inv2N, lags = [0.0, 4000.0, 20000.0], [1 / 2e4, 1 / 8e3, 1 / 3e4], [3000.0, 1500.0, 800.0]
+    R, seqlen = 60, 30000.0
+    x_end, al, is_site = _rows(n, R, seqlen, seed=21)
+    out = []
+    for flat in (False, True):
+        if flat:
+            monkeypatch.setenv("SMC_FLAT_SEARCH", "1")
+        pf = S.ParticleFilter(n, N, t_start, inv2N, 2.5e-8, 1e-8, seqlen, lags, seed=5, ess_fraction=0.9)
+        pf.upload_rows(x_end, al, is_site)
+        pf.init_particles()
+        pf.sweep()
+        out.append((pf.last_ancestry(), pf.particles(), pf.counters()))
+        pf.close()
+    assert out[0][2]["resamples"] > 10 and out[0][2] == out[1][2]
+    assert np.array_equal(out[0][0], out[1][0])
+    for a, b in zip(out[0][1], out[1][1]):
+        assert np.array_equal(a, b)
+
+
 def test_large_population_properties(S):
     """size-independent properties at a BASELINE-scale particle count (n=8, N=100k): weights normalised, trees valid
     (height-sorted binary trees), resampling ancestry monotone, opportunity tallies positive and consistent"""
