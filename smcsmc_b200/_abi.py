@@ -63,7 +63,8 @@ SYMBOLS = {
 
 
 def lib_path():
-    return os.path.join(HERE, "lib", "libsmcgpu.so")
+    # SMCSMC_B200_LIB: another build of the same library (kernel experiments); never a fallback
+    return os.environ.get("SMCSMC_B200_LIB") or os.path.join(HERE, "lib", "libsmcgpu.so")
 
 
 def lib():

@@ -30,7 +30,15 @@ struct Rng {
   int have;
 };
 
-__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+// One out-of-line copy of the Philox rounds and of the fp64 logarithm: the row kernel calls them from half a dozen
+// places; out of line the kernel needs 96 instead of 122 registers (5 instead of 4 blocks of 128 per SM) and is ~5 %
+// faster end to end (profiles/r1_row_kernel_summary.md).  -DSMC_INLINE_MATH restores the inlined build.
+#if defined(__CUDA_ARCH__) && !defined(SMC_INLINE_MATH)
+#define SMC_RNG_ATTR __noinline__
+#else
+#define SMC_RNG_ATTR inline
+#endif
+__host__ __device__ SMC_RNG_ATTR void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
                                               uint32_t k1, uint32_t out[4]) {
 #pragma unroll
   for (int round = 0; round < 10; round++) {
@@ -67,10 +75,31 @@ __host__ __device__ inline double rng_uniform(Rng& r) {
   return u53(o[0], o[1]);
 }
 
+// one out-of-line copy of the fp64 logarithm for the hot loop (the inlined expansion is ~100 instructions per call site)
+#ifndef SMC_INLINE_MATH
+__device__ __noinline__ double dlog(double x) { return log(x); }
+#else
+__device__ __forceinline__ double dlog(double x) { return log(x); }
+#endif
+#ifdef SMC_NOINLINE_EXP
+__device__ __noinline__ double dexp(double x) { return exp(x); }
+#else
+__device__ __forceinline__ double dexp(double x) { return exp(x); }
+#endif
+
 // particle.cpp:30-40 -- continued-fraction exp; same rational expression, no contraction
 __host__ __device__ inline double fastexp(double x) {
   double xx = x * x;
   if (xx < 0.516167859) return 1 + 2 * x / (2 - x + xx / (6 + xx * 0.1));
+  return exp(x);
+}
+// The same function with the two divisions folded into one: 1 + 2x(6 + 0.1xx) / ((2 - x)(6 + 0.1xx) + xx).  Differs from
+// fastexp in the last bits only (a few 1e-16 relative); used for the 2n-2 branch factors of the pruning pass, whose
+// parity bar against the reference is 1e-12 relative (tests/test_gpu_parity.py).  The no-mutation factor and the
+// stand-alone entry point keep the reference's exact expression.
+__host__ __device__ inline double fastexp1(double x) {
+  double xx = x * x;
+  if (xx < 0.516167859) { double d = 6 + xx * 0.1; return 1 + 2 * x * d / ((2 - x) * d + xx); }
   return exp(x);
 }
 
@@ -185,7 +214,7 @@ __device__ inline double prune_likelihood(const ModelDev& m, const TV& T, const 
     int p = T.par(v);
     if (p < 0) { r0 = a0; r1 = a1; continue; }
     double t = T.hw(p) - T.h(v);
-    double pr = fastexp(-t * m.mu);
+    double pr = fastexp1(-t * m.mu);
     double q = 1 - pr;
     // 1.0 * x == x exactly, so the first child's factor is stored as is and the second multiplies it: (left)*(right)
     T.l0(p) = T.l0(p) * (a0 * pr + a1 * q);
@@ -309,7 +338,7 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
   // ONE unit exponential for the whole float: an interval of length d at rate r uses up r * d of it, the lineage
   // coalesces in the interval in which it runs out (memoryless, the same law as a fresh draw per interval; the reference
   // re-uses its unit exponential the same way, random_generator.cc:32-78)
-  double ex = -log(rng_uniform(r));
+  double ex = -dlog(rng_uniform(r));
   for (;;) {
     double tnode = DBL_MAX;
     above_root = !(tt < hroot);
@@ -374,7 +403,7 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
 // particle.cpp:1195-1254 with multiplicity 1 and one rho segment; forest.h:140-151 for the re-draw after resampling
 __device__ inline double draw_next_base(const ModelDev& m, double tree_len, Rng& r, double from) {
   double rate = m.rho * tree_len;
-  double len = -log(rng_uniform(r)) / rate;
+  double len = -dlog(rng_uniform(r)) / rate;
   double next = from + len;
   if (next == from) next = nextafter(from, from * 2);
   if (!(next < m.seqlen)) next = m.seqlen;
@@ -403,7 +432,7 @@ __device__ inline int extend_row(const ModelDev& m, const TV& T, Rng& r, double 
     L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
     if (moved) next_base = draw_next_base(m, tl, r, updated_to);
     double new_to = x1 < next_base ? x1 : next_base;
-    logw += log(fastexp(-m.mu * L_obs * (new_to - updated_to)));     // particle.cpp:770
+    logw += dlog(fastexp(-m.mu * L_obs * (new_to - updated_to)));     // particle.cpp:770
     record_recomb_opportunity(m, T, sink, updated_to, new_to, max_rec_epoch);
     updated_to = new_to;
     moved = false;
@@ -415,7 +444,7 @@ __device__ inline int extend_row(const ModelDev& m, const TV& T, Rng& r, double 
     }
   }
   sink.row_end();
-  if (is_site) logw += log(site_likelihood(m, T, data));
+  if (is_site) logw += dlog(site_likelihood(m, T, data));
   return nrec;
 }
 

@@ -141,12 +141,13 @@ __device__ __forceinline__ Tp* at_peer(Tp* p, long long delta) {
 }
 
 // the frozen record (4 doubles) of closed bucket (e, slot s) that belongs to particle i's ancestor
+template <bool SH>
 __device__ __forceinline__ void load_frozen(const Params& P, const int* map, int e, int s, long long i, double out[4]) {
   const size_t es = (size_t)(e * P.B + s);
   const int m = map[es * P.N + i];
   const double* f = P.frozen;
   long long l = m;
-  if (P.world > 1) { const int r = m / P.N; l = m - r * P.N; f = at_peer(f, P.peer_tally[r]); }
+  if constexpr (SH) { const int r = m / P.N; l = m - r * P.N; f = at_peer(f, P.peer_tally[r]); }
   const double2* c2 = reinterpret_cast<const double2*>(f + (es * P.N + l) * 4);
   double2 a = c2[0], b = c2[1];
   out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
@@ -407,17 +408,24 @@ __device__ __forceinline__ STreeViewT<BS> tree_view_of(const Params& P, unsigned
 }
 
 // pointer to the frozen record (Q doubles) of closed bucket (e, slot s) that belongs to particle i's ancestor
+template <bool SH>
 __device__ __forceinline__ const double* frozen_record(const Params& P, const int* map, int e, int s, long long i, int Q) {
   const size_t es = (size_t)(e * P.B + s);
   const int m = map[es * P.N + i];
   const double* f = P.frozen;
   long long l = m;
-  if (P.world > 1) { const int r = m / P.N; l = m - r * P.N; f = at_peer(f, P.peer_tally[r]); }
+  if constexpr (SH) { const int r = m / P.N; l = m - r * P.N; f = at_peer(f, P.peer_tally[r]); }
   return f + (es * P.N + l) * Q;
 }
 
-template <int BS, bool ST>
-__global__ void __launch_bounds__(BS)
+// SH: the population is sharded over ranks (smc_shard_attach); the single-GPU instantiation carries none of that code
+#ifdef SMC_MINBLOCKS
+#define SMC_ROW_BOUNDS __launch_bounds__(BS, SMC_MINBLOCKS)     // occupancy experiments
+#else
+#define SMC_ROW_BOUNDS __launch_bounds__(BS)
+#endif
+template <int BS, bool ST, bool SH>
+__global__ void SMC_ROW_BOUNDS
 smc_row_kernel(const __grid_constant__ Params P, int mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int t = threadIdx.x;
@@ -450,13 +458,13 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     // at most one bucket per epoch falls due per row; the per-warp sums of all of them are staged in the (still
     // unused) tree area and handed to the global tallies with one pass
     double* scr = reinterpret_cast<double*>(smem_raw);           // [c1 - c0][6][nwarp]  (structured: [..][2Q][nwarp])
-    const double w = live ? exp(src.logw[i] - lse) : 0.0;
+    const double w = live ? dexp(src.logw[i] - lse) : 0.0;
     const double w2 = w * w;
     if constexpr (ST) {
       // every cell is summed with w and with w^2: rows [0, QC) and [QC, 2Q) of the tallies
       for (int q = c0; q < c1; q++) {
         int2 ek = P.cons[q];
-        const double* fr = live ? frozen_record(P, src.map, ek.x, ek.y % P.B, i, QC) : nullptr;
+        const double* fr = live ? frozen_record<SH>(P, src.map, ek.x, ek.y % P.B, i, QC) : nullptr;
         for (int a = 0; a < QC; a++) {
           const double f = live ? fr[a] : 0.0;
           const double v0 = warp_sum(w * f), v1 = warp_sum(w2 * f);
@@ -478,7 +486,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
         double v[6] = {0, 0, 0, 0, 0, 0};
         if (live) {
           double f[4];
-          load_frozen(P, src.map, ek.x, ek.y % P.B, i, f);
+          load_frozen<SH>(P, src.map, ek.x, ek.y % P.B, i, f);
           v[0] = w * f[0]; v[1] = w * f[1]; v[2] = w2 * f[1]; v[3] = w * f[2]; v[4] = w * f[3]; v[5] = w2 * f[3];
         }
 #pragma unroll
@@ -535,7 +543,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       const double norm = c->norm;
       // did the parent get more than one offspring?  (then every copy re-draws its next recombination position,
       // particleContainer.cpp:357-367 / forest.h:140-151)
-      if (P.world == 1) {
+      if constexpr (!SH) {
         double uj = u_at(c, i);
         a = parent_of(P, pprev, uj, norm, BS);
         if (i > 0) {
@@ -739,7 +747,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   __syncthreads();
   mx = red[0][0];
   for (int w = 1; w < nwarp; w++) mx = fmax(mx, red[0][w]);
-  double ex = live ? exp(logw - mx) : 0.0;
+  double ex = live ? dexp(logw - mx) : 0.0;
   double incl = ex;
   for (int o = 1; o < 32; o <<= 1) {
     double y = __shfl_up_sync(0xffffffffu, incl, o);
@@ -786,7 +794,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   for (int w = 1; w < nwarp; w++) gm = fmax(gm, red[0][w]);
   double S = 0.0, Q = 0.0;
   for (int b = t; b < nb; b += BS) {
-    double f = exp(__ldcg(P.bmax[pnow] + b) - gm);
+    double f = dexp(__ldcg(P.bmax[pnow] + b) - gm);
     S += __ldcg(P.bsum[pnow] + b) * f;
     Q += __ldcg(P.bsq[pnow] + b) * f * f;
   }
@@ -796,7 +804,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   __syncthreads();
   S = 0.0; Q = 0.0;
   for (int w = 0; w < nwarp; w++) { S += red[1][w]; Q += red[2][w]; }
-  const bool sharded = P.world > 1;
+  constexpr bool sharded = SH;
   const double new_lse = gm + log(S);
   const double ess = S * S / Q;
   // a sharded rank scales its partials by its own maximum only: peers read them before the global normaliser is known
@@ -806,7 +814,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   const int b0 = t * per, b1 = min(nb, b0 + per);
   double run = 0.0;
   for (int b = b0; b < b1; b++) {
-    double sc = exp(__ldcg(P.bmax[pnow] + b) - ref);
+    double sc = dexp(__ldcg(P.bmax[pnow] + b) - ref);
     P.bscale[pnow][b] = sc;
     run += __ldcg(P.bsum[pnow] + b) * sc;
   }
@@ -898,7 +906,7 @@ __global__ void __launch_bounds__(128) smc_flush_kernel(const __grid_constant__ 
       for (int k = first_pending[e]; k < nbk; k++) {
         double f[4];
         if (k < nbk - 1) {
-          load_frozen(P, src.map, e, k % P.B, i, f);
+          if (P.world > 1) load_frozen<true>(P, src.map, e, k % P.B, i, f); else load_frozen<false>(P, src.map, e, k % P.B, i, f);
         } else {
           const double2* o2 = reinterpret_cast<const double2*>(src.open + ((size_t)e * P.N + i) * 4);
           double2 a = o2[0], b = o2[1];
@@ -934,7 +942,7 @@ __global__ void __launch_bounds__(128) smc_flush_struct_kernel(const __grid_cons
       double f = 0.0;
       if (live)
         for (int k = first_pending[e]; k < nbk; k++)
-          f += k < nbk - 1 ? frozen_record(P, src.map, e, k % P.B, i, Q)[a] : src.open[((size_t)e * P.N + i) * Q + a];
+          f += k < nbk - 1 ? frozen_record<false>(P, src.map, e, k % P.B, i, Q)[a] : src.open[((size_t)e * P.N + i) * Q + a];
       const double v0 = warp_sum(w * f), v1 = warp_sum(w * w * f);
       if (lane == 0) { tal[0][warp] = v0; tal[1][warp] = v1; }
       __syncthreads();
@@ -1324,15 +1332,21 @@ int launch_row(smc_engine* e, int mode) {
   int nb = e->P.nblocks;
   if (e->P.sm.P > 1) {
     switch (e->BS) {
-      case 32: smc_row_kernel<32, true><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
-      case 64: smc_row_kernel<64, true><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
-      default: smc_row_kernel<128, true><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+      case 32: smc_row_kernel<32, true, false><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
+      case 64: smc_row_kernel<64, true, false><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+      default: smc_row_kernel<128, true, false><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+    }
+  } else if (e->P.world > 1) {
+    switch (e->BS) {
+      case 32: smc_row_kernel<32, false, true><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
+      case 64: smc_row_kernel<64, false, true><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+      default: smc_row_kernel<128, false, true><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
     }
   } else {
     switch (e->BS) {
-      case 32: smc_row_kernel<32, false><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
-      case 64: smc_row_kernel<64, false><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
-      default: smc_row_kernel<128, false><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+      case 32: smc_row_kernel<32, false, false><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
+      case 64: smc_row_kernel<64, false, false><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+      default: smc_row_kernel<128, false, false><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
     }
   }
   e->launches++;
@@ -1385,13 +1399,21 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   cudaEventCreate(&e->ev0); cudaEventCreate(&e->ev1);
   // opt in to the full 227 KB once (the attribute is per function, not per engine)
   if (e->smem > 230400) { smc_destroy(e); return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has"); }
-  ce = cudaFuncSetAttribute(smc_row_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  ce = cudaFuncSetAttribute(smc_row_kernel<32, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (const char* cv = getenv("SMC_CARVEOUT")) {   // tuning knob: shared-memory share of the 256 KB L1/shared array, in percent
+    const int pct = atoi(cv);
+    if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  }
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
   const size_t N = cfg->N;
