@@ -1178,6 +1178,10 @@ struct smc_engine {
   std::vector<size_t> alloc_bytes;
   bool rows_ready = false, inited = false, finished = false;
   long long swept = 0;
+  // GRAPH_ROWS consecutive row launches as one CUDA graph: the launches of a sweep are identical (the row index lives in
+  // the device control block), so the graph is captured once and replayed; rebuilt when a parameter changed
+  cudaGraphExec_t row_graph = nullptr;
+  bool graph_dirty = true;
   std::vector<int> first_pending_h;     // per epoch: number of buckets the regular schedule consumes
   int* first_pending_d = nullptr;
   // particle sharding
@@ -1353,6 +1357,34 @@ int launch_row(smc_engine* e, int mode) {
   return 0;
 }
 
+// `count` consecutive rows of an unsharded engine: batches of GRAPH_ROWS through the captured graph (one host call per
+// batch instead of one ~11 us launch per row -- the host launch rate bounds small populations), the rest directly
+constexpr int GRAPH_ROWS = 32;
+int launch_rows(smc_engine* e, int64_t count) {
+  static const bool no_graph = getenv("SMC_NO_GRAPH") != nullptr;
+  if (!no_graph && count >= GRAPH_ROWS) {
+    if (!e->row_graph || e->graph_dirty) {
+      if (e->row_graph) { cudaGraphExecDestroy(e->row_graph); e->row_graph = nullptr; }
+      cudaGraph_t g = nullptr;
+      const long long before = e->launches;
+      CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+      for (int k = 0; k < GRAPH_ROWS; k++) launch_row(e, 0);
+      CUDA_TRY(cudaStreamEndCapture(e->stream, &g));
+      e->launches = before;
+      cudaError_t ce = cudaGraphInstantiate(&e->row_graph, g, 0);
+      cudaGraphDestroy(g);
+      if (ce != cudaSuccess) { e->row_graph = nullptr; return fail(SMC_ERR_CUDA, cudaGetErrorString(ce)); }
+      e->graph_dirty = false;
+    }
+    for (; count >= GRAPH_ROWS; count -= GRAPH_ROWS) {
+      CUDA_TRY(cudaGraphLaunch(e->row_graph, e->stream));
+      e->launches += GRAPH_ROWS;
+    }
+  }
+  for (; count > 0; count--) launch_row(e, 0);
+  return 0;
+}
+
 int materialise(smc_engine* e) {
   launch_row(e, 1);
   smc_commit_kernel<<<1, 1, 0, e->stream>>>(e->P.ctrl);
@@ -1466,6 +1498,7 @@ void smc_destroy(smc_engine* e) {
   if (!e) return;
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  if (e->row_graph) cudaGraphExecDestroy(e->row_graph);
   for (void* p : e->peer_maps) cudaIpcCloseMemHandle(p);
   if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
   const bool shared = e->comm != nullptr;        // peers hold IPC mappings of this engine's slabs: really free them
@@ -1489,6 +1522,7 @@ int smc_shard_unique_id(uint8_t id[128]) {
 }
 
 int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t id[128]) {
+  if (e) e->graph_dirty = true;
   if (!e || !id) return fail(SMC_ERR_ARG, "null argument");
   if (world < 2 || world > SMC_MAX_RANKS || rank < 0 || rank >= world) return fail(SMC_ERR_ARG, "rank/world out of range (2..8 ranks)");
   if (e->rows_ready || e->inited) return fail(SMC_ERR_STATE, "attach the shard before uploading rows");
@@ -1515,6 +1549,7 @@ int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t i
 
 int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const double* mig, const double* single_mig,
                         const int32_t* leaf_pop, int32_t max_marks) {
+  if (e) e->graph_dirty = true;
   if (!e || !inv2N || !leaf_pop) return fail(SMC_ERR_ARG, "null argument");
   if (npop < 2 || npop > SMC_MAX_POPULATIONS) return fail(SMC_ERR_ARG, "populations must be in 2..4");
   Params& P = e->P;
@@ -1626,6 +1661,7 @@ int smc_get_population_state(smc_engine* e, int32_t* pop, int32_t* nmarks, int32
 
 int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, const uint8_t* is_site,
                     const int32_t* max_rec_epoch, int64_t R) {
+  if (e) e->graph_dirty = true;
   if (!e || !x_end || !alleles || !is_site) return fail(SMC_ERR_ARG, "null argument");
   if (R < 1) return fail(SMC_ERR_ARG, "R must be >= 1");
   if (e->rows_ready) return fail(SMC_ERR_STATE, "rows already uploaded");
@@ -1759,6 +1795,7 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
 }
 
 int smc_init_particles(smc_engine* e) {
+  if (e) e->graph_dirty = true;
   if (!e) return fail(SMC_ERR_ARG, "null engine");
   if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows before initialising particles");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
@@ -1782,7 +1819,8 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   cudaEventRecord(e->ev0, e->stream);
   if (e->P.world == 1) {
-    for (int64_t r = row_begin; r < row_end; r++) launch_row(e, 0);
+    int rc = launch_rows(e, row_end - row_begin);
+    if (rc) return rc;
   } else {
     // sharded: row kernel (rank-local partials) -> exchange of the ranks' summaries -> commit (identical on all ranks).
     // The exchange is also what orders a rank's writes against its peers' pulls.
@@ -1830,8 +1868,10 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
       smc_engine* e = engines[k];
       if (e->swept >= e->P.R) continue;
       CUDA_TRY(cudaSetDevice(e->cfg.device));
-      int64_t stop = std::min<int64_t>(e->P.R, e->swept + rows_per_turn);
-      for (int64_t r = e->swept; r < stop; r++) launch_row(e, 0);
+      // a turn is at least one graph batch; the streams keep the chunks concurrent on the device either way
+      int64_t stop = std::min<int64_t>(e->P.R, e->swept + std::max<int64_t>(rows_per_turn, GRAPH_ROWS));
+      int rc = launch_rows(e, stop - e->swept);
+      if (rc) return rc;
       e->swept = stop;
       if (e->swept < e->P.R) more = true;
     }
@@ -1860,6 +1900,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
 }
 
 int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_logfac, uint64_t seed) {
+  if (e) e->graph_dirty = true;
   if (!e) return fail(SMC_ERR_ARG, "null engine");
   if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows first");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
@@ -2001,6 +2042,7 @@ int smc_get_particles(smc_engine* e, int32_t* parent, double* height, double* lo
 
 int smc_set_particles(smc_engine* e, const int32_t* parent, const double* height, const double* logw,
                       const double* next_base) {
+  if (e) e->graph_dirty = true;
   if (!e || !parent || !height || !logw || !next_base) return fail(SMC_ERR_ARG, "null argument");
   if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows first");
   if (e->swept != 0) return fail(SMC_ERR_STATE, "set_particles only before the first row");

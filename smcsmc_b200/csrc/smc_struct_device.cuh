@@ -171,6 +171,13 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
   const double hroot = T.h(root);
   double tt = t0;
   int pf = pop0, pr = T.pop(root), e = epoch_of(m, tt);
+  // branches that carry marks: only those need the mark pool to tell their population at a given time (the marks this
+  // sweep adds belong to the two floating lineages, which are not branches of the tree yet)
+  unsigned long long marked = 0ull;
+  {
+    const int nm0 = T.nm();
+    for (int q = 0; q < nm0; q++) { const int mb = T.mb(q); if (mb >= 0) marked |= 1ull << mb; }
+  }
   for (;;) {
     const bool above = !(tt < hroot);
     int k = 0;
@@ -182,7 +189,7 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
         double hv = T.h(v);
         if (v >= n && hv > tt && hv < tend) tend = hv;
         int p = T.par(v);
-        if (p >= 0 && hv <= tt && tt < T.h(p) && s_pop_at(T, v, tt) == pf) k++;
+        if (p >= 0 && hv <= tt && tt < T.h(p) && (((marked >> v) & 1ull) ? s_pop_at(T, v, tt) : (int)T.pop(v)) == pf) k++;
       }
       const int nm = T.nm();
       for (int q = 0; q < nm; q++) { double mt = T.mt(q); if (mt > tt && mt < tend) tend = mt; }
@@ -228,7 +235,7 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
           if (!((present >> v) & 1ull)) continue;
           int p = T.par(v);
           if (p < 0) continue;
-          if (T.h(v) <= ts && ts < T.h(p) && s_pop_at(T, v, ts) == pf) { if (idx == 0) { target = v; return tt; } idx--; }
+          if (T.h(v) <= ts && ts < T.h(p) && (((marked >> v) & 1ull) ? s_pop_at(T, v, ts) : (int)T.pop(v)) == pf) { if (idx == 0) { target = v; return tt; } idx--; }
         }
         target = -2;                                     // cannot happen
         return tt;

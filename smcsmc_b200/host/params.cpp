@@ -49,8 +49,14 @@ Epoch& epoch_at(Params& P, double t) {
   return P.epochs[pos];
 }
 
+// Populations exist in command-line order: -I declares the first ones, every -es adds one (Model::addPopulation,
+// model.cc:672-686).  Tables are sized for the final number from the start; an option that addresses "all populations"
+// touches the ones declared so far and leaves the later ones as "not given" (NaN), which is what scrm's
+// addPopToVectorList / addPopToMatrixList produce.
+int g_cur_pops = 1;
+
 void check_pop(const Params& P, int pop, const std::string& flag) {
-  if (pop < 0 || pop >= P.npop) throw std::invalid_argument("Invalid population in option " + flag);
+  if (pop < 0 || pop >= g_cur_pops) throw std::invalid_argument("Invalid population in option " + flag);
 }
 
 // Model::addPopulationSizes / addPopulationSize (model.cc:202-281); pop < 0: all populations
@@ -58,8 +64,9 @@ void add_size_change(Params& P, double t_scaled, int pop, double rel_size, doubl
   if (!(rel_size * P.N0 > 0.0)) throw std::invalid_argument("population size <= 0");
   Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
   if (pop < 0) {
-    e.pop_size.assign(P.npop, rel_size * P.N0);
-    e.vb_count.assign(P.npop, count);
+    e.pop_size.assign(P.npop, kNaN);
+    e.vb_count.assign(P.npop, kNaN);
+    for (int p = 0; p < g_cur_pops; p++) { e.pop_size[p] = rel_size * P.N0; e.vb_count[p] = count; }
   } else {
     if (e.pop_size.empty()) { e.pop_size.assign(P.npop, kNaN); e.vb_count.assign(P.npop, kNaN); }
     e.pop_size[pop] = rel_size * P.N0;
@@ -70,7 +77,10 @@ void add_size_change(Params& P, double t_scaled, int pop, double rel_size, doubl
 // Model::addMigrationRates / addMigrationRate / addSymmetricMigration (model.cc:370-459); M = 4 N0 m
 void add_mig_all(Params& P, double t_scaled, double M) {
   Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
-  e.mig.assign((size_t)P.npop * P.npop, std::isnan(M) ? kNaN : M / (4 * P.N0));
+  e.mig.assign((size_t)P.npop * P.npop, kNaN);
+  if (!std::isnan(M))
+    for (int i = 0; i < g_cur_pops; i++)
+      for (int j = 0; j < g_cur_pops; j++) e.mig[(size_t)i * P.npop + j] = M / (4 * P.N0);
 }
 void add_mig_one(Params& P, double t_scaled, int i, int j, double M) {
   Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
@@ -151,11 +161,15 @@ void parse(int argc, char** argv, Params& P) {
     if (scrm[k] == "-N0") P.N0 = to_double(scrm[k + 1], "-N0");
   // -I fixes the number of populations; every table row is sized by it, so it is read ahead of the other options
   // (scrm itself needs -I to come first for the same reason, param.cc:148-160)
+  g_cur_pops = 1;
   for (size_t k = 0; k + 1 < scrm.size(); k++)
     if (scrm[k] == "-I") {
       P.npop = (int)to_double(scrm[k + 1], "-I");
-      if (P.npop < 1 || P.npop > 4) throw std::invalid_argument("-I: the B200 engine takes 1 to 4 populations");
+      if (P.npop < 1) throw std::invalid_argument("Failed to parse option: -I");
+      g_cur_pops = P.npop;
     }
+  for (const std::string& f : scrm) if (f == "-es") P.npop++;      // every admixture event adds a population
+  if (P.npop > 4) throw std::invalid_argument("-I / -es: the B200 engine takes 1 to 4 populations");
   {
     Epoch e0;
     e0.t_start = 0.0;
@@ -216,7 +230,7 @@ void parse(int argc, char** argv, Params& P) {
     else if (f == "-I") {
       (void)s.next(f);
       P.leaf_pop.clear();
-      for (int p = 0; p < P.npop; p++) {
+      for (int p = 0; p < g_cur_pops; p++) {
         int cnt = (int)s.next_double(f);
         if (cnt < 0) throw std::invalid_argument("Failed to parse option: -I");
         for (int k = 0; k < cnt; k++) P.leaf_pop.push_back(p);
@@ -227,22 +241,22 @@ void parse(int argc, char** argv, Params& P) {
         double M = std::strtod(s.v[s.i + 1].c_str(), &end);
         if (end != s.v[s.i + 1].c_str() && *end == '\0') {
           s.i++;
-          if (P.npop > 1) { add_mig_all(P, 0.0, M / (P.npop - 1)); if (M > 0) P.has_migration = true; }
+          if (g_cur_pops > 1) { add_mig_all(P, 0.0, M / (g_cur_pops - 1)); if (M > 0) P.has_migration = true; }
         }
       }
     }
     else if (f == "-ma" || f == "-ema") {
       double t = time_of(f, f == "-ema");
       std::vector<double> M((size_t)P.npop * P.npop, 0.0);
-      for (int i = 0; i < P.npop; i++)
-        for (int j = 0; j < P.npop; j++) {
+      for (int i = 0; i < g_cur_pops; i++)
+        for (int j = 0; j < g_cur_pops; j++) {
           if (i == j) { (void)s.next(f); if (P.vb) (void)s.next(f); continue; }
           M[(size_t)i * P.npop + j] = s.next_double(f);
           if (P.vb) (void)s.next_double(f);
         }
       add_mig_all(P, t, 0.0);
-      for (int i = 0; i < P.npop; i++)
-        for (int j = 0; j < P.npop; j++)
+      for (int i = 0; i < g_cur_pops; i++)
+        for (int j = 0; j < g_cur_pops; j++)
           if (i != j) { add_mig_one(P, t, i, j, M[(size_t)i * P.npop + j]); if (M[(size_t)i * P.npop + j] > 0) P.has_migration = true; }
     }
     else if (f == "-m" || f == "-em") {
@@ -254,8 +268,8 @@ void parse(int argc, char** argv, Params& P) {
     }
     else if (f == "-M" || f == "-eM") {
       double t = time_of(f, f == "-eM");
-      if (P.npop < 2) throw std::invalid_argument(f + " needs more than one population (-I)");
-      double M = s.next_double(f) / (P.npop - 1);
+      if (g_cur_pops < 2) throw std::invalid_argument(f + " needs more than one population (-I)");
+      double M = s.next_double(f) / (g_cur_pops - 1);
       if (P.vb) (void)s.next_double(f);
       add_mig_all(P, t, M);
       if (M > 0) P.has_migration = true;
@@ -265,7 +279,7 @@ void parse(int argc, char** argv, Params& P) {
       min_time = t;
       int i = next_pop(f), j = next_pop(f);
       add_single_mig(P, t, i, j, 1.0);
-      for (int k = 0; k < P.npop; k++)
+      for (int k = 0; k < g_cur_pops; k++)
         if (k != i) add_mig_one(P, t, k, i, 0.0);               // nobody migrates into the dissolved population
     }
     else if (f == "-eps") {
@@ -277,7 +291,16 @@ void parse(int argc, char** argv, Params& P) {
       if (fraction > 1.0) throw std::invalid_argument("Probability in `-eps` argument greater than one.");
       add_single_mig(P, t, i, j, 1 - fraction);
     }
-    else if (f == "-es") unsupported(f, "admixture into a new population");
+    else if (f == "-es") {                                      // param.cc:299-317: admixture into a NEW population
+      double t = time_of(f, true);
+      min_time = t;
+      int i = next_pop(f);
+      double fraction = s.next_double(f);
+      if (fraction < 0.0) throw std::invalid_argument("Probability in `-es` argument is negative.");
+      if (fraction > 1.0) throw std::invalid_argument("Probability in `-es` argument greater than one.");
+      const int fresh = g_cur_pops++;
+      add_single_mig(P, t, i, fresh, 1 - fraction);
+    }
     else if (f == "-eI") unsupported(f, "ancient samples");
     else if (f == "-G" || f == "-eG" || f == "-g" || f == "-eg") unsupported(f, "exponential growth");
     else if (f == "-bias_heights" || f == "-bias_strengths") unsupported(f, "biased recombination sampling");

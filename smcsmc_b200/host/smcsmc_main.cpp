@@ -137,8 +137,8 @@ void print_help(const Params& P) {
   opt("-dephase", " ", "Dephase heterozygous sites");
   opt("-record_ess", " ", "Generate *.resample file");
   cout << endl << "Model (scrm syntax): -t THETA  -r RHO LENGTH  -N0 N  -eN T SIZE  -en T POP SIZE  -vb  -seed S" << endl;
-  cout << "  -I NPOP n1..nP [M]  -eM T M  -em T i j M  -ema T M11..  -ej T i j  -eps T i j f   (up to 4 populations)" << endl;
-  cout << "Not supported by this engine yet (rejected with an error): -es, -eI, -eG (growth), -guide," << endl
+  cout << "  -I NPOP n1..nP [M]  -eM T M  -em T i j M  -ema T M11..  -ej T i j  -eps T i j f  -es T i f   (up to 4 populations)" << endl;
+  cout << "Not supported by this engine yet (rejected with an error): -eI, -eG (growth), -guide," << endl
        << "  -bias_heights/-bias_strengths, -apf > 0, -arg, -vb together with -I" << endl;
 }
 

@@ -180,6 +180,8 @@ STRUCT_MODELS = {
     "config3": (8, "-I 2 4 4 -em 0 2 1 1 -ej 0.5 2 1"),
     "island2_epochs": (6, "-I 2 3 3 0.5 -en 0.05 1 0.3 -en 0.05 2 2 -eM 0.2 3.0 -eN 0.6 1.5"),
     "three": (6, "-I 3 2 2 2 -em 0.1 2 1 2.0 -ej 0.3 3 2 -ej 0.8 2 1"),
+    # admixture: at 0.1 a lineage of population 1 moves to a new population 3 with probability 0.7 (-es t i p keeps p)
+    "admix3": (6, "-I 2 3 3 0.5 -es 0.1 1 0.3 -ej 0.4 3 2 -ej 0.9 2 1"),
 }
 
 

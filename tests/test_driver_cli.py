@@ -56,7 +56,7 @@ def test_parse_errors(args, message):
 
 
 @pytest.mark.parametrize("args", [
-    ["-es", "0.5", "1", "0.3"], ["-eI", "0.1", "1"], ["-eG", "0", "1"], ["-vb", "-I", "2", "2", "2", "1.0"],
+    ["-eI", "0.1", "1"], ["-eG", "0", "1"], ["-vb", "-I", "2", "2", "2", "1.0"],
     ["-guide", "x.gz"], ["-bias_heights", "400"], ["-apf", "1"], ["-arg"], ["-sr", "100", "2"],
 ])
 def test_unsupported_features_are_rejected_not_ignored(args):
@@ -95,6 +95,7 @@ def test_structured_models_parse_like_scrm():
         "config3": (8, "-I 2 4 4 -em 0 2 1 1 -ej 0.5 2 1"),
         "island2_epochs": (6, "-I 2 3 3 0.5 -en 0.05 1 0.3 -en 0.05 2 2 -eM 0.2 3.0 -eN 0.6 1.5"),
         "three": (6, "-I 3 2 2 2 -em 0.1 2 1 2.0 -ej 0.3 3 2 -ej 0.8 2 1"),
+        "admix3": (6, "-I 2 3 3 0.5 -es 0.1 1 0.3 -ej 0.4 3 2 -ej 0.9 2 1"),
     }
     L = 100000000
     for name, (n, flags) in models.items():
@@ -118,6 +119,8 @@ def test_structured_models_parse_like_scrm():
     (["-I", "2", "2", "2", "-ej", "0.5", "2", "1", "-em", "0", "2", "1", "1"], "sort both arguments by time"),
     (["-I", "2", "2", "2", "1.0", "-en", "0.1", "3", "1"], "Invalid population"),
     (["-I", "5", "1", "1", "1", "1", "0", "1.0"], "1 to 4 populations"),
+    (["-I", "3", "2", "1", "1", "1.0", "-es", "0.1", "1", "0.5", "-es", "0.2", "2", "0.5"], "1 to 4 populations"),
+    (["-I", "2", "2", "2", "1.0", "-es", "0.1", "1", "1.5"], "greater than one"),
 ])
 def test_structured_parse_errors(args, message):
     r = run("-nsam", "4", "-Np", "10", "-t", "10", "-r", "10", "1000", *args)
