@@ -84,9 +84,14 @@ const char* smc_version(void);
  *   0 recombination count, 1 recombination opportunity, 2+3p coalescence count in p, 3+3p coalescence opportunity in p,
  *   4+3p migration opportunity in p, 2+3*npop + p*npop + q migration count p -> q
  * (CountModel::total_coal_count / total_coal_opportunity / total_mig_count / total_mig_opportunity, count.hpp).
- * Not yet combinable with smc_shard_attach; -vb factors are not applied to structured moves. */
+ * Not yet combinable with smc_shard_attach.  cfg.vb_logfac is not used by the structured move: see smc_set_population_vb. */
 int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const double* mig, const double* single_mig,
                         const int32_t* leaf_pop, int32_t max_marks);
+/* -vb with populations (particle.cpp:262-272): the log of exp_digamma(c) / c, c = Model::coalescent_event_count(pop) resp.
+ * Model::migration_event_count(from, to) of the epoch, is added to a particle's log weight at every coalescence
+ * (pairwise ones included) resp. migration of its moves.  coal_logfac[E][npop], mig_logfac[E][npop][npop]; NULL = zeros.
+ * Call after smc_set_populations, between sweeps. */
+int smc_set_population_vb(smc_engine* e, const double* coal_logfac, const double* mig_logfac);
 /* rows of the array smc_get_tallies fills: 6 for a single population, 2Q after smc_set_populations */
 int smc_tally_rows(smc_engine* e);
 /* populations and migration marks of the current particles (tests): pop[N][2n-1] population at the bottom of the branch

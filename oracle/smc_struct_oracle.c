@@ -76,7 +76,7 @@ static void fixed_time_events(const orc_smodel* m, int e, double t, int* pop, sp
  * coalescence time; *target is the branch it coalesces into, or -1 for the pairwise coalescence with the old root's
  * lineage above the root.  fa / ra collect the population changes of the floating and of the root lineage. */
 static double sfloat(const orc_smodel* m, const orc_sparticle* p, const char* present, int root, orc_rng* r, double t0,
-                     int pop0, spath* fa, spath* ra, int* target, int* coal_pop, orc_srecords* recs) {
+                     int pop0, spath* fa, spath* ra, int* target, int* coal_pop, orc_srecords* recs, double* vb_logw) {
   const int n = m->base.n, nn = 2 * n - 1;
   const int* parent = p->tree.parent; const double* height = p->tree.height;
   const double hroot = height[root];
@@ -120,6 +120,11 @@ static double sfloat(const orc_smodel* m, const orc_sparticle* p, const char* pr
     }
     srecord(recs, 0, e, pf, k + (pw > 0.0 ? 1 : 0), tev - tt, ev_f, to_f);
     if (above) srecord(recs, 1, e, pr, 0, tev - tt, ev_r, to_r);
+    if (vb_logw) {                                        /* particle.cpp:262-272, before the record masks apply */
+      if (ev_f == 1) *vb_logw += m->vb_coal[e][pf];
+      if (ev_f == 2) *vb_logw += m->vb_mig[e][pf][to_f];
+      if (ev_r == 2) *vb_logw += m->vb_mig[e][pr][to_r];
+    }
     const double ts = tt;                                 /* start of the interval: where the contemporaries were counted */
     tt = tev;
     if (hit) {
@@ -198,7 +203,7 @@ void orc_sinit_particle(const orc_smodel* m, orc_sparticle* p, orc_rng* r, doubl
   for (int i = 1; i < n; i++) {
     spath fa, ra;
     int target = -1, cpop = 0;
-    double tc = sfloat(m, p, present, root, r, 0.0, m->leaf_pop[i], &fa, &ra, &target, &cpop, 0);
+    double tc = sfloat(m, p, present, root, r, 0.0, m->leaf_pop[i], &fa, &ra, &target, &cpop, 0, 0);
     const int nw = used++;
     present[i] = 1; present[nw] = 1;
     p->tree.height[nw] = tc; p->pop[nw] = cpop;
@@ -250,7 +255,8 @@ void orc_ssmc_move(const orc_smodel* m, orc_sparticle* p, orc_rng* r, orc_srecor
   /* 2. float */
   spath fa, ra;
   int target = -1, cpop = 0;
-  const double tc = sfloat(m, p, present, root, r, hh, orc_spop_at(p, b, hh), &fa, &ra, &target, &cpop, recs);
+  const double tc = sfloat(m, p, present, root, r, hh, orc_spop_at(p, b, hh), &fa, &ra, &target, &cpop, recs,
+                           recs ? &p->tree.logw : 0);   /* the -vb factors belong to the filter, not to the prior walks */
   /* 3. surgery.  The stub of b above the cut disappears unless the lineage coalesces back into it. */
   if (target == b) {
     drop_marks(p, b, hh, tc);

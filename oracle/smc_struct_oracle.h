@@ -3,8 +3,8 @@
  * population (forest.cc:299-347,423-756,995-1175; time_interval.cc:60-141; contemporaries_container.h:249-379) and the
  * records ForestState::record_all_event writes for them (particle.cpp:193-302).
  *
- * Status: groundwork for SURVEY.md section 8 rows a2/a4/a9/a14 with P > 1.  No CUDA kernel uses these semantics yet
- * (DESIGN.md section 10); the file pins the algorithm against the unmodified reference DISTRIBUTIONALLY
+ * Status: the checker of the structured CUDA path (smc_struct_device.cuh, tests/test_gpu_struct.py compares draw for
+ * draw); the file itself is pinned against the unmodified reference DISTRIBUTIONALLY
  * (tests/test_struct_oracle.py: moments of ARG walks under structured models, reference side from
  * oracle/_ref/libsmcref.so, committed as tests/golden/struct_moments.npz).
  *
@@ -30,6 +30,10 @@ typedef struct {
   double mig[ORC_MAXE][ORC_MAXP][ORC_MAXP];         /* Model::migration_rate(i, j), per generation, backwards i -> j */
   double single_mig[ORC_MAXE][ORC_MAXP][ORC_MAXP];  /* Model::single_mig_pop(i, j) at the START of the epoch (-ej/-es) */
   int leaf_pop[ORC_MAXN];                           /* Model::sample_population */
+  /* -vb (particle.cpp:262-272): log(exp_digamma(c) / c) added to the particle's log weight at every coalescence in
+   * (epoch, pop) resp. migration (epoch, from, to) of a move; all zero = no correction */
+  double vb_coal[ORC_MAXE][ORC_MAXP];
+  double vb_mig[ORC_MAXE][ORC_MAXP][ORC_MAXP];
 } orc_smodel;
 
 typedef struct {

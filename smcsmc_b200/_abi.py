@@ -39,6 +39,7 @@ SYMBOLS = {
     "smc_shard_unique_id": (_I, [_V]),
     "smc_shard_attach": (_I, [_V, ctypes.c_int32, ctypes.c_int32, _V]),
     "smc_set_populations": (_I, [_V, ctypes.c_int32, _V, _V, _V, _V, ctypes.c_int32]),
+    "smc_set_population_vb": (_I, [_V, _V, _V]),
     "smc_tally_rows": (_I, [_V]),
     "smc_get_population_state": (_I, [_V, _V, _V, _V, _V, _V]),
     "smc_reset": (_I, [_V, _V, _D, _V, ctypes.c_uint64]),

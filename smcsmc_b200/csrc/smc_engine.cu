@@ -1595,7 +1595,10 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
     smem = std::max(smem, (size_t)E * 2 * Q * (e->BS / 32) * sizeof(double) + 16);   // hand-over staging of phase 0
     if (smem > 230400 || stree_smem(nn, E, K, AUX_BS) > 230400)
       return fail(SMC_ERR_ARG, "n, E and max_marks need more shared memory than one SM has (fewer particles per block: SMC_BLOCK=32)");
-    double *d_inv, *d_mig, *d_tot, *d_single; unsigned char* d_fixed; signed char* d_leaf;
+    double *d_inv, *d_mig, *d_tot, *d_single, *d_vbc, *d_vbm; unsigned char* d_fixed; signed char* d_leaf;
+    if ((rc = dev_alloc(e, &d_vbc, h_inv.size(), false)) || (rc = dev_alloc(e, &d_vbm, h_mig.size(), false))) return rc;
+    CUDA_TRY(cudaMemsetAsync(d_vbc, 0, h_inv.size() * sizeof(double), e->stream));
+    CUDA_TRY(cudaMemsetAsync(d_vbm, 0, h_mig.size() * sizeof(double), e->stream));
     if ((rc = dev_alloc(e, &d_inv, h_inv.size(), false)) || (rc = dev_alloc(e, &d_mig, h_mig.size(), false)) ||
         (rc = dev_alloc(e, &d_tot, h_tot.size(), false)) || (rc = dev_alloc(e, &d_single, h_single.size(), false)) ||
         (rc = dev_alloc(e, &d_fixed, (size_t)E, false)) || (rc = dev_alloc(e, &d_leaf, (size_t)n, false)))
@@ -1611,6 +1614,7 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
     P.sm.K = K; P.sm.Q = Q;
     P.sm.inv2N = d_inv; P.sm.mig = d_mig; P.sm.migtot = d_tot; P.sm.single_mig = d_single; P.sm.fixed = d_fixed;
     P.sm.leaf_pop = d_leaf;
+    P.sm.vb_coal = d_vbc; P.sm.vb_mig = d_vbm;
     e->Q = Q; e->tally_rows = 2 * Q; e->smem = smem;
   }
   CUDA_TRY(cudaMemcpyAsync((void*)P.sm.inv2N, h_inv.data(), h_inv.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
@@ -1621,6 +1625,22 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
   CUDA_TRY(cudaMemcpyAsync((void*)P.sm.leaf_pop, h_leaf.data(), h_leaf.size(), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   P.sm.P = Pp;
+  return 0;
+}
+
+int smc_set_population_vb(smc_engine* e, const double* coal_logfac, const double* mig_logfac) {
+  if (!e) return fail(SMC_ERR_ARG, "null engine");
+  Params& P = e->P;
+  if (P.sm.P < 2) return fail(SMC_ERR_STATE, "call smc_set_populations first");
+  if (e->inited && e->swept > 0 && !e->finished) return fail(SMC_ERR_STATE, "the -vb factors cannot change during a sweep");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  const size_t E = (size_t)e->cfg.E, Pp = (size_t)P.sm.P;
+  std::vector<double> c(E * Pp, 0.0), mg(E * Pp * Pp, 0.0);
+  for (size_t k = 0; k < c.size(); k++) if (coal_logfac) { c[k] = coal_logfac[k]; if (!std::isfinite(c[k])) return fail(SMC_ERR_ARG, "non-finite -vb factor"); }
+  for (size_t k = 0; k < mg.size(); k++) if (mig_logfac) { mg[k] = mig_logfac[k]; if (!std::isfinite(mg[k])) return fail(SMC_ERR_ARG, "non-finite -vb factor"); }
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.vb_coal, c.data(), c.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaMemcpyAsync((void*)P.sm.vb_mig, mg.data(), mg.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
   return 0;
 }
 
@@ -2264,6 +2284,7 @@ static int calibrate_impl(int device, int32_t n, int32_t E, const double* t_star
     sm.inv2N = (const double*)t_inv.p; sm.mig = (const double*)t_mig.p; sm.migtot = (const double*)t_tot.p;
     sm.single_mig = (const double*)t_single.p; sm.fixed = (const unsigned char*)t_fixed.p;
     sm.leaf_pop = (const signed char*)t_leaf.p;
+    sm.vb_coal = nullptr; sm.vb_mig = nullptr;
     smem = stree_smem(m.nn, E, sm.K, BS);
     if (smem > 230400) { sm.K = 2 * n + 8; smem = stree_smem(m.nn, E, sm.K, BS); }
     if (smem > 230400) return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has");

@@ -37,6 +37,8 @@ struct SModelDev {
   const double* single_mig;     // [E][P][P] Model::single_mig_pop(i, j) at the START of the epoch
   const unsigned char* fixed;   // [E]       the epoch start has a fixed-time event
   const signed char* leaf_pop;  // [n]       Model::sample_population
+  const double* vb_coal;        // [E][P]    -vb: log(exp_digamma(c)/c) per coalescence in (epoch, pop), or NULL
+  const double* vb_mig;         // [E][P][P] -vb: the same per migration (epoch, from, to), or NULL
 };
 
 // cell indices inside an epoch's tally record
@@ -165,7 +167,8 @@ struct SNullSink {
 // the floating and of the root lineage are left in the mark pool under MARK_FLOATING / MARK_ROOT_LINEAGE.
 template <class TV, class Sink>
 __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long long present, int root, Rng& r, double t0,
-                                 int pop0, int& target, int& coal_pop, Sink& sink, double x, int max_rec_epoch) {
+                                 int pop0, int& target, int& coal_pop, Sink& sink, double x, int max_rec_epoch,
+                                 double* vb_logw) {
   const SModelDev& s = *T.sm;
   const int n = m.n, nn = m.nn, P = s.P;
   const double hroot = T.h(root);
@@ -215,6 +218,11 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
         ev_r = 2;
         for (int j = 0; j < P; j++) { if (j == pr) continue; to_r = j; u -= s.mig[(e * P + pr) * P + j]; if (u < 0) break; }
       } else ev_f = 1;                                   // pairwise coalescence, booked on the floating lineage
+    }
+    if (vb_logw && s.vb_coal) {                          // particle.cpp:262-272, before the record masks apply
+      if (ev_f == 1) *vb_logw += s.vb_coal[e * P + pf];
+      if (ev_f == 2) *vb_logw += s.vb_mig[(e * P + pf) * P + to_f];
+      if (ev_r == 2) *vb_logw += s.vb_mig[(e * P + pr) * P + to_r];
     }
     if ((m.rec_mask[e] & 2) && e <= max_rec_epoch) {     // particle.cpp:251-300
       const double dt = tev - tt;
@@ -291,7 +299,7 @@ __device__ inline void init_tree(const ModelDev& m, const STreeViewT<BS>& T, Rng
   SNullSink none;
   for (int i = 1; i < n; i++) {
     int target = -1, cpop = 0;
-    double tc = s_float(m, T, present, root, r, 0.0, s.leaf_pop[i], target, cpop, none, 0.0, -1);
+    double tc = s_float(m, T, present, root, r, 0.0, s.leaf_pop[i], target, cpop, none, 0.0, -1, nullptr);
     if (target == -3) return;
     const int nw = used++;
     present |= (1ull << i) | (1ull << nw);
@@ -344,7 +352,7 @@ __device__ inline void smc_move(const ModelDev& m, const STreeViewT<BS>& T, Rng&
   // 2. float
   int target = -1, cpop = 0;
   const unsigned long long all = nn >= 64 ? ~0ull : ((1ull << nn) - 1ull);
-  const double tc = s_float(m, T, all, root, r, hh, s_pop_at(T, b, hh), target, cpop, sink, x, max_rec_epoch);
+  const double tc = s_float(m, T, all, root, r, hh, s_pop_at(T, b, hh), target, cpop, sink, x, max_rec_epoch, &logw);
   if (target <= -2) return;
   // 3. surgery.  The stub of b above the cut disappears unless the lineage coalesces back into it.
   if (target == b) {

@@ -83,6 +83,12 @@ class ParticleFilter:
         self.P = P
         self.max_marks = int(max_marks) if max_marks > 0 else 2 * self.n + 8
 
+    def set_population_vb(self, coal_logfac=None, mig_logfac=None):
+        """-vb with populations: log(exp_digamma(c)/c) per coalescence [E][P] and per migration [E][P][P]"""
+        c = None if coal_logfac is None else _f64(coal_logfac).reshape(self.E, self.P)
+        m = None if mig_logfac is None else _f64(mig_logfac).reshape(self.E, self.P, self.P)
+        check(lib().smc_set_population_vb(self._h, None if c is None else _P(c), None if m is None else _P(m)))
+
     def population_state(self):
         """(pop[N][2n-1], marks) with marks[i] = list of (branch, time, population above) of particle i"""
         nn, K = 2 * self.n - 1, self.max_marks

@@ -75,17 +75,22 @@ void add_size_change(Params& P, double t_scaled, int pop, double rel_size, doubl
 }
 
 // Model::addMigrationRates / addMigrationRate / addSymmetricMigration (model.cc:370-459); M = 4 N0 m
-void add_mig_all(Params& P, double t_scaled, double M) {
+void add_mig_all(Params& P, double t_scaled, double M, double count = 1e10) {
   Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
   e.mig.assign((size_t)P.npop * P.npop, kNaN);
+  e.mig_vb.assign((size_t)P.npop * P.npop, kNaN);
   if (!std::isnan(M))
     for (int i = 0; i < g_cur_pops; i++)
-      for (int j = 0; j < g_cur_pops; j++) e.mig[(size_t)i * P.npop + j] = M / (4 * P.N0);
+      for (int j = 0; j < g_cur_pops; j++) {
+        e.mig[(size_t)i * P.npop + j] = M / (4 * P.N0);
+        e.mig_vb[(size_t)i * P.npop + j] = count;
+      }
 }
-void add_mig_one(Params& P, double t_scaled, int i, int j, double M) {
+void add_mig_one(Params& P, double t_scaled, int i, int j, double M, double count = 1e10) {
   Epoch& e = epoch_at(P, t_scaled * 4 * P.N0);
-  if (e.mig.empty()) e.mig.assign((size_t)P.npop * P.npop, kNaN);
+  if (e.mig.empty()) { e.mig.assign((size_t)P.npop * P.npop, kNaN); e.mig_vb.assign((size_t)P.npop * P.npop, kNaN); }
   e.mig[(size_t)i * P.npop + j] = M / (4 * P.N0);
+  e.mig_vb[(size_t)i * P.npop + j] = count;
 }
 // Model::addSingleMigrationEvent (model.cc:461-480)
 void add_single_mig(Params& P, double t_scaled, int i, int j, double fraction) {
@@ -247,17 +252,20 @@ void parse(int argc, char** argv, Params& P) {
     }
     else if (f == "-ma" || f == "-ema") {
       double t = time_of(f, f == "-ema");
-      std::vector<double> M((size_t)P.npop * P.npop, 0.0);
+      std::vector<double> M((size_t)P.npop * P.npop, 0.0), C((size_t)P.npop * P.npop, 1e10);
       for (int i = 0; i < g_cur_pops; i++)
         for (int j = 0; j < g_cur_pops; j++) {
           if (i == j) { (void)s.next(f); if (P.vb) (void)s.next(f); continue; }
           M[(size_t)i * P.npop + j] = s.next_double(f);
-          if (P.vb) (void)s.next_double(f);
+          if (P.vb) C[(size_t)i * P.npop + j] = s.next_double(f);
         }
       add_mig_all(P, t, 0.0);
       for (int i = 0; i < g_cur_pops; i++)
         for (int j = 0; j < g_cur_pops; j++)
-          if (i != j) { add_mig_one(P, t, i, j, M[(size_t)i * P.npop + j]); if (M[(size_t)i * P.npop + j] > 0) P.has_migration = true; }
+          if (i != j) {
+            add_mig_one(P, t, i, j, M[(size_t)i * P.npop + j], C[(size_t)i * P.npop + j]);
+            if (M[(size_t)i * P.npop + j] > 0) P.has_migration = true;
+          }
     }
     else if (f == "-m" || f == "-em") {
       double t = time_of(f, f == "-em");
@@ -270,8 +278,8 @@ void parse(int argc, char** argv, Params& P) {
       double t = time_of(f, f == "-eM");
       if (g_cur_pops < 2) throw std::invalid_argument(f + " needs more than one population (-I)");
       double M = s.next_double(f) / (g_cur_pops - 1);
-      if (P.vb) (void)s.next_double(f);
-      add_mig_all(P, t, M);
+      double count = P.vb ? s.next_double(f) / (g_cur_pops - 1) : 1e10;     // param.cc:288-290
+      add_mig_all(P, t, M, count);
       if (M > 0) P.has_migration = true;
     }
     else if (f == "-ej") {
@@ -320,7 +328,6 @@ void parse(int argc, char** argv, Params& P) {
   if (P.leaf_pop.empty()) P.leaf_pop.assign(P.nsam, 0);
   if (P.leaf_pop.size() != P.nsam)
     throw std::invalid_argument("-I: the sample sizes of the populations do not add up to -nsam");
-  if (P.npop > 1 && P.vb) unsupported("-vb", "variational Bayes factors with structured populations");
   finalize_model(P);
   if (P.npop > 1 && !P.has_migration)      // Model::check (model.cc:630-633)
     throw std::invalid_argument("Model has multiple populations but no migration. Coalescence impossible");
@@ -332,6 +339,7 @@ void parse(int argc, char** argv, Params& P) {
 void finalize_model(Params& P) {
   const size_t np = (size_t)P.npop;
   const std::vector<double>* last_mig = nullptr;
+  const std::vector<double>* last_vb = nullptr;
   for (size_t e = 0; e < P.epochs.size(); e++) {
     Epoch& ep = P.epochs[e];
     if (ep.pop_size.empty()) { ep.pop_size.assign(np, kNaN); ep.vb_count.assign(np, kNaN); }
@@ -340,13 +348,19 @@ void finalize_model(Params& P) {
       if (std::isnan(ep.vb_count[p])) ep.vb_count[p] = 1e10;
     }
     if (ep.mig.empty()) {
-      if (last_mig) ep.mig = *last_mig; else ep.mig.assign(np * np, 0.0);
+      if (last_mig) { ep.mig = *last_mig; ep.mig_vb = *last_vb; }
+      else { ep.mig.assign(np * np, 0.0); ep.mig_vb.assign(np * np, 1e10); }
     } else {
-      for (size_t k = 0; k < np * np; k++)
+      for (size_t k = 0; k < np * np; k++) {
         if (std::isnan(ep.mig[k])) ep.mig[k] = last_mig ? (*last_mig)[k] : 0.0;
+        // Model::finalize does not fill the event counts of entries that were not given (they stay NaN and are never
+        // read for a rate of zero); here they fall back to "no correction"
+        if (std::isnan(ep.mig_vb[k])) ep.mig_vb[k] = last_vb ? (*last_vb)[k] : 1e10;
+      }
     }
     for (size_t p = 0; p < np; p++) ep.mig[p * np + p] = 0.0;
     last_mig = &ep.mig;
+    last_vb = &ep.mig_vb;
     if (ep.single_mig.empty()) ep.single_mig.assign(np * np, 0.0);
   }
 }

@@ -22,6 +22,7 @@ struct Epoch {
   std::vector<double> pop_size;    // [P] absolute N_e
   std::vector<double> vb_count;    // [P] -vb event counts (1e10 = no correction)
   std::vector<double> mig;         // [P*P] per-generation rate of a lineage in i moving to j (backwards in time)
+  std::vector<double> mig_vb;      // [P*P] -vb event counts of the migration rates (1e10 = no correction)
   std::vector<double> single_mig;  // [P*P] probability of being moved i -> j at the START of the epoch (-ej / -eps)
 };
 

@@ -139,7 +139,7 @@ void print_help(const Params& P) {
   cout << endl << "Model (scrm syntax): -t THETA  -r RHO LENGTH  -N0 N  -eN T SIZE  -en T POP SIZE  -vb  -seed S" << endl;
   cout << "  -I NPOP n1..nP [M]  -eM T M  -em T i j M  -ema T M11..  -ej T i j  -eps T i j f  -es T i f   (up to 4 populations)" << endl;
   cout << "Not supported by this engine yet (rejected with an error): -eI, -eG (growth), -guide," << endl
-       << "  -bias_heights/-bias_strengths, -apf > 0, -arg, -vb together with -I" << endl;
+       << "  -bias_heights/-bias_strengths, -apf > 0, -arg" << endl;
 }
 
 // the flattened Model the engine takes: [E] times, [E][P] 1/(2N), [E][P][P] migration rates and fixed-time moves
@@ -258,6 +258,19 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
       int marks = min(120, 2 * n + 8 + 10 * (int)ceil(msum));
       if (const char* mm = getenv("SMCSMC_MAX_MARKS")) marks = atoi(mm);
       check(smc_set_populations(eng[k], np, M.inv2N.data(), M.mig.data(), M.single_mig.data(), M.leaf_pop.data(), marks));
+      if (P.vb) {   // particle.cpp:262-272: exp_digamma(c) / c per coalescence resp. migration
+        vector<double> vc((size_t)E * np), vm((size_t)E * np * np, 0.0);
+        for (int e = 0; e < E; e++)
+          for (int p = 0; p < np; p++) {
+            const double c = P.epochs[e].vb_count[p];
+            vc[(size_t)e * np + p] = log(exp_digamma(c) / c);
+            for (int q = 0; q < np; q++) {
+              const double cm = P.epochs[e].mig_vb[(size_t)p * np + q];
+              if (p != q) vm[((size_t)e * np + p) * np + q] = log(exp_digamma(cm) / cm);
+            }
+          }
+        check(smc_set_population_vb(eng[k], vc.data(), vm.data()));
+      }
     }
     check(smc_upload_rows(eng[k], rows.x_end.data(), rows.alleles.data(), rows.is_site.data(), max_rec.data(), (int64_t)R));
     check(smc_init_particles(eng[k]));

@@ -252,7 +252,9 @@ class OrcSModel(ctypes.Structure):
                 ("inv2N", (ctypes.c_double * ORC_MAXP) * 64),
                 ("mig", ((ctypes.c_double * ORC_MAXP) * ORC_MAXP) * 64),
                 ("single_mig", ((ctypes.c_double * ORC_MAXP) * ORC_MAXP) * 64),
-                ("leaf_pop", ctypes.c_int * 64)]
+                ("leaf_pop", ctypes.c_int * 64),
+                ("vb_coal", (ctypes.c_double * ORC_MAXP) * 64),
+                ("vb_mig", ((ctypes.c_double * ORC_MAXP) * ORC_MAXP) * 64)]
 
 
 class OrcSParticle(ctypes.Structure):
@@ -261,8 +263,9 @@ class OrcSParticle(ctypes.Structure):
                 ("mark_pop", ctypes.c_int * ORC_MAXMARKS), ("overflow", ctypes.c_int)]
 
 
-def make_smodel(n, t_start, inv2N, mig, single, leaf_pop, mu, rho, seqlen):
-    """inv2N [E][P], mig / single [E][P][P] (backward rates per generation / fixed-time move probabilities)"""
+def make_smodel(n, t_start, inv2N, mig, single, leaf_pop, mu, rho, seqlen, vb_coal=None, vb_mig=None):
+    """inv2N [E][P], mig / single [E][P][P] (backward rates per generation / fixed-time move probabilities);
+    vb_coal [E][P] / vb_mig [E][P][P]: -vb log factors (default none)"""
     import numpy as np
     inv2N, mig, single = np.asarray(inv2N), np.asarray(mig), np.asarray(single)
     E, Pn = inv2N.shape
@@ -278,6 +281,10 @@ def make_smodel(n, t_start, inv2N, mig, single, leaf_pop, mu, rho, seqlen):
             for j in range(Pn):
                 m.mig[e][i][j] = mig[e][i][j]
                 m.single_mig[e][i][j] = single[e][i][j]
+                if vb_mig is not None:
+                    m.vb_mig[e][i][j] = vb_mig[e][i][j]
+            if vb_coal is not None:
+                m.vb_coal[e][i] = vb_coal[e][i]
     for i in range(n):
         m.leaf_pop[i] = int(leaf_pop[i])
     return m

@@ -56,7 +56,7 @@ def test_parse_errors(args, message):
 
 
 @pytest.mark.parametrize("args", [
-    ["-eI", "0.1", "1"], ["-eG", "0", "1"], ["-vb", "-I", "2", "2", "2", "1.0"],
+    ["-eI", "0.1", "1"], ["-eG", "0", "1"],
     ["-guide", "x.gz"], ["-bias_heights", "400"], ["-apf", "1"], ["-arg"], ["-sr", "100", "2"],
 ])
 def test_unsupported_features_are_rejected_not_ignored(args):

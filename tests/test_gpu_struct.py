@@ -130,6 +130,45 @@ def test_structured_filter_vs_oracle(S, name):
     pf.close()
 
 
+@pytest.mark.parametrize("name", ["config3", "island2_epochs"])
+def test_structured_vb_factors(S, name):
+    """-vb with populations (smc_set_population_vb): a factor per coalescence (epoch, population) and per migration
+    (epoch, from, to) enters the particle weights exactly as in the restatement -- weights, resampling, ancestry, ln
+    normaliser -- and the run differs from the one without factors"""
+    mu, rho = (1e-7, 4e-8) if name == "config3" else (2.5e-8, 1e-8)
+    N, R, seqlen = 128, 50, 40000.0
+    n, t_start, inv2N, mig, single, leaf, _ = _model(name, seqlen, mu, rho)
+    E, P = inv2N.shape
+    rng = np.random.default_rng(9)
+    vb_c = np.log(rng.uniform(0.7, 1.0, size=(E, P)))
+    vb_m = np.log(rng.uniform(0.5, 1.0, size=(E, P, P)))
+    sm = _libs.make_smodel(n, t_start, inv2N, mig, single, leaf, mu, rho, seqlen, vb_coal=vb_c, vb_mig=vb_m)
+    lags = np.linspace(0.25 * seqlen, 0.02 * seqlen, E)
+    x_end, al, is_site = _rows(n, R, seqlen, seed=77)
+    out = []
+    for with_vb in (True, False):
+        pf = S.ParticleFilter(n, N, t_start, inv2N[:, 0], mu, rho, seqlen, lags, seed=13, chunk=2, parity_scan=True,
+                              populations=dict(inv2N=inv2N, mig=mig, single_mig=single, leaf_pop=leaf,
+                                               max_marks=120 if name == "island2_epochs" else 40))
+        if with_vb:
+            pf.set_population_vb(vb_c, vb_m)
+        pf.upload_rows(x_end, al, is_site)
+        pf.init_particles()
+        pf.sweep()
+        pf.finish()
+        out.append((pf.particles(), pf.ln_normalization_factor(), pf.last_ancestry(), pf.tallies(), pf.counters()))
+        pf.close()
+    ref = _libs.oracle_sfilter(sm, N, 13, 2, 0.0, 0.5, lags, x_end, al.astype(np.int32), is_site.astype(np.int32))
+    (parent, height, logw, nb), lnZ, anc, t, c = out[0]
+    assert c["resamples"] == ref["n_resample"] and ref["n_resample"] > 0
+    assert np.array_equal(parent, ref["parent"]) and np.array_equal(anc, ref["last_anc"])
+    np.testing.assert_allclose(height, ref["height"], rtol=1e-11)
+    np.testing.assert_allclose(logw, ref["logw"], rtol=0, atol=1e-9)
+    assert lnZ == pytest.approx(ref["lnZ"], rel=1e-11)
+    np.testing.assert_allclose(t[0], ref["tallies"][0], rtol=1e-10, atol=1e-13)
+    assert abs(out[1][1] - lnZ) > 1e-3            # the factors do something
+
+
 def test_no_coalescence_is_reported(S):
     """two isolated populations that never join: the reference throws 'Lines did not coalescence'; so does the engine"""
     n = 4
