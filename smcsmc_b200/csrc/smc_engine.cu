@@ -1359,9 +1359,11 @@ int launch_row(smc_engine* e, int mode) {
 
 // `count` consecutive rows of an unsharded engine: batches of GRAPH_ROWS through the captured graph (one host call per
 // batch instead of one ~11 us launch per row -- the host launch rate bounds small populations), the rest directly
-constexpr int GRAPH_ROWS = 32;
+int GRAPH_ROWS = 32;
 int launch_rows(smc_engine* e, int64_t count) {
   static const bool no_graph = getenv("SMC_NO_GRAPH") != nullptr;
+  static const bool tuned = [] { if (const char* g = getenv("SMC_GRAPH_ROWS")) { int v = atoi(g); if (v >= 2 && v <= 4096) GRAPH_ROWS = v; } return true; }();
+  (void)tuned;
   if (!no_graph && count >= GRAPH_ROWS) {
     if (!e->row_graph || e->graph_dirty) {
       if (e->row_graph) { cudaGraphExecDestroy(e->row_graph); e->row_graph = nullptr; }
@@ -1889,7 +1891,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
       if (e->swept >= e->P.R) continue;
       CUDA_TRY(cudaSetDevice(e->cfg.device));
       // a turn is at least one graph batch; the streams keep the chunks concurrent on the device either way
-      int64_t stop = std::min<int64_t>(e->P.R, e->swept + std::max<int64_t>(rows_per_turn, GRAPH_ROWS));
+      int64_t stop = std::min<int64_t>(e->P.R, e->swept + std::max<int64_t>(rows_per_turn, (int64_t)GRAPH_ROWS));
       int rc = launch_rows(e, stop - e->swept);
       if (rc) return rc;
       e->swept = stop;
