@@ -248,10 +248,11 @@ def run_ours(a):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = abytes / avg_launch_s / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the six launches in
-    # profiles/r1_row_kernel_t2_ncu_full.csv (n = 8, E = 11, N = 10 000; ncu runs every launch cold-cache)
+    # profiles/r1_row_kernel_final_ncu_full.csv (n = 8, E = 11, N = 10 000; ncu runs every launch cold-cache, so the
+    # ancestor slots and open cells a resampling row gathers all come from DRAM: 4.8 - 8.1 MB per launch)
     traffic = None
     if (NSAM, E, N) == (8, 11, 10000):
-        traffic = 4.99e6
+        traffic = 6.78e6
     line = {
         "metric": "particle*sites/sec (s per EM iteration in ms_per_step)", "value": units / wall,
         "unit": "particle*sites/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
