@@ -22,6 +22,20 @@ def S():
     return smcsmc_b200
 
 
+@pytest.mark.parametrize("n", [4, 8, 16])
+def test_dephase_vs_reference_golden(S, n):
+    """-dephase: the driver recodes genotypes whose haplotypes differ as unphased pairs; the device likelihood of the
+    recoded data equals the reference's likelihood with dephase = true on the phased data (tests/golden/dephase.npz)"""
+    from test_oracle_golden import _dephased
+    g, d = np.load(os.path.join(G, "prune.npz")), np.load(os.path.join(G, "dephase.npz"))
+    mu = float(g[f"n{n}_mu"])
+    data = np.array([_dephased(row) for row in g[f"n{n}_phased"]])
+    assert (data == 2).any()
+    for aa, key in ((0, "site_dephase"), (1, "site_dephase_aa")):
+        got = S.site_likelihood(g[f"n{n}_parent"], g[f"n{n}_height"], data, mu, ancestral_aware=aa)
+        np.testing.assert_allclose(got, d[f"n{n}_{key}"], rtol=1e-12, atol=0)
+
+
 def test_fastexp_bit_exact(S):
     L = _libs.oracle()
     x = -np.concatenate([np.logspace(-12, 1.5, 4001), [0.0, 0.7184, 0.71845, 0.7185]])
