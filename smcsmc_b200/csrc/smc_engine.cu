@@ -168,6 +168,7 @@ struct RingSink {
   const int* kn;   // bucket index of the NEXT row's left end [E]: the bucket that stays open
   double* ACC;     // [E][BS] shared
   int t;
+  const double* ubf;          // [E] shared: upper bound of the bucket open at the row's left end
   unsigned long long split;   // bit e: a bound of epoch e lies inside this row
   // cells per epoch and where the recombination cells sit (single population: coal cnt, coal opp, rec cnt, rec opp)
   __device__ __forceinline__ int Q() const { return ST ? P->sm.Q : 4; }
@@ -188,7 +189,7 @@ struct RingSink {
     split = 0ull;
     for (int e = 0; e < P->m.E; e++) {
       ACC[e * BS + t] = 0.0;
-      if (P->ub[P->ub_off[e] + ks[e]] < x1) split |= 1ull << e;
+      if (ubf[e] < x1) split |= 1ull << e;
     }
   }
   __device__ void row_end() const {
@@ -230,7 +231,10 @@ struct RingSink {
     *cell(e, k, REC_CNT) += 1.0;
   }
   __device__ void rec_opp(int e, double xa, double xb, double rate) const {
-    if (!((split >> e) & 1ull)) { ACC[e * BS + t] += rate * (xb - xa); return; }
+    // a stretch that ends before the first bound inside the row belongs to the bucket of the row's left end, whose
+    // cell row_end() adds the accumulator to -- only what lies beyond that bound is written through
+    if (!((split >> e) & 1ull) || xb <= ubf[e]) { ACC[e * BS + t] += rate * (xb - xa); return; }
+    if (xa < ubf[e]) { ACC[e * BS + t] += rate * (ubf[e] - xa); xa = ubf[e]; }
     int k = bucket(e, xa);
     const double* ub = P->ub + P->ub_off[e];
     while (xa < xb) {
@@ -704,7 +708,17 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     }
   }
 
-  if (npend >= 0) __syncthreads();   // the slot list shares its storage with the accumulators phase 2 is about to zero
+  // the row's tally schedule is the same for every particle: one copy per block in shared memory
+  __shared__ int s_ks[SMC_MAX_EPOCHS], s_ksl[SMC_MAX_EPOCHS], s_kn[SMC_MAX_EPOCHS];
+  __shared__ double s_ubf[SMC_MAX_EPOCHS];
+  if (mode == 0) {
+    for (int e = t; e < E; e += BS) {
+      const int k0 = P.kstart[row * E + e];
+      s_ks[e] = k0; s_ksl[e] = P.kslot[row * E + e]; s_kn[e] = P.kstart[(row + 1) * E + e];
+      s_ubf[e] = P.ub[P.ub_off[e] + k0];
+    }
+  }
+  __syncthreads();   // also: the slot list shares its storage with the accumulators phase 2 is about to zero
 
   // ---- phase 2: the row ----------------------------------------------------------------------------------------
   int nrec = 0;
@@ -715,7 +729,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
-    RingSink<BS, ST> sink{&P, dst.open, (int)i, P.kstart + row * E, P.kslot + row * E, P.kstart + (row + 1) * E, T.ACC, t, 0ull};
+    RingSink<BS, ST> sink{&P, dst.open, (int)i, s_ks, s_ksl, s_kn, T.ACC, t, s_ubf, 0ull};
     nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
   }
 
