@@ -315,6 +315,18 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
       for (int64_t q = 0; q < got; q++) f << (long long)(pos[q] + (C > 1 ? chunk_start[k] - 1 : 0)) << "\t" << ess[q] << endl;
     }
   }
+  {
+    double dev_ms = 0;
+    int64_t launches = 0;
+    for (size_t k = 0; k < C; k++) {
+      double ms = 0;
+      int64_t l = 0;
+      check(smc_get_timing(eng[k], &ms, &l));
+      dev_ms += ms; launches += l;
+    }
+    clog << " Device time of the sweep: " << dev_ms << " ms in " << launches << " kernel launches ("
+         << (double)P.N * chunk_len * C / (dev_ms * 1e-3) << " particle*sites/s)" << endl;
+  }
   clog << "Got to end of sequence; resampled " << counters[1] << " times" << endl;
   clog << " Inference step completed." << endl;
 

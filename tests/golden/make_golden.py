@@ -164,6 +164,41 @@ def golden_dephase():
     np.savez_compressed(os.path.join(HERE, "dephase.npz"), **out)
 
 
+def golden_smc2_cmdlines():
+    """Command lines exactly as the reference's Python frontend emits them (smcsmc/populationmodels.py:
+    Population.core_command_line, with and without -vb, for its own model classes) and the tables of the reference's
+    parsed Model for each (scrm Param::parse + Model::finalize through libsmcref.so).  The CPU test feeds the same
+    strings to the drop-in driver's -dump_model.  populationmodels.py is loaded on its own (the package __init__ pulls
+    matplotlib, which this image lacks)."""
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location("populationmodels", "/root/reference/smcsmc/populationmodels.py")
+    pm = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(pm)
+    R = _libs.ref()
+    cases = []
+    two = dict(sample_populations=[1, 1, 1, 1, 2, 2, 2, 2])
+    for cls, kw in ((pm.PopSingleConst, {}), (pm.PopSingleBottleneck, {}), (pm.PopSingleExpand, {}), (pm.Pop4, {}),
+                    (pm.TwoPopUniDirMigr, two), (pm.TwoPopBiDirMigr, two), (pm.TwoPopSplitNoMigr, two)):
+        for vb in (False, True):
+            pop = cls(**kw)
+            cmd = pop.core_command_line(vb=vb)
+            n = pop.num_samples
+            h = _libs.ref_open("smcsmc -nsam %d -Np 10 -tmax 4 %s -seed 1" % (n, cmd))
+            E, Pn = R.ref_num_epochs(h), R.ref_num_pops(h)
+            ts, inv = np.zeros(E), np.zeros((E, Pn))
+            R.ref_epoch_table(h, P(ts), P(inv))
+            mig, single = np.zeros((E, Pn, Pn)), np.zeros((E, Pn, Pn))
+            R.ref_mig_table(h, P(mig), P(single))
+            pops = np.zeros(n, dtype=np.int32)
+            R.ref_sample_pops(h, P(pops))
+            cases.append({"model": cls.__name__, "vb": vb, "nsam": n, "cmd": cmd, "t_start": ts.tolist(),
+                          "inv2N": inv.tolist(), "mig": mig.tolist(), "single_mig": single.tolist(),
+                          "leaf_pop": pops.tolist(), "mu": R.ref_mutation_rate(h), "rho": R.ref_recombination_rate(h)})
+            R.ref_close(h)
+    json.dump(cases, open(os.path.join(HERE, "smc2_cmdlines.json"), "w"), indent=1)
+
+
 MOMENT_MODELS = {
     # name: (n, scrm demography flags)
     "const4": (4, ""),

@@ -113,6 +113,28 @@ def test_structured_models_parse_like_scrm():
         assert d["recombination_rate"] == pytest.approx(float(G[name + "_rho"]), rel=1e-14)
 
 
+def test_smc2_frontend_command_lines_parse_like_the_reference():
+    """the command lines the reference's Python frontend emits for its own model classes (populationmodels.py
+    core_command_line, EM and -vb form: -I, -eN with event counts, -ema with diagonal placeholders and counts, -eM,
+    -ej) give the driver the tables the reference's own parser builds from them (tests/golden/smc2_cmdlines.json,
+    make_golden.py::golden_smc2_cmdlines)"""
+    import json
+    import numpy as np
+    cases = json.load(open(os.path.join(ROOT, "tests", "golden", "smc2_cmdlines.json")))
+    assert len(cases) >= 14 and any(c["vb"] and len(c["inv2N"][0]) == 2 for c in cases)
+    for c in cases:
+        d = _dump("-nsam", str(c["nsam"]), "-Np", "10", "-tmax", "4", *c["cmd"].split(), "-seed", "1")
+        E, P = np.array(c["inv2N"]).shape
+        assert d["npop"] == P and d["epochs"] == E, c["model"]
+        assert d["leaf_pop"] == c["leaf_pop"], c["model"]
+        np.testing.assert_allclose([e[0] for e in d["rows"]], c["t_start"], rtol=1e-14)
+        np.testing.assert_allclose([e[1] for e in d["rows"]], c["inv2N"], rtol=1e-14)
+        np.testing.assert_allclose(np.array([e[2] for e in d["rows"]]).reshape(E, P, P), c["mig"], rtol=1e-14)
+        np.testing.assert_allclose(np.array([e[3] for e in d["rows"]]).reshape(E, P, P), c["single_mig"], rtol=1e-14)
+        assert d["mutation_rate"] == pytest.approx(c["mu"], rel=1e-14)
+        assert d["recombination_rate"] == pytest.approx(c["rho"], rel=1e-14)
+
+
 @pytest.mark.parametrize("args, message", [
     (["-I", "2", "2", "2"], "Model has multiple populations but no migration"),
     (["-I", "2", "2", "3", "1.0"], "do not add up to -nsam"),
