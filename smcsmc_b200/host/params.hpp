@@ -61,6 +61,7 @@ struct Params {
   std::vector<int> leaf_pop;                // [nsam] Model::sample_population (0-based)
   bool has_migration = false;               // Model::has_migration()
   bool dump_model = false;                  // -dump_model (extension): print the flattened tables and exit
+  int marks_scale = 1;                      // doubled by the driver when a sweep ran out of migration-mark slots
   std::vector<std::string> argv;
   // derived
   double mutation_rate = 0, recombination_rate = 0, original_recombination_rate = 0;

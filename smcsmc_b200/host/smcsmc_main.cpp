@@ -30,6 +30,9 @@ void check(int rc) {
   if (rc != 0) throw runtime_error(string("engine: ") + smc_last_error());
 }
 
+// a particle needed more migration marks than the engine was given room for: the sweep is repeated with twice the room
+struct MarksOverflow : runtime_error { MarksOverflow() : runtime_error("migration marks") {} };
+
 // particle.cpp:65-74
 double exp_digamma(double x) {
   if (x > 10) return x - 0.5 + (x + 0.5) / (24 * x * x);
@@ -246,16 +249,18 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     c.t_start = t_start.data(); c.inv2N = inv2N0.data(); c.vb_logfac = vb.data(); c.rec_mask = mask.data(); c.lags = lags.data();
     check(smc_create(&c, &eng[k]));
     if (np > 1) {
-      // capacity of the per-particle pool of migration marks: a local tree of n leaves is ~ 4 N0 * 2 * H(n-1) generations
-      // long and collects marks at the summed migration rate; room for several times the expectation, engine maximum 120
-      // (a particle that still overflows makes the run fail loudly at the end, smc_get_lnZ)
+      // capacity of the per-particle pool of migration marks.  Marks live in shared memory (10 bytes each), so room that
+      // is never used costs resident blocks: start from a pool that fits the typical tree (a branch per sample that
+      // changes population once, plus what the summed migration rate adds) and, should any particle overflow it -- the
+      // engine raises a flag, nothing is silently dropped -- repeat the sweep with twice the room (engine maximum 120).
       double msum = 0;
       for (int e = 0; e < E; e++) {
         double s = 0;
         for (int q = 0; q < np * np; q++) s += M.mig[(size_t)e * np * np + q];
         msum = max(msum, s * 4 * P.N0);
       }
-      int marks = min(120, 2 * n + 8 + 10 * (int)ceil(msum));
+      int marks = min(120, (n + 4 * (int)ceil(msum)) * P.marks_scale);
+      if (const char* mb = getenv("SMCSMC_MARKS_BASE")) marks = min(120, atoi(mb) * P.marks_scale);   // tests: force the retry
       if (const char* mm = getenv("SMCSMC_MAX_MARKS")) marks = atoi(mm);
       check(smc_set_populations(eng[k], np, M.inv2N.data(), M.mig.data(), M.single_mig.data(), M.leaf_pop.data(), marks));
       if (P.vb) {   // particle.cpp:262-272: exp_digamma(c) / c per coalescence resp. migration
@@ -300,6 +305,9 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     int64_t ck[4];
     check(smc_get_tallies(eng[k], tk.data()));
     int rc = smc_get_lnZ(eng[k], &lz);
+    if (rc == SMC_ERR_NUMERIC && string(smc_last_error()).find("migration marks") != string::npos &&
+        !getenv("SMCSMC_MAX_MARKS") && (n + 4) * P.marks_scale < 120)
+      throw MarksOverflow();
     if (rc == SMC_ERR_NUMERIC) throw runtime_error(string(smc_last_error()).find("probabilit") != string::npos
                                                        ? string("Zero or negative probabilities") : string(smc_last_error()));
     check(rc);
@@ -307,14 +315,17 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     for (size_t q = 0; q < tk.size(); q++) t[q] += tk[q];
     lnZ += lz;
     for (int q = 0; q < 4; q++) counters[q] += ck[q];
-    if (P.record_resample_file) {
+  }
+  if (P.record_resample_file)
+    for (size_t k = 0; k < C; k++) {
+      int64_t ck[4];
+      check(smc_get_counters(eng[k], ck));
       vector<double> pos(ck[1] + 1), ess(ck[1] + 1);
       int64_t got = 0;
       check(smc_get_resample_log(eng[k], pos.data(), ess.data(), ck[1], &got));
       ofstream f(out.resample_name.c_str(), ios::out | ios::app | ios::binary);
       for (int64_t q = 0; q < got; q++) f << (long long)(pos[q] + (C > 1 ? chunk_start[k] - 1 : 0)) << "\t" << ess[q] << endl;
     }
-  }
   {
     double dev_ms = 0;
     int64_t launches = 0;
@@ -478,7 +489,14 @@ int main(int argc, char* argv[]) {
     out.header();
     for (int i = 0; i <= P.EM_steps; i++) {
       clog << "EM step " << i << endl;
-      pfARG_core(P, chunks, chunk_start, chunk_len, out, i, devices);
+      for (;;) {
+        try { pfARG_core(P, chunks, chunk_start, chunk_len, out, i, devices); break; }
+        catch (const MarksOverflow&) {
+          P.marks_scale *= 2;
+          clog << " A particle ran out of migration-mark slots; repeating the sweep with room for "
+               << min(120, (int)(P.nsam + 4) * P.marks_scale) << "+ marks per particle" << endl;
+        }
+      }
       clog << "End of EM step " << i << endl;
       auto dur = chrono::duration_cast<chrono::seconds>(chrono::system_clock::now() - start);
       clog << "Elapsed time: " << setprecision(3) << (double)dur.count() << endl;

@@ -133,3 +133,20 @@ def test_structured_em_within_monte_carlo_error(runs):
             assert 7000 < mean(("Coal", ep, pop, "-1"), "Ne") < 14000
     assert 1.0e-5 < mean(("Migr", "1", "1", "0"), "Rate") < 5.0e-5
     assert mean(("Migr", "1", "0", "1"), "Rate") == 0.0
+
+
+def test_mark_pool_grows_on_overflow(tmp_path):
+    """migration marks live in a fixed pool per particle; when a particle needs more the engine raises a flag and the
+    driver repeats the sweep with twice the room -- the result is the one of a run that had enough room from the start"""
+    ref = json.load(open(REF))
+    outs = {}
+    for name, env in (("tiny", {"SMCSMC_MARKS_BASE": "1"}), ("ample", {"SMCSMC_MAX_MARKS": "60"})):
+        out = str(tmp_path / name)
+        cmd = [BIN] + ref["base"].format(extra="-EM 0 -lag 20000", seed=3, seg=SEG, out=out).split()
+        r = subprocess.run(cmd, capture_output=True, text=True, env=dict(os.environ, **env))
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[name] = (parse_out(out + ".out")[1], r.stderr)
+    assert "repeating the sweep" in outs["tiny"][1] and "repeating the sweep" not in outs["ample"][1]
+    for a, b in zip(outs["tiny"][0], outs["ample"][0]):
+        assert (a["Opp"], a["Count"]) == (b["Opp"], b["Count"]), (a, b)
+
