@@ -211,8 +211,12 @@ struct RingSink {
   }
   __device__ void coal(int e, double x, int cnt, double opp) const {
     int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
-    if (cnt) *cell(e, k, 0) += 1.0;
-    *cell(e, k, 1) += opp;
+    // count and opportunity sit side by side (16-byte aligned): one read-modify-write instead of two dependent ones
+    double2* c2 = reinterpret_cast<double2*>(cell(e, k, 0));
+    double2 v = *c2;
+    v.x += cnt ? 1.0 : 0.0;
+    v.y += opp;
+    *c2 = v;
   }
   // structured records (particle.cpp:251-300): coalescence opportunity / event of a floating lineage in population p,
   // and its migration opportunity dt / event p -> to
