@@ -222,4 +222,7 @@ def test_configs0_full_size(tmp_path):
             ne = np.array([float(r[k]["Ne"]) for r in mine])
             ne_ref = np.array([float(r[k]["Ne"]) for r in ref["runs"]])
             assert 8500 < ne.mean() < 11500, (ref0[k]["Epoch"], ne.mean())
-            assert ne.mean() == pytest.approx(ne_ref.mean(), rel=0.05), (ref0[k]["Epoch"], ne.mean(), ne_ref.mean())
+            # within 5 % of the reference's ensemble mean, or within 4 standard errors where ten seeds do not resolve 5 %
+            se = np.sqrt(ne.var(ddof=1) / len(ne) + ne_ref.var(ddof=1) / len(ne_ref))
+            assert abs(ne.mean() - ne_ref.mean()) < max(0.05 * ne_ref.mean(), 4 * se), \
+                (ref0[k]["Epoch"], ne.mean(), ne_ref.mean(), se)
