@@ -196,6 +196,30 @@ def golden_smc2_cmdlines():
                           "inv2N": inv.tolist(), "mig": mig.tolist(), "single_mig": single.tolist(),
                           "leaf_pop": pops.tolist(), "mu": R.ref_mutation_rate(h), "rho": R.ref_recombination_rate(h)})
             R.ref_close(h)
+    # further command lines a user (or smc2 -P / -p) may write: PSMC-style patterns, options out of time order,
+    # per-population sizes, symmetric and single migration rates, partial joins, admixture
+    extra = [
+        (4, "-N0 10000 -t 1000 -r 400 1000000 -p 1*3+15*4+1 -tmax 4"),
+        (4, "-N0 10000 -t 1000 -r 400 1000000 -p 4+25*2+4+6 -tmax 2"),
+        (4, "-N0 14312 -t 1000 -r 400 1000000 -eN 0.5 2 -eN 0.1 0.5 -eN 0 3"),
+        (6, "-N0 10000 -t 1000 -r 400 1000000 -I 2 3 3 2.0 -en 0.05 2 0.25 -eM 0.1 0.5 -en 0.2 1 4 -ej 0.7 2 1"),
+        (6, "-N0 10000 -t 1000 -r 400 1000000 -I 3 2 2 2 -ema 0 x 1 2 3 x 4 5 6 x -eps 0.2 3 1 0.4 -ej 0.5 3 2 -ej 0.9 2 1"),
+        (6, "-N0 10000 -t 1000 -r 400 1000000 -I 2 3 3 -em 0 1 2 0.7 -es 0.05 2 0.6 -en 0.05 3 0.3 -ej 0.3 3 1 -ej 0.6 2 1"),
+        (8, "-N0 10000 -t 1000 -r 400 1000000 -I 2 4 4 -ej 0.5 2 1 -eN 0.5 2 -eN 1.0 1"),
+    ]
+    for n, cmd in extra:
+        h = _libs.ref_open("smcsmc -nsam %d -Np 10 %s -seed 1" % (n, cmd))
+        E, Pn = R.ref_num_epochs(h), R.ref_num_pops(h)
+        ts, inv = np.zeros(E), np.zeros((E, Pn))
+        R.ref_epoch_table(h, P(ts), P(inv))
+        mig, single = np.zeros((E, Pn, Pn)), np.zeros((E, Pn, Pn))
+        R.ref_mig_table(h, P(mig), P(single))
+        pops = np.zeros(n, dtype=np.int32)
+        R.ref_sample_pops(h, P(pops))
+        cases.append({"model": "extra", "vb": False, "nsam": n, "cmd": cmd, "tmax_in_cmd": True, "t_start": ts.tolist(),
+                      "inv2N": inv.tolist(), "mig": mig.tolist(), "single_mig": single.tolist(),
+                      "leaf_pop": pops.tolist(), "mu": R.ref_mutation_rate(h), "rho": R.ref_recombination_rate(h)})
+        R.ref_close(h)
     json.dump(cases, open(os.path.join(HERE, "smc2_cmdlines.json"), "w"), indent=1)
 
 

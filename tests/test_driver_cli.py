@@ -121,9 +121,10 @@ def test_smc2_frontend_command_lines_parse_like_the_reference():
     import json
     import numpy as np
     cases = json.load(open(os.path.join(ROOT, "tests", "golden", "smc2_cmdlines.json")))
-    assert len(cases) >= 14 and any(c["vb"] and len(c["inv2N"][0]) == 2 for c in cases)
+    assert len(cases) >= 21 and any(c["vb"] and len(c["inv2N"][0]) == 2 for c in cases)
     for c in cases:
-        d = _dump("-nsam", str(c["nsam"]), "-Np", "10", "-tmax", "4", *c["cmd"].split(), "-seed", "1")
+        tmax = [] if c.get("tmax_in_cmd") else ["-tmax", "4"]
+        d = _dump("-nsam", str(c["nsam"]), "-Np", "10", *tmax, *c["cmd"].split(), "-seed", "1")
         E, P = np.array(c["inv2N"]).shape
         assert d["npop"] == P and d["epochs"] == E, c["model"]
         assert d["leaf_pop"] == c["leaf_pop"], c["model"]
