@@ -401,6 +401,7 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
       double rate = coal_count[at] / coal_opp[at];
       double pop = 1.0 / (2.0 * rate);
       P.epochs[e].pop_size[p] = (P.useCap && pop >= P.Ne_cap) ? P.Ne_cap : pop;
+      P.epochs[e].vb_count[p] = 1e10;   // Model::addPopulationSize's default event count: the in-binary M-step drops -vb counts
       clog << " Setting size of population " << p << " @ " << setw(8) << t_start[e] << " to " << setw(8) << pop
            << " ( 0.5 * " << coal_opp[at] << " / " << coal_count[at] << "; post-lag ESS "
            << 1.0 / (coal_weight[at] / coal_opp[at]) << " )" << endl;
@@ -409,7 +410,10 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     for (int e = 0; e < E; e++)
       for (int p = 0; p < np; p++)
         for (int q = 0; q < np; q++)
-          if (p != q) P.epochs[e].mig[(size_t)p * np + q] = mig_count[((size_t)e * np + p) * np + q] / mig_opp[(size_t)e * np + p];
+          if (p != q) {
+            P.epochs[e].mig[(size_t)p * np + q] = mig_count[((size_t)e * np + p) * np + q] / mig_opp[(size_t)e * np + p];
+            P.epochs[e].mig_vb[(size_t)p * np + q] = 1e10;                   // Model::addMigrationRate's default
+          }
 
   // CountModel::log_counts (count.cpp:66-158) and the LogL row (smcsmc.cpp:391)
   auto t_end = [&](int e) { return e == E - 1 ? 1e+99 : t_start[e + 1]; };

@@ -59,6 +59,12 @@ def _rows(path):
 @pytest.mark.parametrize("name, seg, model", [
     ("single", SEG1, "-nsam 4 -Np 400 -N0 10000 -t 2000 -r 800 2000000 -eN 0 1 -eN 0.05 1 -eN 0.2 1 -eN 0.6 1"),
     ("structured", SEG2, "-nsam 8 -Np 300 -N0 10000 -t 2000 -r 800 2000000 -I 2 4 4 -em 0 2 1 1 -eN 0.1 1 -ej 0.5 2 1"),
+    # -vb in the form the smc2 frontend writes it: an event count after every size and every migration rate
+    ("single_vb", SEG1, "-nsam 4 -Np 400 -N0 10000 -t 2000 -r 800 2000000 -vb -eN 0 1 40 -eN 0.05 1 60 -eN 0.2 1 25 "
+                        "-eN 0.6 1 10000000000.0"),
+    ("structured_vb", SEG2, "-nsam 8 -Np 300 -N0 10000 -t 2000 -r 800 2000000 -I 2 4 4 -vb -eN 0 1 50 "
+                            "-ema 0 0 1e10 0 1e10 1 30 0 1e10 -eN 0.1 1 80 -ema 0.1 0 1e10 0 1e10 1 45 0 1e10 "
+                            "-eN 0.5 1 1e10 -ema 0.5 0 1e10 0 1e10 1 1e10 0 1e10 -ej 0.5 2 1"),
 ])
 def test_patched_reference_driver_equals_drop_in_driver(tmp_path, name, seg, model):
     if not os.path.exists(PATCHED):
