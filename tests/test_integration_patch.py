@@ -19,6 +19,7 @@ BIN = os.path.join(ROOT, "smcsmc_b200", "bin", "smcsmc")
 SEG1 = os.path.join(ROOT, "tests", "data", "const_n4_2Mb_seed7.seg")
 SEG2 = os.path.join(ROOT, "tests", "data", "split_mig_n8_2Mb_seed13.seg")
 HAVE_REF = os.path.isdir("/root/reference/src")
+BASE1 = "-nsam 4 -Np 300 -N0 10000 -t 2000 -r 800 2000000 -eN 0 1 -eN 0.05 1 -eN 0.2 1 -eN 0.6 1"
 
 
 @pytest.mark.skipif(not HAVE_REF, reason="needs the reference sources (/root/reference) to build the patched driver")
@@ -65,6 +66,14 @@ def _rows(path):
     ("structured_vb", SEG2, "-nsam 8 -Np 300 -N0 10000 -t 2000 -r 800 2000000 -I 2 4 4 -vb -eN 0 1 50 "
                             "-ema 0 0 1e10 0 1e10 1 30 0 1e10 -eN 0.1 1 80 -ema 0.1 0 1e10 0 1e10 1 45 0 1e10 "
                             "-eN 0.5 1 1e10 -ema 0.5 0 1e10 0 1e10 1 1e10 0 1e10 -ej 0.5 2 1"),
+    # the other flags of the boundary that reach the engine or the M-step
+    ("aa_masks", SEG1, BASE1 + " -ancestral_aware -xr 1-2 -xc 0"),
+    ("cap_ess", SEG1, BASE1 + " -cap 9800 -ESS 0.9"),
+    ("pattern", SEG1, "-nsam 4 -Np 300 -N0 10000 -t 2000 -r 800 2000000 -p 1*2+3*2+1 -tmax 3"),
+    ("window", SEG1, "-nsam 4 -Np 300 -N0 10000 -t 1000 -r 400 1000000 -eN 0 1 -eN 0.1 1 -startpos 500001"),
+    ("dephase", SEG2, "-nsam 8 -Np 200 -N0 10000 -t 2000 -r 800 2000000 -eN 0 1 -eN 0.1 1 -dephase"),
+    ("admixture", SEG2, "-nsam 8 -Np 200 -N0 10000 -t 2000 -r 800 2000000 -I 2 4 4 0.5 -es 0.05 1 0.4 -ej 0.3 3 2 "
+                        "-ej 0.8 2 1"),
 ])
 def test_patched_reference_driver_equals_drop_in_driver(tmp_path, name, seg, model):
     if not os.path.exists(PATCHED):
