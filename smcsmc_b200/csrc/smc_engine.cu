@@ -1422,7 +1422,23 @@ static int read_ctrl(smc_engine* e, Ctrl* c);
 const char* smc_last_error(void) { return g_err.c_str(); }
 const char* smc_version(void) { return "smcsmc_b200 0.1 (sm_100a)"; }
 
+// SMC_DEBUG_ARGS=1: one line per call with the scalar arguments and an FNV-1a checksum of every array, to compare what two
+// host programs hand to the engine
+static unsigned long long dbg_hash(const void* p, size_t bytes) {
+  unsigned long long h = 1469598103934665603ull;
+  const unsigned char* c = (const unsigned char*)p;
+  for (size_t k = 0; k < bytes; k++) { h ^= c[k]; h *= 1099511628211ull; }
+  return p ? h : 0ull;
+}
+static bool dbg_args() { static const bool on = getenv("SMC_DEBUG_ARGS") != nullptr; return on; }
+
 int smc_create(const smc_config* cfg, smc_engine** out) {
+  if (cfg && dbg_args())
+    fprintf(stderr, "[smc args] create n=%d N=%d E=%d seed=%llu chunk=%u slot=%u mu=%.17g rho=%.17g seqlen=%.17g start=%.17g ess=%.17g aa=%d "
+            "t_start=%llx inv2N=%llx vb=%llx mask=%llx lags=%llx\n", cfg->n, cfg->N, cfg->E, (unsigned long long)cfg->seed, cfg->chunk,
+            cfg->slot_offset, cfg->mu, cfg->rho, cfg->seqlen, cfg->start_pos, cfg->ess_fraction, cfg->ancestral_aware,
+            dbg_hash(cfg->t_start, cfg->E * 8), dbg_hash(cfg->inv2N, cfg->E * 8), dbg_hash(cfg->vb_logfac, cfg->vb_logfac ? cfg->E * 8 : 0),
+            dbg_hash(cfg->rec_mask, cfg->rec_mask ? cfg->E : 0), dbg_hash(cfg->lags, cfg->E * 8));
   if (!cfg || !out) return fail(SMC_ERR_ARG, "null argument");
   *out = nullptr;
   if (cfg->N < 1) return fail(SMC_ERR_ARG, "N must be >= 1");
@@ -1701,6 +1717,10 @@ int smc_get_population_state(smc_engine* e, int32_t* pop, int32_t* nmarks, int32
 
 int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, const uint8_t* is_site,
                     const int32_t* max_rec_epoch, int64_t R) {
+  if (e && dbg_args())
+    fprintf(stderr, "[smc args] rows R=%lld x_end=%llx alleles=%llx is_site=%llx max_rec=%llx\n", (long long)R,
+            dbg_hash(x_end, (size_t)R * 8), dbg_hash(alleles, (size_t)R * e->cfg.n), dbg_hash(is_site, (size_t)R),
+            dbg_hash(max_rec_epoch, max_rec_epoch ? (size_t)R * 4 : 0));
   if (e) e->graph_dirty = true;
   if (!e || !x_end || !alleles || !is_site) return fail(SMC_ERR_ARG, "null argument");
   if (R < 1) return fail(SMC_ERR_ARG, "R must be >= 1");
@@ -2024,8 +2044,9 @@ int smc_get_lnZ(smc_engine* e, double* lnZ) {
   int rc = read_ctrl(e, &c);
   if (rc) return rc;
   *lnZ = c.lnZ;
-  if (c.sflags & SFLAG_NOCOAL) return fail(SMC_ERR_NUMERIC, "Lines did not coalescence: the populations of the model never join and do not exchange migrants");
+  // an overflowing mark pool loses population changes, after which a lineage may well be stranded: report the cause
   if (c.sflags & SFLAG_MARKS) return fail(SMC_ERR_NUMERIC, "a particle needed more migration marks than max_marks (smc_set_populations)");
+  if (c.sflags & SFLAG_NOCOAL) return fail(SMC_ERR_NUMERIC, "Lines did not coalescence: the populations of the model never join and do not exchange migrants");
   if (c.err) return fail(SMC_ERR_NUMERIC, "Zero or negative probabilities");
   return 0;
 }

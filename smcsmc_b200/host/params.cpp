@@ -190,6 +190,8 @@ void parse(int argc, char** argv, Params& P) {
   s.v = scrm;
   bool have_t = false, have_r = false;
   double min_time = 0.0;
+  size_t L_cur = 1;                            // the default Model's locus length (model.cc:31)
+  double mu_bits = 0.0, rho_bits = 0.0;
   auto time_of = [&](const std::string& f, bool timed) {
     double t = timed ? s.next_double(f) : 0.0;
     if (t < min_time)
@@ -203,8 +205,26 @@ void parse(int argc, char** argv, Params& P) {
   };
   for (; s.more(); s.i++) {
     const std::string f = s.cur();
-    if (f == "-t") { P.theta = s.next_double(f); have_t = true; }
-    else if (f == "-r") { P.rho_per_locus = s.next_double(f); P.loci_length = s.next_double(f); have_r = true; }
+    if (f == "-t") {
+      // Model::setMutationRate(theta, per_locus, scaled) at the locus length known so far (model.cc:749-759)
+      P.theta = s.next_double(f); have_t = true;
+      double rate = P.theta;
+      rate /= 4.0 * P.N0;
+      mu_bits = rate / (double)L_cur;
+    }
+    else if (f == "-r") {
+      // Model::setLocusLength rescales the per-base mutation rate, then setRecombinationRate (param.cc:102-106,
+      // model.h:455-462): reproduced operation for operation so that the rates carry the reference's last bits
+      P.rho_per_locus = s.next_double(f); P.loci_length = s.next_double(f); have_r = true;
+      const size_t L_new = (size_t)P.loci_length;
+      if (L_new > 1) {
+        mu_bits *= (double)L_cur / L_new;
+        L_cur = L_new;
+        double rate = P.rho_per_locus;
+        rate /= 4.0 * P.N0;
+        rho_bits = rate / (double)(L_cur - 1);
+      }
+    }
     else if (f == "-N0") { (void)s.next(f); }
     else if (f == "-vb" || f == "-VB") {
       if (P.epochs.size() > 1) throw std::invalid_argument("-vb must occur before -eN / -en / -eM / -ema");
@@ -332,6 +352,8 @@ void parse(int argc, char** argv, Params& P) {
   if (P.npop > 1 && !P.has_migration)      // Model::check (model.cc:630-633)
     throw std::invalid_argument("Model has multiple populations but no migration. Coalescence impossible");
   finalize_rates(P);
+  P.mutation_rate = mu_bits;               // the same numbers as finalize_rates, with the reference's rounding
+  P.recombination_rate = P.original_recombination_rate = rho_bits;
 }
 
 // Model::finalize (model.cc:553-670): sizes not given at a change time continue from the epoch before (default N0),

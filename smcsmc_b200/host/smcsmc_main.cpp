@@ -153,7 +153,13 @@ struct FlatModel {
   explicit FlatModel(const Params& P) : E(P.num_epochs()), np(P.npop) {
     for (const auto& e : P.epochs) {
       t_start.push_back(e.t_start);
-      for (int p = 0; p < np; p++) inv2N.push_back(1.0 / (2.0 * e.pop_size[p]));
+      for (int p = 0; p < np; p++) {
+        // the same roundings as the reference's own round trip: Model stores 1/(2N), population_size() returns
+        // 0.5 / stored, the engine takes 1 / (2 * population_size()) (model.cc:268-281, model.h:167-169)
+        const double stored = 1.0 / (2.0 * e.pop_size[p]);
+        const double size = 0.5 / stored;
+        inv2N.push_back(1.0 / (2.0 * size));
+      }
       mig.insert(mig.end(), e.mig.begin(), e.mig.end());
       single_mig.insert(single_mig.end(), e.single_mig.begin(), e.single_mig.end());
     }
