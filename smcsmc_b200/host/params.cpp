@@ -161,9 +161,8 @@ void parse(int argc, char** argv, Params& P) {
   }
   if (P.help || P.version) return;
 
-  // ---- the scrm part (param.cc): two passes so that -N0 applies wherever it stands ----
-  for (size_t k = 0; k + 1 < scrm.size(); k++)
-    if (scrm[k] == "-N0") P.N0 = to_double(scrm[k + 1], "-N0");
+  // ---- the scrm part (param.cc), options in the order given: like scrm, -N0 scales what FOLLOWS it (theta, times,
+  // sizes, migration rates), so a command line that names it late is read the way the reference reads it ----
   // -I fixes the number of populations; every table row is sized by it, so it is read ahead of the other options
   // (scrm itself needs -I to come first for the same reason, param.cc:148-160)
   g_cur_pops = 1;
@@ -191,6 +190,7 @@ void parse(int argc, char** argv, Params& P) {
   bool have_t = false, have_r = false;
   double min_time = 0.0;
   size_t L_cur = 1;                            // the default Model's locus length (model.cc:31)
+  bool n0_used = false;                        // Model::default_pop_size() was consulted (scaling_factor_ > 0)
   double mu_bits = 0.0, rho_bits = 0.0;
   auto time_of = [&](const std::string& f, bool timed) {
     double t = timed ? s.next_double(f) : 0.0;
@@ -205,6 +205,9 @@ void parse(int argc, char** argv, Params& P) {
   };
   for (; s.more(); s.i++) {
     const std::string f = s.cur();
+    if (f != "-N0" && f != "-vb" && f != "-VB" && f != "-seed" && f != "--seed" && f != "-seeds" && f != "--seeds" &&
+        f != "-l" && f != "-I")
+      n0_used = true;                            // every other option scales a rate, a size or a time with N0
     if (f == "-t") {
       // Model::setMutationRate(theta, per_locus, scaled) at the locus length known so far (model.cc:749-759)
       P.theta = s.next_double(f); have_t = true;
@@ -225,7 +228,12 @@ void parse(int argc, char** argv, Params& P) {
         rho_bits = rate / (double)(L_cur - 1);
       }
     }
-    else if (f == "-N0") { (void)s.next(f); }
+    else if (f == "-N0") {
+      // Model::set_default_pop_size(int) (model.h:85-88): an integer, and only before anything was scaled with it
+      const double v = s.next_double(f);
+      if (n0_used) throw std::invalid_argument("Default population size (-N0) must be set before other population-related parameters");
+      P.N0 = (double)(int)v;
+    }
     else if (f == "-vb" || f == "-VB") {
       if (P.epochs.size() > 1) throw std::invalid_argument("-vb must occur before -eN / -en / -eM / -ema");
       P.vb = true;
@@ -266,6 +274,7 @@ void parse(int argc, char** argv, Params& P) {
         double M = std::strtod(s.v[s.i + 1].c_str(), &end);
         if (end != s.v[s.i + 1].c_str() && *end == '\0') {
           s.i++;
+          n0_used = true;
           if (g_cur_pops > 1) { add_mig_all(P, 0.0, M / (g_cur_pops - 1)); if (M > 0) P.has_migration = true; }
         }
       }

@@ -206,6 +206,10 @@ def golden_smc2_cmdlines():
         (6, "-N0 10000 -t 1000 -r 400 1000000 -I 3 2 2 2 -ema 0 x 1 2 3 x 4 5 6 x -eps 0.2 3 1 0.4 -ej 0.5 3 2 -ej 0.9 2 1"),
         (6, "-N0 10000 -t 1000 -r 400 1000000 -I 2 3 3 -em 0 1 2 0.7 -es 0.05 2 0.6 -en 0.05 3 0.3 -ej 0.3 3 1 -ej 0.6 2 1"),
         (8, "-N0 10000 -t 1000 -r 400 1000000 -I 2 4 4 -ej 0.5 2 1 -eN 0.5 2 -eN 1.0 1"),
+        # -N0 is read as an integer (Model::set_default_pop_size(int))
+        (4, "-N0 14312.7 -t 1000 -r 400 1000000 -eN 0.1 2 -eN 0.3 0.5"),
+        # -r before -t: the mutation rate is divided by the final locus length directly
+        (4, "-N0 5000 -r 400 1000000 -t 1000 -eN 0.2 3"),
     ]
     for n, cmd in extra:
         h = _libs.ref_open("smcsmc -nsam %d -Np 10 %s -seed 1" % (n, cmd))

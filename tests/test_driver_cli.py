@@ -47,6 +47,7 @@ def test_help_and_version():
     (["-Np", "10", "-t", "10", "-r", "10", "1", ], "Locus length must be at least two"),
     (["-Np", "10", "-t", "10", "-r", "10", "1000", "-eN", "0.1", "1", "-vb"], "-vb must occur before"),
     (["-Np", "10", "-t", "10", "-r", "10", "1000", "-nsam", "40"], "-nsam must be between 2 and 32"),
+    (["-Np", "10", "-t", "10", "-r", "10", "1000", "-N0", "5000"], "(-N0) must be set before other population-related"),
 ])
 def test_parse_errors(args, message):
     r = run(*args)
@@ -120,7 +121,7 @@ def test_smc2_frontend_command_lines_parse_like_the_reference():
     import json
     import numpy as np
     cases = json.load(open(os.path.join(ROOT, "tests", "golden", "smc2_cmdlines.json")))
-    assert len(cases) >= 21 and any(c["vb"] and len(c["inv2N"][0]) == 2 for c in cases)
+    assert len(cases) >= 23 and any(c["vb"] and len(c["inv2N"][0]) == 2 for c in cases)
     for c in cases:
         tmax = [] if c.get("tmax_in_cmd") else ["-tmax", "4"]
         d = _dump("-nsam", str(c["nsam"]), "-Np", "10", *tmax, *c["cmd"].split(), "-seed", "1")
