@@ -196,6 +196,24 @@ int smc_calibrate_survival_struct(int device, int32_t n, int32_t E, const double
 /* fastexp (particle.cpp:30-40) evaluated on the device, for the 1e-12 no-mutation-factor parity test */
 int smc_fastexp(int device, const double* x, int64_t count, double* out);
 
+/* ---- allocation-free entry point ------------------------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same computation as
+ * smc_resample_counts (partial sums -- sequential when parity_scan -- then ESS and the bit-exact systematic offspring
+ * counts), but
+ *   - d_w[N], d_ess[1] and d_counts[N] are DEVICE pointers on `device`, supplied by the caller;
+ *   - the scratch (u-chain control block + N+1 partial sums) is a file-scope static __device__ array of
+ *     (SMC_NOALLOC_MAX_N + 1) * 8 bytes plus a ~6 KB control block (about 1.06 MB) that every GPU loading the library
+ *     holds until exit; N > SMC_NOALLOC_MAX_N is rejected with SMC_ERR_ARG;
+ *   - the work is queued on `stream` (a cudaStream_t passed as void*, NULL = the default stream) and the call returns
+ *     without synchronising; it calls no cudaMalloc / cudaFree / allocating library routine.
+ * Every call on a device shares the one array (the control block is cleared on the stream at the start of each call):
+ * calls that overlap on the GPU -- different streams, or graph replays in flight together -- race; serialise them.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress); make it outside graph capture. */
+#define SMC_NOALLOC_MAX_N 131072
+int smc_resample_counts_noalloc(int device, const double* d_w, int64_t N, double u, int32_t parity_scan,
+                                double* d_ess, int32_t* d_counts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

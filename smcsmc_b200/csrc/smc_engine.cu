@@ -2391,3 +2391,60 @@ int smc_fastexp(int device, const double* x, int64_t count, double* out) {
 }
 
 }  // extern "C"
+
+// ---- allocation-free variant of smc_resample_counts (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops) ------------
+// The scratch smc_resample_counts takes from cudaMalloc (the u-chain control block and the N+1 partial sums) lives in a
+// file-scope device array instead.  Every GPU that loads libsmcgpu.so holds these SMC_NOALLOC_SCRATCH_BYTES until exit.
+// In host code the array's name is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, asked once per device with that device current (noalloc_scratch below).
+constexpr size_t NOALLOC_CTRL_BYTES = (sizeof(Ctrl) + 255) / 256 * 256;
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_CTRL_BYTES + ((size_t)SMC_NOALLOC_MAX_N + 1) * sizeof(double);
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// device address of g_noalloc_scratch on `device`, which must be the current device
+int noalloc_scratch(int device, unsigned char** out) {
+  if (device >= NOALLOC_MAX_DEVICES) return fail(SMC_ERR_ARG, "device ordinal beyond the no-alloc scratch table (64)");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[device]) {
+    void* ptr = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+    if (!ptr) return fail(SMC_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the no-alloc scratch");
+    g_noalloc_ptr[device] = ptr;
+  }
+  *out = (unsigned char*)g_noalloc_ptr[device];
+  return 0;
+}
+}  // namespace
+
+extern "C" int smc_resample_counts_noalloc(int device, const double* d_w, int64_t N, double u, int32_t parity_scan,
+                                           double* d_ess, int32_t* d_counts, void* stream) {
+  if (!d_w || !d_counts || !d_ess) return fail(SMC_ERR_ARG, "null argument");
+  if (N < 1) return fail(SMC_ERR_ARG, "N must be >= 1");
+  if (N > SMC_NOALLOC_MAX_N)
+    return fail(SMC_ERR_ARG, "smc_resample_counts_noalloc: N = " + std::to_string((long long)N) +
+                                 " exceeds the static scratch capacity SMC_NOALLOC_MAX_N = " +
+                                 std::to_string((long long)SMC_NOALLOC_MAX_N) + " (use smc_resample_counts)");
+  if (!(u >= 0.0 && u < 1.0)) return fail(SMC_ERR_ARG, "u must be in [0,1)");
+  int rc = use_device(device);
+  if (rc) return rc;
+  unsigned char* scratch = nullptr;
+  if ((rc = noalloc_scratch(device, &scratch))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  Ctrl* ctrl = (Ctrl*)scratch;
+  double* psum = (double*)(scratch + NOALLOC_CTRL_BYTES);
+  // the array keeps the previous call's contents: the control block must start at zero, the partial sums are
+  // overwritten in full ([0, N]) before they are read
+  CUDA_TRY(cudaMemsetAsync(ctrl, 0, sizeof(Ctrl), st));
+  if (parity_scan) k_seq_partial_sums<<<1, 1, 0, st>>>(d_w, N, psum, d_ess);
+  else k_par_partial_sums<<<1, 1024, 0, st>>>(d_w, N, psum, d_ess);
+  k_build_chain<<<1, 1, 0, st>>>(ctrl, u, N);
+  k_offspring_counts<<<(unsigned)((N + 127) / 128), 128, 0, st>>>(ctrl, psum, N, d_counts);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
