@@ -16,6 +16,7 @@
 //   ParticleContainer::calculate_initial_haplotype_configuration / next_haplotype   particleContainer.cpp:138,163
 //   Forest::buildInitialTree / sampleNextGenealogy / sampleRecSeqPosition   scrm/src/forest.cc:299,423,474
 //   CountModel::extract_and_update_count         count.cpp:355
+//   ForestState copy-ctor / resample_recombination_position / record_recomb_extension   particle.cpp:113,393,305
 #include <vector>
 #include <string>
 #include <queue>
@@ -498,6 +499,64 @@ extern "C" int ref_tally_script(void* hv, int N, const double* lags, const doubl
       out[5 * E + e] = cm.total_recomb_weight[e][0] - base[5 * E + e];
     }
     pc.clear();
+    return 0;
+  } catch (std::exception& e) { g_err = e.what(); return 1; }
+}
+
+
+// The reference's REAL recording path around a spawn, with the heap block of the copy pre-filled with a byte pattern.
+// extend_ARG, when a particle of multiplicity > 1 recombines (particle.cpp:836-854), runs
+//     spawn()  ->  new ForestState(*this)            (particle.hpp:137, copy constructor particle.cpp:113-136)
+//     copy->set_current_base(updated_to); copy->setMultiplicity(mult - 1);
+//     copy->resample_recombination_position();       (particle.cpp:393-436)
+// and only later does ParticleContainer::extend_ARGs assign copy->max_epoch_to_record_ (particleContainer.cpp:123).  The
+// copy constructor never writes that field, so the guard `epoch <= max_epoch_to_record_` (particle.cpp:402) reads whatever
+// the allocator handed out.  The probe makes "whatever" explicit: the copy is placement-constructed into a block filled
+// with fill_byte.  Outputs: the field as the copy sees it, the number of epochs that hold a recombination-opportunity
+// record of the parent, the number of those whose record the copy extended to its new next_base, and the opportunity
+// (lineages x generations x bp) recorded for the copy's stretch [spawn point, new next_base) next to the tree length
+// times that distance.
+extern "C" int ref_spawn_probe(void* hv, int fill_byte, int* field_seen, int* epochs_recorded, int* epochs_extended,
+                               double* recorded, double* expected) {
+  RefHandle* h = (RefHandle*)hv;
+  try {
+    Model* model = &h->pf->model;
+    const int E = (int)model->change_times_.size();
+    ForestState* p = new ForestState(model, h->rng, h->pf, false);
+    p->init_EventContainers(model);
+    p->buildInitialTree(true);
+    p->set_max_epoch_to_record(E - 1);
+    p->record_recomb_extension();            // as the ParticleContainer constructor does (particleContainer.cpp:54)
+    p->save_recomb_state();
+    p->setMultiplicity(3);
+    const double updated_to = p->next_base();   // the parent's recombination point
+    void* mem = operator new(sizeof(ForestState));
+    memset(mem, fill_byte, sizeof(ForestState));
+    ForestState* c = new (mem) ForestState(*p);  // == spawn()
+    *field_seen = c->max_epoch_to_record_;
+    c->set_current_base(updated_to);
+    c->setMultiplicity(2);
+    p->save_recomb_state();
+    c->restore_recomb_state();
+    c->resample_recombination_position();
+    c->save_recomb_state();
+    p->restore_recomb_state();
+    const double x1 = c->next_base();
+    *epochs_recorded = 0; *epochs_extended = 0; *recorded = 0.0;
+    for (int e = 0; e < E; e++) {
+      if (p->eventTrees[e] && p->eventTrees[e]->is_recomb()) (*epochs_recorded)++;
+      bool extended = false;
+      for (EvolutionaryEvent* ev = c->eventTrees[e]; ev; ev = ev->parent()) {
+        if (!ev->is_recomb()) continue;
+        if (ev->end_base() == x1) extended = true;
+        *recorded += ev->recomb_opportunity_between(0.0, DBL_MAX, updated_to, x1);
+      }
+      if (extended) (*epochs_extended)++;
+    }
+    *expected = c->getLocalTreeLength() * (x1 - updated_to);
+    c->~ForestState();
+    operator delete(mem);
+    delete p;
     return 0;
   } catch (std::exception& e) { g_err = e.what(); return 1; }
 }

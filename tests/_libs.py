@@ -207,6 +207,8 @@ def ref():
         L.ref_arg_walk.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 4
         L.ref_tally_script.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                        ctypes.c_long, ctypes.c_void_p]
+        if hasattr(L, "ref_spawn_probe"):
+            L.ref_spawn_probe.argtypes = [ctypes.c_void_p, ctypes.c_int, c_ip, c_ip, c_ip, c_dp, c_dp]
         _ref = L
     return _ref
 
@@ -231,6 +233,17 @@ def ref_open(cmdline):
     if not h:
         raise RuntimeError("ref_open failed: %s" % L.ref_last_error())
     return ctypes.c_void_p(h)
+
+
+def ref_spawn_probe(h, fill_byte):
+    """oracle/ref_harness.cpp::ref_spawn_probe -> dict(field, epochs_recorded, epochs_extended, recorded, expected)"""
+    L = ref()
+    f, a, b = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    r, e = ctypes.c_double(), ctypes.c_double()
+    if L.ref_spawn_probe(h, fill_byte, ctypes.byref(f), ctypes.byref(a), ctypes.byref(b), ctypes.byref(r), ctypes.byref(e)):
+        raise RuntimeError("ref_spawn_probe failed: %s" % L.ref_last_error())
+    return {"field": f.value, "epochs_recorded": a.value, "epochs_extended": b.value, "recorded": r.value,
+            "expected": e.value}
 
 
 def ref_model(h, n, seqlen):

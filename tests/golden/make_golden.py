@@ -347,7 +347,20 @@ EM_VARIANTS = {
     # three in-binary EM iterations on the population sizes; recombination excluded from the EM (-xr) so that the
     # recombination rate stays at its input value (see DESIGN.md 7a on the reference's recombination opportunity)
     "em_ne": "-xr 0-3 -EM 2",
+    # three in-binary EM iterations on the population sizes AND the recombination rate (CountModel::reset_recomb_rate,
+    # count.cpp:296-325) -- comparable since the corrected reference tallies the full recombination opportunity
+    "em_rho": "-EM 2",
 }
+
+
+def ref_binary(fixed=True):
+    """oracle/_ref/smcsmc_fixed: the reference with ForestState::max_epoch_to_record_ initialised (two added lines,
+    tools/patch_reference_uninit.py, built by oracle/build_fixed_ref.sh).  The unmodified binary reads that field
+    uninitialised when a particle with multiplicity > 1 recombines and loses 15-20 % of the recombination opportunity,
+    by an amount that changes with the process environment -- it cannot serve as a fixture source for
+    anything that depends on the recombination opportunity."""
+    d = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref")
+    return os.path.join(d, "smcsmc_fixed" if fixed else "smcsmc")
 
 
 def parse_out(path):
@@ -360,10 +373,9 @@ def parse_out(path):
 
 
 # BASELINE.json configs[0] at full size: 4 haplotypes x 10 Mb simulated under a constant size, inferred with 8 log-spaced
-# epochs from all-ones sizes, 1000 particles, 3 EM iterations (4 sweeps), seeds 1..10; recombination excluded from the
-# EM for the reason given above
+# epochs from all-ones sizes, 1000 particles, 3 EM iterations (4 sweeps), seeds 1..10; EM on sizes and recombination rate
 C0_BASE = ("-nsam 4 -Np 1000 -N0 10000 -t 10000 -r 4000 10000000 -eN 0 1 -eN 0.01 1 -eN 0.02 1 -eN 0.04 1 -eN 0.08 1 "
-           "-eN 0.16 1 -eN 0.32 1 -eN 0.64 1 -xr 0-7 -EM 3 -seed {seed} -seg {seg} -o {out}")
+           "-eN 0.16 1 -eN 0.32 1 -eN 0.64 1 -EM 3 -seed {seed} -seg {seg} -o {out}")
 
 
 def golden_configs0(seeds=range(1, 11)):
@@ -375,8 +387,8 @@ def golden_configs0(seeds=range(1, 11)):
     import tempfile
     from concurrent.futures import ThreadPoolExecutor
     segz = os.path.join(os.path.dirname(HERE), "data", "const_n4_10Mb_seed11.seg.gz")
-    binp = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref", "smcsmc")
-    out = {"base": C0_BASE, "seeds": list(seeds)}
+    binp = ref_binary()
+    out = {"base": C0_BASE, "seeds": list(seeds), "binary": "smcsmc_fixed"}
     with tempfile.TemporaryDirectory() as tmp:
         seg = os.path.join(tmp, "c0.seg")
         with gzip.open(segz, "rb") as f, open(seg, "wb") as g:
@@ -400,6 +412,8 @@ EM_STRUCT_VARIANTS = {
     "sweep": "-EM 0",
     # three in-binary EM iterations on population sizes AND migration rates (recombination excluded)
     "em": "-xr 0-2 -EM 2",
+    # the same with the recombination rate in the EM as well
+    "em_all": "-EM 2",
 }
 
 
@@ -411,8 +425,8 @@ def golden_em_struct(seeds=range(1, 13)):
     import tempfile
     from concurrent.futures import ThreadPoolExecutor
     seg = os.path.join(os.path.dirname(HERE), "data", "split_mig_n8_2Mb_seed13.seg")
-    binp = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref", "smcsmc")
-    out = {"base": EM_STRUCT_BASE, "variants": EM_STRUCT_VARIANTS, "seeds": list(seeds), "runs": {}}
+    binp = ref_binary()
+    out = {"base": EM_STRUCT_BASE, "variants": EM_STRUCT_VARIANTS, "seeds": list(seeds), "runs": {}, "binary": "smcsmc_fixed"}
     with tempfile.TemporaryDirectory() as tmp:
         for name, extra in EM_STRUCT_VARIANTS.items():
             def run(seed):
@@ -425,7 +439,7 @@ def golden_em_struct(seeds=range(1, 13)):
     json.dump(out, open(os.path.join(HERE, "em_struct_reference.json"), "w"))
 
 
-def golden_em(seeds=range(1, 13)):
+def golden_em(seeds=range(1, 25)):
     """End-to-end reference runs (the unmodified smcsmc binary, oracle/_ref/smcsmc) on tests/data/const_n4_2Mb_seed7.seg:
     12 seeds per command variant; stores every .out row per seed (tests/test_em_parity.py compares the B200 driver's
     seed ensemble with this one)."""
@@ -434,8 +448,8 @@ def golden_em(seeds=range(1, 13)):
     import tempfile
     from concurrent.futures import ThreadPoolExecutor
     seg = os.path.join(os.path.dirname(HERE), "data", "const_n4_2Mb_seed7.seg")
-    binp = os.path.join(os.path.dirname(os.path.dirname(HERE)), "oracle", "_ref", "smcsmc")
-    out = {"base": EM_BASE, "variants": EM_VARIANTS, "seeds": list(seeds), "runs": {}}
+    binp = ref_binary()
+    out = {"base": EM_BASE, "variants": EM_VARIANTS, "seeds": list(seeds), "runs": {}, "binary": "smcsmc_fixed"}
     with tempfile.TemporaryDirectory() as tmp:
         for name, extra in EM_VARIANTS.items():
             def run(seed):
@@ -445,4 +459,82 @@ def golden_em(seeds=range(1, 13)):
                 return parse_out(o + ".out")
             with ThreadPoolExecutor(8) as ex:
                 out["runs"][name] = list(ex.map(run, seeds))
+
+        # the UNMODIFIED binary on the sweep, twice per seed under environments of different size: its recombination
+        # opportunity is low and not even a function of its inputs (the Coal rows and the recombination count are)
+        def run_unmodified(arg):
+            seed, pad = arg
+            o = os.path.join(tmp, "u_s%d_%d" % (seed, pad))
+            env = dict(os.environ, SMC_ENV_PAD="x" * pad)
+            subprocess.run([ref_binary(False)] + EM_BASE.format(extra="-EM 0", seed=seed, seg=seg, out=o).split(),
+                           check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, env=env)
+            return parse_out(o + ".out")
+        with ThreadPoolExecutor(8) as ex:
+            out["unmodified_sweep"] = {str(pad): list(ex.map(run_unmodified, [(sd, pad) for sd in seeds]))
+                                       for pad in (0, 64)}
     json.dump(out, open(os.path.join(HERE, "em_reference.json"), "w"))
+
+
+def golden_spawn_probe():
+    """oracle/ref_harness.cpp::ref_spawn_probe on the unmodified reference: what a spawned particle records for its
+    first stretch as a function of the bytes its heap block held (tests/test_oracle_golden.py)."""
+    import json
+    cmd = "-nsam 4 -Np 10 -N0 10000 -t 2000 -r 800 2000000 -eN 0 1 -eN 0.05 1 -eN 0.2 1 -eN 0.6 1 -seed 3"
+    h = _libs.ref_open("smcsmc " + cmd)
+    out = {"cmd": cmd, "probes": []}
+    for fill in (0x00, 0xFF, 0x7F, 0x01):
+        for _ in range(4):
+            r = _libs.ref_spawn_probe(h, fill)
+            r["fill"] = fill
+            out["probes"].append(r)
+    json.dump(out, open(os.path.join(HERE, "spawn_probe.json"), "w"), indent=1)
+
+
+# BASELINE.json configs[1] in medium: 8 haplotypes, the first 10 Mb of the zigzag bench data, the 11 zigzag epochs from
+# all-ones sizes, 1000 particles, 5 EM iterations (6 sweeps) on sizes and recombination rate, seeds 1..10
+C1_TIMES = [0, .0025, .005, .01, .02, .04, .08, .16, .32, .64, 1.28]
+C1_BASE = ("-nsam 8 -Np 1000 -N0 10000 -t 10000 -r 4000 10000000 " + " ".join("-eN %r 1" % t for t in C1_TIMES) +
+           " -EM 5 -seed {seed} -seg {seg} -o {out}")
+# BASELINE.json configs[2] in medium: 4 + 4 haplotypes, the first 5 Mb of bench_data/split_mig_n8_10Mb_seed3.seg.gz,
+# 2000 particles, 2 EM iterations (3 sweeps) on sizes, migration and recombination rates, seeds 1..10
+C2_BASE = ("-nsam 8 -Np 2000 -N0 10000 -t 5000 -r 2000 5000000 -I 2 4 4 -em 0 2 1 1 -eN 0.1 1 -ej 0.5 2 1 -EM 2 "
+           "-seed {seed} -seg {seg} -o {out}")
+
+
+def cut_seg(gz_path, out_path, length):
+    """the rows of a .seg.gz that start before `length` (the driver clips the last one to the locus length)"""
+    import gzip
+    with gzip.open(gz_path, "rt") as f, open(out_path, "w") as g:
+        for line in f:
+            if not line.startswith("#") and int(line.split("\t", 1)[0]) > length:
+                break
+            g.write(line)
+
+
+def _golden_medium(name, base, gz, length, seeds):
+    import json
+    import subprocess
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+    root = os.path.dirname(os.path.dirname(HERE))
+    out = {"base": base, "seeds": list(seeds), "binary": "smcsmc_fixed", "data": gz, "length": length}
+    with tempfile.TemporaryDirectory() as tmp:
+        seg = os.path.join(tmp, "d.seg")
+        cut_seg(os.path.join(root, gz), seg, length)
+
+        def run(seed):
+            o = os.path.join(tmp, "s%d" % seed)
+            subprocess.run([ref_binary()] + base.format(seed=seed, seg=seg, out=o).split(), check=True,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            return parse_out(o + ".out")
+        with ThreadPoolExecutor(8) as ex:
+            out["runs"] = list(ex.map(run, seeds))
+    json.dump(out, open(os.path.join(HERE, name), "w"))
+
+
+def golden_configs1_medium(seeds=range(1, 11)):
+    _golden_medium("configs1_medium_reference.json", C1_BASE, "bench_data/zigzag_n8_100Mb_seed1.seg.gz", 10000000, seeds)
+
+
+def golden_configs2_medium(seeds=range(1, 11)):
+    _golden_medium("configs2_medium_reference.json", C2_BASE, "bench_data/split_mig_n8_10Mb_seed3.seg.gz", 5000000, seeds)

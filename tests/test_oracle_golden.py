@@ -148,3 +148,67 @@ def test_fastexp_branches(L):
             assert v == pytest.approx(np.exp(x), rel=2e-6)
         else:
             assert v == np.exp(x)
+
+
+# ---- the reference's recombination-opportunity defect --------------------------------------------------
+def test_unmodified_reference_spawn_reads_uninitialised_field():
+    """ForestState's copy constructor (particle.cpp:113-136) never writes max_epoch_to_record_ (particle.hpp:254); the copy
+    that spawn() makes (particle.cpp:843) runs resample_recombination_position (:393-436, guard `epoch <=
+    max_epoch_to_record_` at :402) before extend_ARGs assigns the field (particleContainer.cpp:123).  The probe
+    (oracle/ref_harness.cpp::ref_spawn_probe) constructs the copy in a heap block pre-filled with a byte pattern and
+    reports what the reference's own code then records: the field is whatever the block held, and only epochs <= that
+    garbage get their opportunity record extended over the copy's first stretch."""
+    import json
+    g = json.load(open(os.path.join(G, "spawn_probe.json")))
+    probes = g["probes"]
+    live = []
+    if _libs.ref() is not None and hasattr(_libs.ref(), "ref_spawn_probe"):
+        h = _libs.ref_open("smcsmc " + g["cmd"])
+        live = [dict(_libs.ref_spawn_probe(h, p["fill"]), fill=p["fill"]) for p in probes]
+    for ps in (probes, live):
+        for p in ps:
+            fill = p["fill"]
+            want = int.from_bytes(bytes([fill] * 4), "little", signed=True)
+            assert p["field"] == want                                   # the constructor left the block's bytes in place
+            assert p["epochs_recorded"] >= 3 and p["expected"] > 0
+            if want < 0:
+                assert p["epochs_extended"] == 0 and p["recorded"] == 0.0
+            elif want == 0:
+                assert p["epochs_extended"] == 1                        # epoch 0 only
+                assert p["recorded"] < 0.5 * p["expected"]
+            else:
+                assert p["epochs_extended"] == p["epochs_recorded"]
+                assert p["recorded"] == pytest.approx(p["expected"], rel=1e-12)
+
+
+def test_unmodified_reference_recombination_opportunity_is_not_reproducible():
+    """end to end (tests/golden/em_reference.json, make_golden.py::golden_em): the unmodified binary run twice per seed,
+    the second time with 64 more bytes in an unrelated environment variable.  Trees, weights and event counts are
+    identical in both runs (every Coal row, the recombination COUNT, LogL), the recombination OPPORTUNITY is not, and it
+    sits 12-25 % below the corrected binary's (two added lines, tools/patch_reference_uninit.py), whose own value equals the
+    particle-weighted tree length integral."""
+    import json
+    d = json.load(open(os.path.join(G, "em_reference.json")))
+    a, b, fixed = d["unmodified_sweep"]["0"], d["unmodified_sweep"]["64"], d["runs"]["sweep"]
+    assert d["binary"] == "smcsmc_fixed"
+    differ = 0
+    for ra, rb, rf in zip(a, b, fixed):
+        for xa, xb, xf in zip(ra, rb, rf):
+            if xa["Type"] == "Recomb":
+                assert xa["Count"] == xb["Count"] == xf["Count"]
+                differ += xa["Opp"] != xb["Opp"]
+                for x in (xa, xb):
+                    assert 0.75 < float(x["Opp"]) / float(xf["Opp"]) < 0.88, (x["Opp"], xf["Opp"])
+            elif xa["Type"] in ("Coal", "LogL", "Resamp"):
+                assert (xa["Opp"], xa["Count"]) == (xb["Opp"], xb["Count"])
+                # the corrected binary draws the same trees (LogL, Resamp identical); its Coal rows of the epochs above 0
+                # come out a few 0.1 % higher -- un-extended shared records also change when chains are pruned
+                if xa["Type"] != "Coal":
+                    assert (xa["Opp"], xa["Count"]) == (xf["Opp"], xf["Count"])
+                else:
+                    assert float(xa["Opp"]) == pytest.approx(float(xf["Opp"]), rel=5e-3)
+                    assert float(xa["Count"]) == pytest.approx(float(xf["Count"]), rel=2e-2)
+    assert differ >= len(a) // 2     # same seed, same inputs, different answer
+    # the corrected binary is self-consistent: count / opportunity = the simulated rate (1e-8) within sampling error
+    rates = [float(x["Rate"]) for r in fixed for x in r if x["Type"] == "Recomb"]
+    assert np.mean(rates) == pytest.approx(1e-8, rel=0.03)
