@@ -12,8 +12,14 @@ resample), end-of-data flush.  With --gpus N every rank sweeps its own 100 Mb ch
 independent chunks, tallies summed; weak scaling), the tallies are all-reduced once per step over NCCL.
 
   value  particle*sites/s with the rows already resident in HBM (engine re-used, smc_reset between steps)
-  e2e    the same through the public C-ABI calls with HOST buffers: create + upload rows (H2D from pinned memory) +
-         sweep + finish + read tallies/lnZ (D2H), engine destroyed afterwards
+  e2e    the same through the public C-ABI calls with HOST buffers, everything the drop-in driver does per EM iteration:
+         lag calibration on the device (smc_calibrate_survival -- the reference's step pays its own calibration too,
+         smcsmc.cpp:287-288), max_epoch_to_update per row from those lags, create + upload rows (H2D from pinned
+         memory) + sweep + finish + read tallies/lnZ (D2H), engines destroyed afterwards
+
+Extra records on the same line (not the headline): `target_shape` (ONE population of 10^5 particles x 16 Mb, the
+north-star shape per GPU), `struct` (configs[2] at full size through the drop-in driver binary) at --gpus 1, and `shard`
+(ONE population of 10^6 particles x 4 Mb split over the ranks, strong scaling) at --gpus N > 1.
 """
 import argparse
 import json
@@ -129,18 +135,19 @@ def run_ours(a):
     h2d = sum(t.numel() * t.element_size() for d in pin for t in d.values())
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
 
-    def make_engines(seed):
+    def make_engines(seed, lags=ZIGZAG_LAGS, max_rec=None):
         pfs = []
         for c in range(C):
             if shard:
-                pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, chunk=c,
+                pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, lags, seed=seed, chunk=c,
                                       device=local, ess_fraction=a.ess,
                                       shard=(rank, world, broadcast_unique_id(device="cuda")))
             else:
-                pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed,
+                pf = S.ParticleFilter(NSAM, N, t_start, inv2N, MU, RHO, seqlen, lags, seed=seed,
                                       chunk=rank * C + c, device=local, ess_fraction=a.ess)
             d = pin[c]
-            pf.upload_rows(d["x_end"].numpy(), d["alleles"].numpy(), d["is_site"].numpy(), d["max_rec"].numpy())
+            pf.upload_rows(d["x_end"].numpy(), d["alleles"].numpy(), d["is_site"].numpy(),
+                           d["max_rec"].numpy() if max_rec is None else max_rec[c])
             pfs.append(pf)
         return pfs
 
@@ -207,9 +214,17 @@ def run_ours(a):
     dev_ms = ms1 - ms0
     launches = l1 - l0
     # ---- e2e leg: host buffers through the public calls, H2D + D2H inside the timed region ----
+    cal_events = []
+
     def step_e2e(seed):
         tr = [time.perf_counter()]
-        p = make_engines(seed)
+        # lag calibration as the drop-in driver does it (smcsmc_main.cpp: 8192 prior ARGs on the device, medians per
+        # epoch, lag = 2 x median) and the rows' max_epoch_to_update under those lags -- inside the timed region
+        med, cnt = S.calibrate_survival(NSAM, t_start, inv2N, RHO, seqlen, seed=1, n_args=8192, device=local)
+        lags = [2.0 * x for x in med]
+        cal_events.append(int(min(cnt)))
+        max_rec = [r.max_epoch_to_record(lags) for r in rows]
+        p = make_engines(seed, lags, max_rec)
         tr.append(time.perf_counter())
         sweep_all(p)
         tr.append(time.perf_counter())
@@ -219,7 +234,7 @@ def run_ours(a):
             pf.close()
         tr.append(time.perf_counter())
         if os.environ.get("BENCH_TRACE") and rank == 0:
-            print("[bench] e2e step: create+upload %.1f ms, sweep %.1f ms, read-back %.1f ms, destroy %.1f ms"
+            print("[bench] e2e step: calibrate+create+upload %.1f ms, sweep %.1f ms, read-back %.1f ms, destroy %.1f ms"
                   % tuple((tr[k + 1] - tr[k]) * 1e3 for k in range(4)), file=sys.stderr, flush=True)
         return out
     step_e2e(300)
@@ -263,9 +278,11 @@ def run_ours(a):
                                "configs[1]: 8 haplotypes x %g Mb zigzag, %d particles, 11 epochs, 1 EM iteration per step, "
                                "swept as %d concurrent chunks (smc2 -chunks)" % (a.len_mb, N, C), "chunks": C, "rows": R, "particles": N, "haplotypes": NSAM, "epochs": E,
                    "per_gpu": "the whole %g Mb data set per GPU" % a.len_mb, "l2": "flushed between steps (256 MiB write)",
-                   "lags": "reference-calibrated (DESIGN.md)"},
+                   "lags": "value: reference-calibrated (DESIGN.md); e2e: calibrated on the device every step"},
         "e2e": {"value": units / wall_e2e, "unit": "particle*sites/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": C * (6 * E * 8 + 8), "ms_per_step": wall_e2e / a.steps * 1e3},
+                "d2h_bytes_per_step": C * (6 * E * 8 + 8) + 2 * E * 8, "ms_per_step": wall_e2e / a.steps * 1e3,
+                "includes": "device lag calibration (8192 ARGs, fewest events in an epoch: %d), max_epoch_to_update, "
+                            "engine create/upload/sweep/finish/read-back/destroy" % (min(cal_events) if cal_events else -1)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "kernel": "smc_row_kernel", "avg_launch_us": avg_launch_s * 1e6,
@@ -277,12 +294,145 @@ def run_ours(a):
         "particle_rows_per_s": float(N) * R * a.steps * world / wall,
         "resample_fraction": rs_frac, "lnZ": lnZ,
     }
+    if not a.no_extras and not shard:
+        if world == 1:
+            line["target_shape"] = extra_target_shape(S, torch, local, a)
+            line["struct"] = extra_struct_driver(local)
+        else:
+            line["shard"] = extra_shard(S, torch, dist, rank, world, local, a)
     if rank == 0:
         if not a.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_reference_sample(a)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _timed(torch, fn):
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    out = fn()
+    ev1.record()
+    torch.cuda.synchronize()
+    return ev0.elapsed_time(ev1) * 1e-3, out
+
+
+def extra_target_shape(S, torch, local, a, particles=100000, len_mb=16.0):
+    """the north-star shape per GPU: ONE population of 10^5 particles (n = 8, 11 epochs) over 16 Mb in one chunk"""
+    rows, t_start, inv2N, seqlen = workload(len_mb, 1)
+    r = rows[0]
+    pf = S.ParticleFilter(NSAM, particles, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=7, device=local,
+                          ess_fraction=a.ess)
+    pf.upload_rows(r.x_end, r.alleles, r.is_site, r.max_epoch_to_record(ZIGZAG_LAGS))
+
+    def step(seed):
+        pf.reset(seed=seed)
+        pf.init_particles()
+        pf.sweep()
+        pf.finish()
+        return pf.ln_normalization_factor()
+    step(1)                                                    # warm-up
+    secs, lnz = _timed(torch, lambda: step(2))
+    c = pf.counters()
+    pf.close()
+    return {"workload": "8 haplotypes x %g Mb zigzag, ONE population of %d particles, 11 epochs, one chunk" % (len_mb, particles),
+            "value": particles * seqlen / secs, "unit": "particle*sites/s", "ms_per_step": secs * 1e3,
+            "rows": len(r.x_end), "us_per_row": secs / len(r.x_end) * 1e6, "resamples": c["resamples"], "lnZ": lnz}
+
+
+STRUCT_SEG = os.path.join(ROOT, "bench_data", "split_mig_n8_10Mb_seed3.seg.gz")
+DRIVER_BIN = os.path.join(ROOT, "smcsmc_b200", "bin", "smcsmc")
+
+
+def extra_struct_driver(local, particles=50000, length=10000000):
+    """BASELINE.json configs[2] at full size through the drop-in driver itself (reference command line, .seg parsed from
+    disk, device lag calibration, .out written): 4 + 4 haplotypes with split and directional migration, 50 000 particles
+    x 10 Mb, one sweep.  Wall time of the process; the device time of the sweep is what the driver logs."""
+    import gzip
+    import shutil
+    if not os.path.exists(DRIVER_BIN):
+        return {"unavailable": "smcsmc_b200/bin/smcsmc not built"}
+    with tempfile.TemporaryDirectory() as tmp:
+        seg = os.path.join(tmp, "c2.seg")
+        with gzip.open(STRUCT_SEG, "rb") as f, open(seg, "wb") as g:
+            shutil.copyfileobj(f, g)
+        theta, R = 4 * N0 * MU * length, 4 * N0 * RHO * length
+        cmd = [DRIVER_BIN, "-nsam", "8", "-Np", str(particles), "-N0", repr(N0), "-t", repr(theta), "-r", repr(R),
+               str(length), "-I", "2", "4", "4", "-em", "0", "2", "1", "1", "-eN", "0.1", "1", "-ej", "0.5", "2", "1",
+               "-EM", "0", "-seed", "1", "-seg", seg, "-o", os.path.join(tmp, "c2")]
+        env = dict(os.environ, SMCSMC_DEVICE=str(local))
+        t0 = time.perf_counter()
+        r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+        wall = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"unavailable": "driver exited with %d: %s" % (r.returncode, r.stderr[-300:])}
+        dev_ms = None
+        for ln in r.stderr.splitlines():
+            if "device time" in ln:
+                try:
+                    dev_ms = float(ln.split("device time")[1].split("ms")[0].strip(" :="))
+                except Exception:
+                    pass
+    out = {"workload": "configs[2]: 4+4 haplotypes, split at 0.5 and migration 2->1, %d particles x %g Mb, 3 epochs, one sweep "
+                       "through smcsmc_b200/bin/smcsmc" % (particles, length / 1e6),
+           "wall_s": wall, "value": particles * length / wall, "unit": "particle*sites/s (process wall: parse + calibrate + sweep + write)"}
+    if dev_ms:
+        out["sweep_device_ms"] = dev_ms
+        out["value_sweep"] = particles * length / (dev_ms * 1e-3)
+    return out
+
+
+def extra_shard(S, torch, dist, rank, world, local, a, particles=1000000, len_mb=4.0):
+    """ONE population of 10^6 particles (n = 8, 11 epochs) x 4 Mb split over the ranks (smc_shard_attach): strong scaling.
+    value = resident sweep (engine re-used), e2e = attach + upload + sweep + finish + read-back + destroy."""
+    from smcsmc_b200.sharding import broadcast_unique_id
+    rows, t_start, inv2N, seqlen = workload(len_mb, 1)
+    r = rows[0]
+    n_loc = particles // world
+    max_rec = r.max_epoch_to_record(ZIGZAG_LAGS)
+
+    def make(seed):
+        pf = S.ParticleFilter(NSAM, n_loc, t_start, inv2N, MU, RHO, seqlen, ZIGZAG_LAGS, seed=seed, device=local,
+                              ess_fraction=a.ess, shard=(rank, world, broadcast_unique_id(device="cuda")))
+        pf.upload_rows(r.x_end, r.alleles, r.is_site, max_rec)
+        return pf
+
+    def sweep(pf, seed=None):
+        if seed is not None:
+            pf.reset(seed=seed)
+        pf.init_particles()
+        pf.sweep()
+        pf.finish()
+        return pf.ln_normalization_factor()
+
+    def tmax(x):
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.cpu())
+    pf = make(11)
+    sweep(pf)                                                  # warm-up
+    dist.barrier()
+    secs, lnz = _timed(torch, lambda: sweep(pf, 12))
+    secs = tmax(secs)
+    c = pf.counters()
+    pf.close()
+    dist.barrier()
+
+    def e2e():
+        p = make(13)
+        z = sweep(p)
+        p.tallies()
+        p.close()
+        return z
+    secs_e2e, _ = _timed(torch, e2e)
+    secs_e2e = tmax(secs_e2e)
+    units = float(n_loc) * world * seqlen
+    return {"workload": "8 haplotypes x %g Mb zigzag, ONE population of %d particles sharded over %d GPUs, 11 epochs"
+                        % (len_mb, n_loc * world, world), "scaling": "strong", "value": units / secs,
+            "unit": "particle*sites/s", "ms_per_step": secs * 1e3, "rows": len(r.x_end),
+            "us_per_row": secs / len(r.x_end) * 1e6, "resamples": c["resamples"], "lnZ": lnz,
+            "e2e": {"value": units / secs_e2e, "ms_per_step": secs_e2e * 1e3}}
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -392,8 +542,10 @@ def main():
     ap.add_argument("--rows-per-turn", type=int, default=1)
     ap.add_argument("--ess", type=float, default=0.5, help="-ESS resampling threshold fraction (reference default 0.5)")
     ap.add_argument("--cpu-particles", type=int, default=1000)
-    ap.add_argument("--cpu-chunk-mb", type=float, default=2.0)
+    ap.add_argument("--cpu-chunk-mb", type=float, default=6.25,
+                    help="chunk length of the bounded CPU sample (6.25 Mb = configs[1]'s 100 Mb in 16 chunks)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the target_shape / struct / shard records")
     ap.add_argument("--shard", action="store_true",
                     help="with N > 1 ranks: split ONE population of --particles over the GPUs (smc_shard_attach) instead "
                          "of giving every GPU its own chunks; a single chunk of --len-mb is swept")

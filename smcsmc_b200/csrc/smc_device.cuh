@@ -280,14 +280,26 @@ __device__ inline int epoch_of(const ModelDev& m, double t) {
   return e;
 }
 
+// Slot s holds a changed height: move it to its place in the ascending order of the internal slots and rename the parent
+// pointers accordingly.  One rotation; the result is that of the chain of adjacent slot swaps it replaces (5 % of the
+// sweep: every swap was a pass over all parent pointers).
 template <class TV>
-__device__ inline void swap_slots(const ModelDev& m, const TV& T, int a, int b) {
-  double th = T.hw(a); T.hw(a) = T.hw(b); T.hw(b) = th;     // internal slots only
-  signed char tp = T.par(a); T.par(a) = T.par(b); T.par(b) = tp;
-  for (int v = 0; v < m.nn; v++) {
-    int p = T.par(v);
-    if (p == a) T.par(v) = (signed char)b;
-    else if (p == b) T.par(v) = (signed char)a;
+__device__ inline void resort_slot(const ModelDev& m, const TV& T, int s) {
+  const int n = m.n, nn = m.nn;
+  const double hs = T.hw(s);
+  int d = s;
+  while (d + 1 < nn && T.hw(d + 1) < hs) d++;
+  if (d == s) while (d - 1 >= n && T.hw(d - 1) > hs) d--;
+  if (d == s) return;
+  const signed char ps = T.par(s);
+  if (d > s) { for (int k = s; k < d; k++) { T.hw(k) = T.hw(k + 1); T.par(k) = T.par(k + 1); } }
+  else { for (int k = s; k > d; k--) { T.hw(k) = T.hw(k - 1); T.par(k) = T.par(k - 1); } }
+  T.hw(d) = hs; T.par(d) = ps;
+  const int lo = d > s ? s : d, hi = d > s ? d : s, shift = d > s ? -1 : 1;
+  for (int v = 0; v < nn; v++) {
+    const int p = T.par(v);
+    if (p == s) T.par(v) = (signed char)d;
+    else if (p >= lo && p <= hi) T.par(v) = (signed char)(p + shift);
   }
 }
 
@@ -395,9 +407,7 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
       T.hw(Pn) = tc;
     }
   }
-  int s = Pn;
-  while (s + 1 < nn && T.hw(s + 1) < T.hw(s)) { swap_slots(m, T, s, s + 1); s++; }
-  while (s - 1 >= n && T.hw(s - 1) > T.hw(s)) { swap_slots(m, T, s, s - 1); s--; }
+  resort_slot(m, T, Pn);
 }
 
 // particle.cpp:1195-1254 with multiplicity 1 and one rho segment; forest.h:140-151 for the re-draw after resampling
@@ -445,6 +455,111 @@ __device__ inline int extend_row(const ModelDev& m, const TV& T, Rng& r, double 
   }
   sink.row_end();
   if (is_site) logw += dlog(site_likelihood(m, T, data));
+  return nrec;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// extend_row with the SMC' moves compacted over the block.
+//
+// Recombinations per particle and row are Poisson (at the bench shape 35 % none, 37 % one, 28 % more): with one thread
+// walking its own particle through `while (updated_to < x1)` a warp runs as long as its unluckiest lane, and the move
+// code -- the bulk of the row -- executes with 8 of 32 lanes on average.  The trees sit in shared memory as
+// [node][column], so any thread of the block can run any resident particle's move.  Here every thread does its own first
+// stretch; then, round by round, the particles that still owe a move are listed (ballot + prefix over the warps) and
+// threads 0..count-1 take one each: full warps run the move and the stretch after it, the other warps wait at the
+// barrier without issuing.  Per particle the draws, the operations and their order are those of extend_row (the oracle
+// stays the checker draw for draw); what a particle carries from round to round lives in shared memory (MoveSmem).
+// ------------------------------------------------------------------------------------------------------------------
+struct MoveSmem {
+  double* X;              // [BS] position of the particle's next recombination (>= x1: no move owed)
+  double* LOGW;           // [BS]
+  double* TL;             // [BS] tree length of the current tree
+  double* SPARE;          // [BS] second uniform of the last Philox call
+  uint32_t* CTR;          // [BS] Philox call counter of the (particle, row) stream
+  unsigned char* HAVE;    // [BS] spare is valid
+  unsigned char* LIST;    // [2][BS] columns that owe a move, by round parity
+};
+__host__ __device__ inline size_t move_bytes_per_thread() { return 4 * 8 + 4 + 1 + 2 + 1; }   // 40
+template <int BS>
+__device__ __forceinline__ MoveSmem make_move_smem(unsigned char* base) {
+  MoveSmem ms;
+  double* d = reinterpret_cast<double*>(base);
+  ms.X = d; ms.LOGW = d + BS; ms.TL = d + 2 * BS; ms.SPARE = d + 3 * BS;
+  ms.CTR = reinterpret_cast<uint32_t*>(d + 4 * BS);
+  ms.HAVE = reinterpret_cast<unsigned char*>(ms.CTR + BS);
+  ms.LIST = ms.HAVE + BS;
+  return ms;
+}
+
+template <int BS, class TV, class Sink>
+__device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, double x0, double x1,
+                                       const signed char* data, int is_site, int max_rec_epoch, Sink& sink, double& logw,
+                                       double& next_base, bool live, const MoveSmem& ms, int* wcnt /* shared [2][BS/32] */) {
+  const int n = m.n, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  constexpr int nwarp = BS >> 5;
+  int nmiss = 0;
+  for (int i = 0; i < n; i++) nmiss += data[i] == -1;
+  const int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);   // particleContainer.cpp:103-111
+  int nrec = 0;
+  bool pending = false;
+  if (live) {
+    sink.row_begin(x1);
+    const double tl = tree_length(m, T);
+    const double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
+    const double new_to = x1 < next_base ? x1 : next_base;
+    if (x0 < x1) {
+      logw += dlog(fastexp(-m.mu * L_obs * (new_to - x0)));     // particle.cpp:770
+      record_recomb_opportunity(m, T, sink, x0, new_to, max_rec_epoch);
+    }
+    pending = new_to < x1;
+    ms.X[t] = next_base; ms.LOGW[t] = logw; ms.TL[t] = tl;
+    ms.CTR[t] = r.c0; ms.SPARE[t] = r.spare; ms.HAVE[t] = (unsigned char)r.have;
+  }
+  unsigned bal = __ballot_sync(0xffffffffu, pending);
+  if (lane == 0) wcnt[warp] = __popc(bal);
+  __syncthreads();
+  int total = 0, off = 0;
+  for (int w = 0; w < nwarp; w++) { const int c = wcnt[w]; if (w < warp) off += c; total += c; }
+  if (pending) ms.LIST[off + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)t;
+  int cur = 0;
+  while (total > 0) {                  // uniform over the block
+    __syncthreads();                   // the list of this round is complete
+    bool again = false;
+    int tp = 0;
+    if (t < total) {
+      tp = ms.LIST[cur * BS + t];
+      TV Tp = T; Tp.t = tp;
+      Sink sp = sink; sp.t = tp; sp.i = sink.i - t + tp;
+      Rng rp = r;
+      rp.c1 = r.c1 - (uint32_t)t + (uint32_t)tp; rp.c0 = ms.CTR[tp]; rp.spare = ms.SPARE[tp]; rp.have = ms.HAVE[tp];
+      double lw = ms.LOGW[tp];
+      const double x = ms.X[tp];
+      smc_move(m, Tp, rp, x, max_rec_epoch, sp, lw, ms.TL[tp]);
+      nrec++;
+      const double tl = tree_length(m, Tp);
+      const double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, Tp, data);
+      const double nb = draw_next_base(m, tl, rp, x);
+      const double new_to = x1 < nb ? x1 : nb;
+      lw += dlog(fastexp(-m.mu * L_obs * (new_to - x)));
+      record_recomb_opportunity(m, Tp, sp, x, new_to, max_rec_epoch);
+      again = new_to < x1;
+      ms.X[tp] = nb; ms.LOGW[tp] = lw; ms.TL[tp] = tl;
+      ms.CTR[tp] = rp.c0; ms.SPARE[tp] = rp.spare; ms.HAVE[tp] = (unsigned char)rp.have;
+    }
+    bal = __ballot_sync(0xffffffffu, again);
+    if (lane == 0) wcnt[(cur ^ 1) * nwarp + warp] = __popc(bal);
+    __syncthreads();                   // counts of the next round are visible, every read of this round's list is done
+    total = 0; off = 0;
+    for (int w = 0; w < nwarp; w++) { const int c = wcnt[(cur ^ 1) * nwarp + w]; if (w < warp) off += c; total += c; }
+    if (again) ms.LIST[(cur ^ 1) * BS + off + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)tp;
+    cur ^= 1;
+  }
+  __syncthreads();                     // the last round's results are visible to their owners
+  if (live) {
+    logw = ms.LOGW[t]; next_base = ms.X[t];
+    sink.row_end();
+    if (is_site) logw += dlog(site_likelihood(m, T, data));
+  }
   return nrec;
 }
 

@@ -32,6 +32,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <tuple>
 #include <type_traits>
 #include <vector>
 #include "../../include/smcsmc_b200.h"
@@ -68,6 +69,7 @@ struct Ctrl {
   int err;
   int sflags;               // SFLAG_* raised by any particle (structured populations)
   long long n_resample, n_recomb;
+  long long gen;            // sweep generation of a sharded engine (smc_reset): tags the ranks' per-row mailbox flags
   int nseg;
   USeg seg[MAXSEG];
 };
@@ -129,8 +131,8 @@ struct Params {
   long long Ntot, base;
   long long peer_state[SMC_MAX_RANKS];   // byte offset: peer r's state slab - mine
   long long peer_tally[SMC_MAX_RANKS];   // byte offset: peer r's tally slab (open, map, frozen) - mine
-  double* summ;             // [3] this rank's (max, sum, sum of squares) after a row
-  double* allsumm;          // [world][3] gathered
+  double* mbox;             // [2][SMC_MAX_RANKS][8] per-row mailbox in the state slab, by row parity: peers store their
+                            // (max, sum, sum of squares, prefix total) and a flag here over NVLink
   double* rank_off[2];      // [world+1] normalised exclusive prefix of the rank totals, by row parity
   double* rank_fac[2];      // [world] exp(rank max - ln normaliser), by row parity
 };
@@ -211,7 +213,9 @@ struct RingSink {
   }
   __device__ void coal(int e, double x, int cnt, double opp) const {
     int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
-    // count and opportunity sit side by side (16-byte aligned): one read-modify-write instead of two dependent ones
+    // count and opportunity sit side by side (16-byte aligned): one read-modify-write instead of two dependent ones.
+    // (Reductions -- atomicAdd without a return value -- were tried for these records and for the split path of rec_opp:
+    // 9 % slower here and 1.9 x slower there, the loop around an atomic no longer reconverges; profiles/r2_kernel_notes.md)
     double2* c2 = reinterpret_cast<double2*>(cell(e, k, 0));
     double2 v = *c2;
     v.x += cnt ? 1.0 : 0.0;
@@ -402,6 +406,31 @@ __device__ void commit_row(const Params& P, Ctrl* c, long long row, double new_l
   c->row = row + 1;
 }
 
+// second half of a sharded row, once the ranks' summaries are in: every rank derives the same ln normaliser, ESS, rank
+// offsets and resampling decision from the same numbers in the same order
+__device__ void shard_commit(const Params& P, Ctrl* c, long long row, const double* all) {
+  const int pnow = (int)(row & 1), G = P.world;
+  double gm = -DBL_MAX;
+  for (int r = 0; r < G; r++) gm = fmax(gm, all[r * 4]);
+  double S = 0.0, Q = 0.0;
+  for (int r = 0; r < G; r++) {
+    double f = exp(all[r * 4] - gm);
+    S += all[r * 4 + 1] * f;
+    Q += all[r * 4 + 2] * f * f;
+  }
+  const double new_lse = gm + log(S);
+  const double ess = S * S / Q;
+  double acc = 0.0;
+  for (int r = 0; r < G; r++) {
+    double fac = exp(all[r * 4] - new_lse);
+    P.rank_fac[pnow][r] = fac;
+    P.rank_off[pnow][r] = acc;
+    acc += all[r * 4 + 3] * fac;
+  }
+  P.rank_off[pnow][G] = acc;
+  commit_row(P, c, row, new_lse, ess, S > 0.0, acc, P.Ntot);
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // the row kernel
 // ---------------------------------------------------------------------------------------------------------------
@@ -460,8 +489,12 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   const int warp = t >> 5, lane = t & 31;
 
   // ---- phase 0: tallies due after the previous row, weighted with the previous row's normalised weights ----------
+  // A materialising getter AFTER the last row (mode 1, row == R) leaves what the last row owes to smc_finish, whose flush
+  // starts from the buckets consumed after rows 0..R-2; consuming them here as well would count them twice.  The pull
+  // below then has to carry the ancestor slots of those owed buckets too: it lists pending buckets as of row R-1.
+  const bool tail = mode == 1 && row >= P.R;
   int c0 = 0, c1 = 0;
-  if (row > 0 && c->cons_done != row) { c0 = P.cons_off[row - 1]; c1 = P.cons_off[row]; }
+  if (row > 0 && c->cons_done != row && !tail) { c0 = P.cons_off[row - 1]; c1 = P.cons_off[row]; }
   if (c1 > c0) {
     // at most one bucket per epoch falls due per row; the per-warp sums of all of them are staged in the (still
     // unused) tree area and handed to the global tallies with one pass
@@ -525,7 +558,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     const long long rowc = row < P.R ? row : P.R;
     const int* ks = P.kstart + rowc * E;
     const int* ksl = P.kslot + rowc * E;
-    const int* kf = P.kfirst + rowc * E;
+    const int* kf = P.kfirst + (tail && rowc > 0 ? rowc - 1 : rowc) * E;
     if (t == 0) {
       int acc = 0;
       for (int e = 0; e < E; e++) { pl_off[e] = acc; int cnt = ks[e] - kf[e]; acc += cnt > 0 ? cnt : 0; }
@@ -614,7 +647,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       const long long rowc = row < P.R ? row : P.R;
       const int* ks = P.kstart + rowc * E;
       const int* ksl = P.kslot + rowc * E;
-      const int* kf = P.kfirst + rowc * E;
+      const int* kf = P.kfirst + (tail && rowc > 0 ? rowc - 1 : rowc) * E;
       const unsigned long long closes = (mode == 0) ? P.closes[row] : 0ull;
       const double* __restrict__ osrc = at_peer(src.open, dR);
       const int* __restrict__ msrc = at_peer(src.map, dR);
@@ -724,9 +757,10 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   }
   __syncthreads();   // also: the slot list shares its storage with the accumulators phase 2 is about to zero
 
-  // ---- phase 2: the row ----------------------------------------------------------------------------------------
+  // ---- phase 2: the row (every thread takes part: the moves are compacted over the block) ------------------------
   int nrec = 0;
-  if (live && mode == 0) {
+  if (mode == 0) {
+    __shared__ int s_wcnt[2 * (BS >> 5)];
     const double x0 = row > 0 ? P.x_end[row - 1] : P.start_pos;
     const double x1 = P.x_end[row];
     signed char data[32];
@@ -734,7 +768,10 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
     RingSink<BS, ST> sink{&P, dst.open, (int)i, s_ks, s_ksl, s_kn, T.ACC, t, s_ubf, 0ull};
-    nrec = extend_row(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base);
+    const size_t tree_bytes = ST ? stree_bytes_per_thread(nn, E, P.sm.K) : tree_bytes_per_thread(nn, E);
+    const MoveSmem ms = make_move_smem<BS>(smem_raw + (((size_t)BS * tree_bytes + 15) & ~(size_t)15));
+    nrec = extend_row_block<BS>(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base, live, ms,
+                                s_wcnt);
   }
 
   // ---- phase 3: store, weight partials, last block finalises ----------------------------------------------------
@@ -852,10 +889,36 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   if (t == 0) P.boff[pnow][nb] = sh[BS];
   __syncthreads();
   if (t != 0) return;
-  if (sharded) {
-    // hand (max, sum, sum of squares, prefix total) to the exchange; smc_shard_commit_kernel finishes the row
-    P.summ[0] = gm; P.summ[1] = S; P.summ[2] = Q; P.summ[3] = sh[BS];
-    c->ticket = 0;
+  if constexpr (sharded) {
+    // The ranks exchange (max, sum, sum of squares, prefix total) inside this launch: every rank stores its four numbers
+    // and then a flag into slot [row parity][own rank] of EVERY rank's mailbox (peer stores over NVLink; the mailbox
+    // sits in the IPC-mapped state slab), waits until all slots of its own mailbox carry this row's flag, and finishes
+    // the row from the same numbers in the same order as everybody else.  One launch per row, graph-capturable like
+    // the unsharded sweep; it replaces launch -> ncclAllGather(4 doubles) -> 1-thread commit launch.  The fence before
+    // the flag is also what orders this rank's state, written by all its blocks before their tickets, against the
+    // pulls of its peers' next launch; two slots by row parity suffice because no rank can reach row
+    // k + 2 before every rank has consumed row k.
+    const int G = P.world, par = (int)(row & 1);
+    const long long flag = (c->gen << 40) | (row + 1);
+    const size_t mine = (size_t)(par * SMC_MAX_RANKS + P.rank) * 8;
+    for (int r = 0; r < G; r++) {
+      double* mb = at_peer(P.mbox, P.peer_state[r]) + mine;
+      mb[0] = gm; mb[1] = S; mb[2] = Q; mb[3] = sh[BS];
+    }
+    __threadfence_system();
+    for (int r = 0; r < G; r++)
+      *reinterpret_cast<volatile long long*>(at_peer(P.mbox, P.peer_state[r]) + mine + 4) = flag;
+    double all[SMC_MAX_RANKS * 4];
+    for (int r = 0; r < G; r++) {
+      const volatile long long* f = reinterpret_cast<const volatile long long*>(P.mbox + (size_t)(par * SMC_MAX_RANKS + r) * 8 + 4);
+      while (*f != flag) __nanosleep(64);
+    }
+    __threadfence_system();
+    for (int r = 0; r < G; r++) {
+      const volatile double* v = P.mbox + (size_t)(par * SMC_MAX_RANKS + r) * 8;
+      for (int k = 0; k < 4; k++) all[r * 4 + k] = v[k];
+    }
+    shard_commit(P, c, row, all);
     return;
   }
   double norm = sh[BS];
@@ -867,35 +930,6 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     norm = acc;
   }
   commit_row(P, c, row, new_lse, ess, S > 0.0, norm, (long long)P.N);
-}
-
-// second half of a sharded row, after the ranks' summaries were gathered: every rank derives the same ln normaliser,
-// ESS, rank offsets and resampling decision from the same numbers in the same order
-__global__ void smc_shard_commit_kernel(const __grid_constant__ Params P) {
-  Ctrl* c = P.ctrl;
-  const long long row = c->row;
-  if (row >= P.R) return;
-  const int pnow = (int)(row & 1), G = P.world;
-  const double* all = P.allsumm;
-  double gm = -DBL_MAX;
-  for (int r = 0; r < G; r++) gm = fmax(gm, all[r * 4]);
-  double S = 0.0, Q = 0.0;
-  for (int r = 0; r < G; r++) {
-    double f = exp(all[r * 4] - gm);
-    S += all[r * 4 + 1] * f;
-    Q += all[r * 4 + 2] * f * f;
-  }
-  const double new_lse = gm + log(S);
-  const double ess = S * S / Q;
-  double acc = 0.0;
-  for (int r = 0; r < G; r++) {
-    double fac = exp(all[r * 4] - new_lse);
-    P.rank_fac[pnow][r] = fac;
-    P.rank_off[pnow][r] = acc;
-    acc += all[r * 4 + 3] * fac;
-  }
-  P.rank_off[pnow][G] = acc;
-  commit_row(P, c, row, new_lse, ess, S > 0.0, acc, P.Ntot);
 }
 
 // commit of a materialise-only pass
@@ -1195,6 +1229,7 @@ struct smc_engine {
   std::vector<void*> allocs;
   std::vector<size_t> alloc_bytes;
   bool rows_ready = false, inited = false, finished = false;
+  long long gen = 0;                    // sweeps started on this engine (smc_reset); tags a sharded row's mailbox flags
   long long swept = 0;
   // GRAPH_ROWS consecutive row launches as one CUDA graph: the launches of a sweep are identical (the row index lives in
   // the device control block), so the graph is captured once and replayed; rebuilt when a parameter changed
@@ -1275,9 +1310,19 @@ struct BlockPool {
 };
 BlockPool g_pool;
 
+// every cudaMalloc'ed block gets a serial number: a peer's cached mapping of (pointer, serial) stays valid exactly as long
+// as that block lives, also when the allocator hands the same address out again later
+std::mutex g_serial_mu;
+std::map<void*, unsigned long long> g_block_serial;
+unsigned long long g_next_serial = 1;
+
 int raw_alloc(smc_engine* e, void** q, size_t bytes) {
   *q = g_pool.take(e->cfg.device, bytes);
-  if (!*q) CUDA_TRY(cudaMalloc(q, bytes));
+  if (!*q) {
+    CUDA_TRY(cudaMalloc(q, bytes));
+    std::lock_guard<std::mutex> g(g_serial_mu);
+    g_block_serial[*q] = g_next_serial++;
+  }
   e->allocs.push_back(*q);
   e->alloc_bytes.push_back(bytes);
   return 0;
@@ -1307,6 +1352,9 @@ int use_device(int device) {
 
 size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * smc::tree_bytes_per_thread(nn, E) + 16; }
 size_t stree_smem(int nn, int E, int K, int BS) { return (size_t)BS * smc::stree_bytes_per_thread(nn, E, K) + 16; }
+// the row kernel: the tree columns plus what a particle carries between the rounds of a row (MoveSmem)
+size_t row_smem(int nn, int E, int BS) { return tree_smem(nn, E, BS) + (size_t)BS * smc::move_bytes_per_thread() + 16; }
+size_t srow_smem(int nn, int E, int K, int BS) { return stree_smem(nn, E, K, BS) + (size_t)BS * smc::move_bytes_per_thread() + 16; }
 
 int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, int aa, const double* t_start,
                const double* inv2N, const double* vb, const uint8_t* mask) {
@@ -1326,25 +1374,57 @@ int fill_model(ModelDev& m, int n, int E, double mu, double rho, double seqlen, 
   return 0;
 }
 
-// All ranks publish the IPC handle of one slab and map everybody else's; delta[r] = peer r's address - mine.
+// All ranks publish one slab (address, allocation serial, IPC handle) and map everybody else's; delta[r] = peer r's
+// address - mine.  Mappings are cached per communicator and (peer, address, serial): the engines of one process come and
+// go (one per EM iteration in the drop-in driver), their slabs return to the block pool and come back with the same
+// address, and cudaIpcOpenMemHandle -- tens of milliseconds per peer -- is paid once per slab instead of once per engine.
+struct SlabNote { unsigned long long ptr, serial; cudaIpcMemHandle_t handle; };
+struct PeerMapKey {
+  ncclComm_t comm; int peer; unsigned long long ptr, serial;
+  bool operator<(const PeerMapKey& o) const {
+    return std::tie(comm, peer, ptr, serial) < std::tie(o.comm, o.peer, o.ptr, o.serial);
+  }
+};
+std::map<PeerMapKey, void*> g_peer_maps;
+std::map<void*, cudaIpcMemHandle_t> g_own_handles;
+
 int exchange_slab(smc_engine* e, void* slab, long long* delta) {
   const int G = e->P.world, me = e->P.rank;
-  cudaIpcMemHandle_t mine;
-  CUDA_TRY(cudaIpcGetMemHandle(&mine, slab));
+  SlabNote mine;
+  memset(&mine, 0, sizeof(mine));
+  mine.ptr = (unsigned long long)slab;
+  {
+    std::lock_guard<std::mutex> g(g_serial_mu);
+    mine.serial = g_block_serial[slab];
+    auto it = g_own_handles.find(slab);
+    if (it == g_own_handles.end() || mine.serial == 0) {
+      cudaIpcMemHandle_t h;
+      CUDA_TRY(cudaIpcGetMemHandle(&h, slab));
+      g_own_handles[slab] = h;
+      it = g_own_handles.find(slab);
+    }
+    mine.handle = it->second;
+  }
   char* d_in = nullptr; char* d_out = nullptr;
   int rc;
   if ((rc = dev_alloc(e, &d_in, sizeof(mine), false)) || (rc = dev_alloc(e, &d_out, sizeof(mine) * (size_t)G, false))) return rc;
   CUDA_TRY(cudaMemcpyAsync(d_in, &mine, sizeof(mine), cudaMemcpyHostToDevice, e->stream));
   NCCL_TRY(g_nccl.AllGather(d_in, d_out, sizeof(mine), ncclChar, e->comm, e->stream));
-  std::vector<cudaIpcMemHandle_t> all(G);
+  std::vector<SlabNote> all(G);
   CUDA_TRY(cudaMemcpyAsync(all.data(), d_out, sizeof(mine) * (size_t)G, cudaMemcpyDeviceToHost, e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
+  std::lock_guard<std::mutex> g(g_serial_mu);
   for (int r = 0; r < G; r++) {
     delta[r] = 0;
     if (r == me) continue;
+    const PeerMapKey key{e->comm, r, all[r].ptr, all[r].serial};
+    auto it = g_peer_maps.find(key);
     void* ptr = nullptr;
-    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, all[r], cudaIpcMemLazyEnablePeerAccess));
-    e->peer_maps.push_back(ptr);
+    if (it != g_peer_maps.end()) ptr = it->second;
+    else {
+      CUDA_TRY(cudaIpcOpenMemHandle(&ptr, all[r].handle, cudaIpcMemLazyEnablePeerAccess));
+      g_peer_maps[key] = ptr;
+    }
     delta[r] = (long long)((char*)ptr - (char*)slab);
   }
   return 0;
@@ -1459,7 +1539,7 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   e->BS = (cfg->N < 8192) ? 64 : 128;     // measured: 128 is 3-6 % faster from 10^4 particles on (profiles/r1_occupancy_probe.txt)
   if (const char* s = getenv("SMC_BLOCK")) { int b = atoi(s); if (b == 32 || b == 64 || b == 128) e->BS = b; }   // tuning knob
   P.nblocks = (cfg->N + e->BS - 1) / e->BS;
-  e->smem = tree_smem(P.m.nn, P.m.E, e->BS);
+  e->smem = row_smem(P.m.nn, P.m.E, e->BS);
   if (getenv("SMC_FLAT_SEARCH")) P.flat_search = 1;   // tests: the one-level parent search the two-level one must reproduce
   if (const char* s = getenv("SMC_EXTRA_SMEM")) e->smem += (size_t)atoi(s);                                       // occupancy experiments
   cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
@@ -1492,10 +1572,12 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
     const size_t s_h = up((size_t)(n - 1) * N * 8), s_p = up((size_t)nn * N), s_d = up(N * 8),
                  s_b1 = up(((size_t)P.nblocks + 1) * 8), s_b = up((size_t)P.nblocks * 8);
     const size_t per = s_h + s_p + s_d + s_d + s_b1 + s_b;
+    const size_t s_mbox = up(2 * (size_t)SMC_MAX_RANKS * 8 * sizeof(double));   // per-row mailbox of a sharded engine
     void* slab = nullptr;
-    if ((rc = raw_alloc(e, &slab, 2 * per))) { smc_destroy(e); return rc; }
-    cudaMemsetAsync(slab, 0, 2 * per, e->stream);
+    if ((rc = raw_alloc(e, &slab, 2 * per + s_mbox))) { smc_destroy(e); return rc; }
+    cudaMemsetAsync(slab, 0, 2 * per + s_mbox, e->stream);
     e->state_slab = slab;
+    P.mbox = (double*)((char*)slab + 2 * per);
     char* q = (char*)slab;
     for (int b = 0; b < 2; b++) {
       P.buf[b].height = (double*)q; q += s_h;
@@ -1535,11 +1617,18 @@ void smc_destroy(smc_engine* e) {
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   if (e->row_graph) cudaGraphExecDestroy(e->row_graph);
-  for (void* p : e->peer_maps) cudaIpcCloseMemHandle(p);
-  if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
-  const bool shared = e->comm != nullptr;        // peers hold IPC mappings of this engine's slabs: really free them
+  // The communicator and the peers' mappings of this engine's slabs belong to the process-wide caches (g_comms,
+  // g_peer_maps) and outlive the engine; its blocks -- slabs included -- go back to the pool.  A block the pool turns
+  // down is really freed: its serial number dies with it, so no peer will ever match its cached mapping again.
   for (size_t k = 0; k < e->allocs.size(); k++)
-    if (shared || !g_pool.give(e->cfg.device, e->alloc_bytes[k], e->allocs[k])) cudaFree(e->allocs[k]);
+    if (!g_pool.give(e->cfg.device, e->alloc_bytes[k], e->allocs[k])) {
+      {
+        std::lock_guard<std::mutex> g(g_serial_mu);
+        g_block_serial.erase(e->allocs[k]);
+        g_own_handles.erase(e->allocs[k]);
+      }
+      cudaFree(e->allocs[k]);
+    }
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -1569,15 +1658,31 @@ int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t i
   int rc = nccl_load();
   if (rc) return rc;
   CUDA_TRY(cudaSetDevice(e->cfg.device));
-  ncclUniqueId u;
-  memcpy(&u, id, 128);
-  NCCL_TRY(g_nccl.CommInitRank(&e->comm, world, u, rank));
+  {
+    // one communicator per (id, rank, world, device) and process: engines attached with the same id share it
+    static std::mutex mu;
+    static std::map<std::string, ncclComm_t> comms;
+    std::lock_guard<std::mutex> g(mu);
+    std::string key((const char*)id, 128);
+    key += "/" + std::to_string(rank) + "/" + std::to_string(world) + "/" + std::to_string(e->cfg.device);
+    auto it = comms.find(key);
+    if (it == comms.end()) {
+      ncclUniqueId u;
+      memcpy(&u, id, 128);
+      ncclComm_t comm = nullptr;
+      NCCL_TRY(g_nccl.CommInitRank(&comm, world, u, rank));
+      it = comms.emplace(key, comm).first;
+    }
+    e->comm = it->second;
+  }
   Params& P = e->P;
   P.rank = rank; P.world = world;
   P.Ntot = (long long)e->cfg.N * world;
   P.base = (long long)e->cfg.N * rank;
   P.slot_offset = e->cfg.slot_offset + (uint32_t)P.base;      // Philox streams are keyed by the global particle slot
-  if ((rc = dev_alloc(e, &P.summ, 4)) || (rc = dev_alloc(e, &P.allsumm, 4 * (size_t)world))) return rc;
+  // a slab from the pool may carry an earlier engine's flags: clear the mailbox before any peer can reach it (the slab
+  // exchange below is a collective, so no peer maps this slab before the memset is queued)
+  CUDA_TRY(cudaMemsetAsync(P.mbox, 0, 2 * (size_t)SMC_MAX_RANKS * 8 * sizeof(double), e->stream));
   for (int b = 0; b < 2; b++)
     if ((rc = dev_alloc(e, &P.rank_off[b], world + 1)) || (rc = dev_alloc(e, &P.rank_fac[b], world))) return rc;
   return exchange_slab(e, e->state_slab, P.peer_state);
@@ -1627,7 +1732,7 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
     const int K = max_marks > 0 ? max_marks : 2 * n + 8;
     if (K > 120) return fail(SMC_ERR_ARG, "max_marks must be at most 120");
     const int Q = 2 + 3 * Pp + Pp * Pp;
-    size_t smem = stree_smem(nn, E, K, e->BS);
+    size_t smem = srow_smem(nn, E, K, e->BS);
     smem = std::max(smem, (size_t)E * 2 * Q * (e->BS / 32) * sizeof(double) + 16);   // hand-over staging of phase 0
     if (smem > 230400 || stree_smem(nn, E, K, AUX_BS) > 230400)
       return fail(SMC_ERR_ARG, "n, E and max_marks need more shared memory than one SM has (fewer particles per block: SMC_BLOCK=32)");
@@ -1878,18 +1983,10 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
   if (row_end < row_begin || row_end > e->P.R) return fail(SMC_ERR_ARG, "row range out of bounds");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   cudaEventRecord(e->ev0, e->stream);
-  if (e->P.world == 1) {
+  {
+    // sharded engines take the same path: the ranks' per-row exchange happens inside the row kernel (peer mailbox)
     int rc = launch_rows(e, row_end - row_begin);
     if (rc) return rc;
-  } else {
-    // sharded: row kernel (rank-local partials) -> exchange of the ranks' summaries -> commit (identical on all ranks).
-    // The exchange is also what orders a rank's writes against its peers' pulls.
-    for (int64_t r = row_begin; r < row_end; r++) {
-      launch_row(e, 0);
-      NCCL_TRY(g_nccl.AllGather(e->P.summ, e->P.allsumm, 4, ncclDouble, e->comm, e->stream));
-      smc_shard_commit_kernel<<<1, 1, 0, e->stream>>>(e->P);
-      e->launches += 2;
-    }
   }
   cudaEventRecord(e->ev1, e->stream);
   CUDA_TRY(cudaGetLastError());
@@ -1979,6 +2076,7 @@ int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_l
   Ctrl init;
   memset(&init, 0, sizeof(init));
   init.cons_done = -1;
+  init.gen = ++e->gen;          // every rank of a sharded population resets the same number of times
   CUDA_TRY(cudaMemcpyAsync(P.ctrl, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   e->swept = 0; e->inited = false; e->finished = false;

@@ -142,6 +142,23 @@ void parse(int argc, char** argv, Params& P) {
       if (P.start_position < 1) throw std::invalid_argument("Out of range: -startpos " + a.cur());
     }
     else if (f == "-lag") { P.lag = a.next_double(f); P.calibrate_lag = false; }
+    else if (f == "-lags") {
+      // (B200 engine) one lag per epoch, comma separated, bp: what the reference prints as "Lags set to:"
+      std::string list = a.next(f), item;
+      P.lags.clear();
+      for (size_t q = 0; q <= list.size(); q++) {
+        if (q == list.size() || list[q] == ',') {
+          if (!item.empty()) {
+            char* end = nullptr;
+            const double v = strtod(item.c_str(), &end);
+            if (*end != 0 || !(v > 0)) throw std::invalid_argument("Out of range: -lags " + list);
+            P.lags.push_back(v);
+          }
+          item.clear();
+        } else item += list[q];
+      }
+      P.calibrate_lag = false;
+    }
     else if (f == "-calibrate_lag") {
       P.calibrate_lag = true; P.lag_fraction = a.next_double(f);
       if (P.lag_fraction < 0.0) throw std::invalid_argument("Out of range: -calibrate_lag " + a.cur());

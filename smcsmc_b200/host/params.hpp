@@ -37,6 +37,7 @@ struct Params {
   double lag = 0.0;
   bool calibrate_lag = true;
   double lag_fraction = 2.0;
+  std::vector<double> lags;                 // -lags: explicit lag per epoch (B200 engine extension)
   bool ancestral_aware = false;
   bool dephase = false;           // -dephase: heterozygous genotypes are summed over both phasings
   double Ne_cap = 200000;

@@ -4,6 +4,7 @@
 // .seg input, <prefix>.out / .log / .recomb.gz / .resample outputs in the reference's formats, in-binary EM
 // (CountModel::reset_model_parameters, count.cpp:44-63,267-325), exceptions -> "Error: ..." + exit 1.  Everything
 // between "read the rows" and "write the tallies" is the CUDA engine behind include/smcsmc_b200.h.
+#include <algorithm>
 #include <zlib.h>
 #include <chrono>
 #include <cmath>
@@ -130,6 +131,7 @@ void print_help(const Params& P) {
   cout << endl << "Inference tuning:" << endl;
   opt("-calibrate_lag", "FLT", "Lag before extracting events (multiple of survival time) [ 2 ]");
   opt("-lag", "FLT", "Constant lag (bp) instead of calibration");
+  opt("-lags", "F,F,..", "(B200 engine) one lag (bp) per epoch instead of calibration");
   opt("-tmax", "FLT", "Maximum tree height, in unit of 4N0 [ 2 ]");
   opt("-p", "STR", "Pattern of time segments, e.g. 1*3+15*4+1");
   opt("-ESS", "FLT", "Fractional ESS threshold for resampling [ 0.5 ]");
@@ -208,16 +210,31 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
       lags[e] = P.lag > 0 ? P.lag : 4.0 / (P.recombination_rate * top_t);
     }
   }
+  if (!P.lags.empty()) {
+    if ((int)P.lags.size() != E) throw invalid_argument("-lags needs one value per epoch (" + to_string(E) + ")");
+    lags = P.lags;
+  }
   if (P.calibrate_lag) {
     vector<double> surv(E);
     vector<int64_t> cnt(E);
-    if (np > 1)
-      check(smc_calibrate_survival_struct(device, n, E, t_start.data(), np, M.inv2N.data(), M.mig.data(),
-                                          M.single_mig.data(), M.leaf_pop.data(), P.recombination_rate, chunk_len, 1,
-                                          8192, surv.data(), cnt.data()));
-    else
-      check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N0.data(), P.recombination_rate, chunk_len, 1,
-                                   8192, surv.data(), cnt.data()));
+    // The reference keeps simulating until every epoch holds 200 survival events (up to 10^6 trees, smcsmc.cpp:169-236);
+    // here the batch of ARGs is quadrupled until that holds (rarely visited epochs: fine -p patterns, two samples)
+    for (int64_t n_args = 8192;; n_args *= 4) {
+      if (np > 1)
+        check(smc_calibrate_survival_struct(device, n, E, t_start.data(), np, M.inv2N.data(), M.mig.data(),
+                                            M.single_mig.data(), M.leaf_pop.data(), P.recombination_rate, chunk_len, 1,
+                                            n_args, surv.data(), cnt.data()));
+      else
+        check(smc_calibrate_survival(device, n, E, t_start.data(), inv2N0.data(), P.recombination_rate, chunk_len, 1,
+                                     n_args, surv.data(), cnt.data()));
+      const int64_t fewest = *min_element(cnt.begin(), cnt.end());
+      if (fewest >= 200 || n_args >= 524288) {
+        if (fewest < 22)
+          clog << " Warning: an epoch saw " << fewest << " survival events in " << n_args
+               << " simulated ARGs; its lag is taken from a neighbouring epoch" << endl;
+        break;
+      }
+    }
     for (int e = 0; e < E; e++) {
       clog << " Epoch " << e << " (" << cnt[e] << " events): survival distance " << surv[e] << endl;
       lags[e] = surv[e] * P.lag_fraction;
@@ -232,6 +249,7 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
   // One engine per chunk.  The reference runs one process per chunk (smc2 -chunks, model.py:563-662) and adds the
   // .out files; here the chunks of one process are swept concurrently on the device (smc_sweep_many) and added up.
   const size_t C = chunks.size();
+  int marks_in_use = 0;                 // capacity of the migration-mark pool this sweep runs with
   vector<smc_engine*> eng(C, nullptr);
   struct Guard { vector<smc_engine*>& v; ~Guard() { for (smc_engine* e : v) smc_destroy(e); } } guard{eng};
   size_t Rtot = 0;
@@ -248,7 +266,9 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     smc_config c;
     memset(&c, 0, sizeof c);
     c.n = n; c.N = (int32_t)P.N; c.E = E; c.device = devices[k % devices.size()];   // chunks round-robin over the GPUs
-    c.seed = P.seed + (uint64_t)em * 0x9E3779B97F4A7C15ull;
+    // RNG sub-stream of the chunk: the low 24 bits of its start go into the Philox counter, the bits above into the key,
+    // so that no two windows of a locus share a stream (starts that differ by a multiple of 2^24 bp used to)
+    c.seed = P.seed + (uint64_t)em * 0x9E3779B97F4A7C15ull + (uint64_t)(((long long)chunk_start[k]) >> 24) * 0xD1B54A32D192ED03ull;
     c.chunk = (uint32_t)(((long long)chunk_start[k]) & 0xFFFFFF);
     c.mu = P.mutation_rate; c.rho = P.recombination_rate; c.seqlen = chunk_len; c.start_pos = 0.0;
     c.ess_fraction = P.ESS_fraction; c.ancestral_aware = P.ancestral_aware; c.parity_scan = 0;
@@ -267,6 +287,7 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
       }
       int marks = min(120, (n + 4 * (int)ceil(msum)) * P.marks_scale);
       if (const char* mb = getenv("SMCSMC_MARKS_BASE")) marks = min(120, atoi(mb) * P.marks_scale);   // tests: force the retry
+      marks_in_use = marks;
       if (const char* mm = getenv("SMCSMC_MAX_MARKS")) marks = atoi(mm);
       check(smc_set_populations(eng[k], np, M.inv2N.data(), M.mig.data(), M.single_mig.data(), M.leaf_pop.data(), marks));
       if (P.vb) {   // particle.cpp:262-272: exp_digamma(c) / c per coalescence resp. migration
@@ -312,7 +333,7 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     check(smc_get_tallies(eng[k], tk.data()));
     int rc = smc_get_lnZ(eng[k], &lz);
     if (rc == SMC_ERR_NUMERIC && string(smc_last_error()).find("migration marks") != string::npos &&
-        !getenv("SMCSMC_MAX_MARKS") && (n + 4) * P.marks_scale < 120)
+        !getenv("SMCSMC_MAX_MARKS") && marks_in_use < 120)      // a pool already at the engine's maximum cannot grow
       throw MarksOverflow();
     if (rc == SMC_ERR_NUMERIC) throw runtime_error(string(smc_last_error()).find("probabilit") != string::npos
                                                        ? string("Zero or negative probabilities") : string(smc_last_error()));
@@ -321,6 +342,19 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
     for (size_t q = 0; q < tk.size(); q++) t[q] += tk[q];
     lnZ += lz;
     for (int q = 0; q < 4; q++) counters[q] += ck[q];
+  }
+  {
+    double dev_ms = 0;
+    int64_t launches = 0;
+    for (size_t k = 0; k < C; k++) {
+      double ms = 0;
+      int64_t ln = 0;
+      check(smc_get_timing(eng[k], &ms, &ln));
+      dev_ms += ms; launches += ln;
+    }
+    clog << " Sweep: device time " << fixed << setprecision(1) << dev_ms << " ms, " << launches << " kernel launches"
+         << setprecision(6) << scientific << endl;
+    clog.unsetf(ios::floatfield);
   }
   if (P.record_resample_file)
     for (size_t k = 0; k < C; k++) {
@@ -504,7 +538,7 @@ int main(int argc, char* argv[]) {
         catch (const MarksOverflow&) {
           P.marks_scale *= 2;
           clog << " A particle ran out of migration-mark slots; repeating the sweep with room for "
-               << min(120, (int)(P.nsam + 4) * P.marks_scale) << "+ marks per particle" << endl;
+               << "twice the room (the engine holds at most 120 marks per particle)" << endl;
         }
       }
       clog << "End of EM step " << i << endl;

@@ -22,13 +22,10 @@ class SegRows:
     def max_epoch_to_record(self, lags):
         """max_epoch_to_update (smcsmc.cpp:266-275) per row."""
         lags = np.asarray(lags, dtype=np.float64)
-        out = np.zeros(len(self.x_end), dtype=np.int32)
-        for r, d in enumerate(self.dist_to_mutation):
-            e = 0
-            while e < len(lags) and d < 0.5 * lags[e]:
-                e += 1
-            out[r] = e - 1
-        return out
+        # number of leading epochs e with d < 0.5 * lag[e] (the reference's loop stops at the first that fails), minus one
+        ok = np.asarray(self.dist_to_mutation, dtype=np.float64)[:, None] < 0.5 * lags[None, :]
+        lead = np.where(ok.all(axis=1), len(lags), np.argmin(ok, axis=1))
+        return (lead - 1).astype(np.int32)
 
 
 _CODE = {".": -1, "/": 2, "0": 0, "1": 1}

@@ -36,16 +36,26 @@ def allreduce_tallies(tallies, lnZ, device=None):
     return out[:-1].reshape(np.shape(tallies)), float(out[-1])
 
 
-def broadcast_unique_id(device=None):
+_ID_CACHE = {}
+
+
+def broadcast_unique_id(device=None, fresh=False):
     """rank 0 draws the id of a sharded population (smc_shard_unique_id) and every rank of the default process group
-    receives it; returns the 128 bytes to pass as ParticleFilter(shard=(rank, world, id))"""
+    receives it; returns the 128 bytes to pass as ParticleFilter(shard=(rank, world, id)).  The id is drawn once per
+    process group and handed out again on later calls (every rank must call in step): engines attached with the same id
+    share one NCCL communicator and the peers' memory mappings inside libsmcgpu, so creating the next engine costs an
+    allocation instead of a communicator.  fresh=True draws a new one."""
     import torch
     import torch.distributed as dist
     from .engine import shard_unique_id
+    key = (dist.get_world_size(), dist.get_rank())
+    if not fresh and key in _ID_CACHE:
+        return _ID_CACHE[key]
     t = torch.zeros(128, dtype=torch.uint8)
     if dist.get_rank() == 0:
         t = torch.frombuffer(bytearray(shard_unique_id()), dtype=torch.uint8).clone()
     if device is not None:
         t = t.to(device)
     dist.broadcast(t, src=0)
-    return bytes(t.cpu().numpy().tobytes())
+    _ID_CACHE[key] = bytes(t.cpu().numpy().tobytes())
+    return _ID_CACHE[key]

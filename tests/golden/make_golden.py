@@ -529,6 +529,15 @@ def _golden_medium(name, base, gz, length, seeds):
             return parse_out(o + ".out")
         with ThreadPoolExecutor(8) as ex:
             out["runs"] = list(ex.map(run, seeds))
+        # the lags the reference calibrates for the first sweep (its calibration has its own fixed seed, so they depend
+        # on the model only): a 2-particle run, "Lags set to:" on stderr
+        o = os.path.join(tmp, "lagprobe")
+        cmd = base.format(seed=1, seg=seg, out=o).split()
+        cmd[cmd.index("-Np") + 1] = "2"
+        cmd[cmd.index("-EM") + 1] = "0"
+        r = subprocess.run([ref_binary()] + cmd, check=True, capture_output=True, text=True)
+        line = [ln for ln in r.stderr.splitlines() if "Lags set to:" in ln][0]
+        out["lags_iter0"] = [float(x) for x in line.split(":")[1].split()]
     json.dump(out, open(os.path.join(HERE, name), "w"))
 
 

@@ -35,6 +35,9 @@ CASES = {
                     [1 / (2e4 * s) for s in (1, .2, 1, .2, 1, .2, 1, .2, 1, .2, 1)],
                     [20000.0, 15000.0, 9000.0, 7000.0, 5000.0, 3000.0, 2000.0, 1500.0, 1000.0, 600.0, 300.0], 1e-7, 4e-8),
 }
+# the first case once more: the new engine finds its slabs in the block pool and the peers' mappings in the cache, the
+# communicator is the one of the first engine (same id), and it sweeps twice (smc_reset in between)
+CASES["n4_small_again"] = CASES["n4_small"]
 
 
 def main():
@@ -44,7 +47,7 @@ def main():
     report = {}
     ok = True
     for name, (n, Ntot, R, seqlen, t_start, inv2N, lags, mu, rho) in CASES.items():
-        x_end, al, is_site = rows(n, R, seqlen, seed=len(name))
+        x_end, al, is_site = rows(n, R, seqlen, seed=len(name.replace("_again", "")))
         uid = broadcast_unique_id(device="cuda")
         N = Ntot // world
         pf = S.ParticleFilter(n, N, t_start, inv2N, mu, rho, seqlen, lags, seed=77, chunk=5, device=local,
@@ -54,6 +57,12 @@ def main():
         pf.sweep(0, R // 2)
         pf.sweep(R // 2, R)
         pf.finish()
+        if name.endswith("_again"):
+            # a second sweep on the same engine (the next EM iteration): smc_reset starts a new mailbox generation
+            pf.reset(seed=78)
+            pf.init_particles()
+            pf.sweep()
+            pf.finish()
         parent, height, logw, nb = pf.particles()
         mine = dict(parent=parent, height=height, logw=logw, nb=nb, lnZ=pf.ln_normalization_factor(),
                     tallies=pf.tallies(), counters=pf.counters(), rs=pf.resample_log(), anc=pf.last_ancestry())
@@ -67,6 +76,11 @@ def main():
         one.init_particles()
         one.sweep()
         one.finish()
+        if name.endswith("_again"):
+            one.reset(seed=78)
+            one.init_particles()
+            one.sweep()
+            one.finish()
         p1, h1, w1, b1 = one.particles()
         res = {}
         try:

@@ -262,6 +262,41 @@ def test_mid_sweep_state_and_ancestry(S):
         pf.close()
 
 
+@pytest.mark.parametrize("name", ["const4", "epochs3_n4_missing", "zigzag11_n8"])
+def test_getter_between_last_row_and_finish(S, name):
+    """sweep(0, R); particles(); finish() -- the header does not forbid it.  The read-out after the last row must not
+    consume the buckets smc_finish's flush is about to consume (they were counted twice), and when it applies a
+    resampling decided at the last row the ancestor slots of those buckets must travel with the offspring."""
+    n, N, R, seqlen, t_start, inv2N, lags, kw = CASES[name]
+    mu, rho = (1e-7, 4e-8) if name == "zigzag11_n8" else (2.5e-8, 1e-8)
+    x_end, al, is_site = _rows(n, R, seqlen, seed=len(name), **kw)
+    out = {}
+    for getter in (False, True):
+        pf = S.ParticleFilter(n, N, t_start, inv2N, mu, rho, seqlen, lags, seed=2024, chunk=3, parity_scan=True)
+        pf.upload_rows(x_end, al, is_site)
+        pf.init_particles()
+        pf.sweep(0, R)
+        if getter:
+            parent, height, logw, nb = pf.particles()
+            assert np.exp(logw).sum() == pytest.approx(1.0, rel=1e-9)
+            pf.last_ancestry()
+        pf.finish()
+        pos, _ = pf.resample_log()
+        out[getter] = (pf.tallies().copy(), pf.ln_normalization_factor(), len(pos) > 0 and pos[-1] == x_end[-1])
+        pf.close()
+    plain, read = out[False], out[True]
+    assert read[1] == plain[1]
+    if not plain[2]:
+        # no resampling pending at the last row: the read-out only normalised the stored weights
+        for q in (0, 1, 3, 4):
+            np.testing.assert_allclose(read[0][q], plain[0][q], rtol=1e-10, atol=1e-13)
+    else:
+        # the read-out applied the pending resampling, so the flush weighted the remaining buckets with the offspring's
+        # equal weights (as the reference does, smcsmc.cpp:346-373) instead of the parents': equal in expectation
+        for q in (1, 4):
+            assert read[0][q].sum() == pytest.approx(plain[0][q].sum(), rel=0.05)
+
+
 def test_set_particles_fixed_tree_set(S):
     """pruning log-likelihoods and tallies over a FIXED tree set: rho so small that no recombination happens, so the
     weights are pure pruning/no-mutation factors and the tallies pure recombination opportunity of the given trees"""
