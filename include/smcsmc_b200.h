@@ -84,7 +84,8 @@ const char* smc_version(void);
  *   0 recombination count, 1 recombination opportunity, 2+3p coalescence count in p, 3+3p coalescence opportunity in p,
  *   4+3p migration opportunity in p, 2+3*npop + p*npop + q migration count p -> q
  * (CountModel::total_coal_count / total_coal_opportunity / total_mig_count / total_mig_opportunity, count.hpp).
- * Not yet combinable with smc_shard_attach.  cfg.vb_logfac is not used by the structured move: see smc_set_population_vb. */
+ * Combinable with smc_shard_attach in either order (both before smc_upload_rows; blocks of 64 or 128 particles).
+ * cfg.vb_logfac is not used by the structured move: see smc_set_population_vb. */
 int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const double* mig, const double* single_mig,
                         const int32_t* leaf_pop, int32_t max_marks);
 /* -vb with populations (particle.cpp:262-272): the log of exp_digamma(c) / c, c = Model::coalescent_event_count(pop) resp.
@@ -131,8 +132,11 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn);
  * local N.  Rank 0 obtains an id, every rank attaches with it after smc_create and before smc_upload_rows (all ranks
  * upload the same rows).  From then on smc_upload_rows, smc_init_particles, smc_sweep, smc_finish, smc_get_particles and
  * smc_reset are collective: every rank calls them with the same arguments.  Per row the ranks exchange four doubles
- * (NCCL all-gather); offspring whose parent lives on another rank read its state straight from that GPU's memory
- * (CUDA IPC mappings over NVLink).  Philox streams are keyed by the global particle slot, so the result does not
+ * INSIDE the row kernel (each rank stores them and a flag into every peer's mailbox over NVLink and waits for its own
+ * to fill: one launch per row, no host round trip, no NCCL call on the data path); offspring whose parent lives on
+ * another rank read its state straight from that GPU's memory (CUDA IPC mappings over NVLink).  The NCCL communicator
+ * -- used to exchange the IPC handles and for the one all-reduce of smc_finish -- and the peers' mappings are cached per
+ * process and id: engines attached with the same id share them, so an engine per EM iteration costs an allocation.  Philox streams are keyed by the global particle slot, so the result does not
  * depend on the number of ranks beyond the order of floating-point sums in the normaliser.  After smc_finish every
  * rank holds the global tallies, ln normaliser, resampling log and counters; smc_get_particles returns the local slice,
  * smc_get_last_ancestry global parent indices.  Needs libnccl.so.2 at run time (bound with dlopen). */

@@ -625,14 +625,15 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       for (int v = n; v < nn; v++) T.hw(v) = sh_[(size_t)(v - n) * P.N + a];
       for (int v = 0; v < nn; v++) T.par(v) = sp_[(size_t)v * P.N + a];
       if constexpr (ST) {
-        const signed char* __restrict__ spop = at_peer(src.pop, dS);
+        // populations and marks sit in the tally slab (smc_upload_rows): a peer's copy is reached through peer_tally
+        const signed char* __restrict__ spop = at_peer(src.pop, dR);
         for (int v = 0; v < nn; v++) T.pop(v) = spop[(size_t)v * P.N + a];
-        const int nm = at_peer(src.nmarks, dS)[a];
+        const int nm = at_peer(src.nmarks, dR)[a];
         T.nm() = (signed char)nm;
         T.FLAG[t] = 0;
-        const double* __restrict__ smt = at_peer(src.mtime, dS);
-        const signed char* __restrict__ smb = at_peer(src.mbranch, dS);
-        const signed char* __restrict__ smp = at_peer(src.mpop, dS);
+        const double* __restrict__ smt = at_peer(src.mtime, dR);
+        const signed char* __restrict__ smb = at_peer(src.mbranch, dR);
+        const signed char* __restrict__ smp = at_peer(src.mpop, dR);
         for (int k = 0; k < nm; k++) {
           T.mt(k) = smt[(size_t)k * P.N + a];
           T.mb(k) = smb[(size_t)k * P.N + a];
@@ -994,7 +995,9 @@ __global__ void __launch_bounds__(128) smc_flush_struct_kernel(const __grid_cons
       double f = 0.0;
       if (live)
         for (int k = first_pending[e]; k < nbk; k++)
-          f += k < nbk - 1 ? frozen_record<false>(P, src.map, e, k % P.B, i, Q)[a] : src.open[((size_t)e * P.N + i) * Q + a];
+          f += k < nbk - 1 ? (P.world > 1 ? frozen_record<true>(P, src.map, e, k % P.B, i, Q)[a]
+                                          : frozen_record<false>(P, src.map, e, k % P.B, i, Q)[a])
+                           : src.open[((size_t)e * P.N + i) * Q + a];
       const double v0 = warp_sum(w * f), v1 = warp_sum(w * w * f);
       if (lane == 0) { tal[0][warp] = v0; tal[1][warp] = v1; }
       __syncthreads();
@@ -1432,7 +1435,12 @@ int exchange_slab(smc_engine* e, void* slab, long long* delta) {
 
 int launch_row(smc_engine* e, int mode) {
   int nb = e->P.nblocks;
-  if (e->P.sm.P > 1) {
+  if (e->P.sm.P > 1 && e->P.world > 1) {
+    switch (e->BS) {
+      case 64: smc_row_kernel<64, true, true><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
+      default: smc_row_kernel<128, true, true><<<nb, 128, e->smem, e->stream>>>(e->P, mode); break;
+    }
+  } else if (e->P.sm.P > 1) {
     switch (e->BS) {
       case 32: smc_row_kernel<32, true, false><<<nb, 32, e->smem, e->stream>>>(e->P, mode); break;
       case 64: smc_row_kernel<64, true, false><<<nb, 64, e->smem, e->stream>>>(e->P, mode); break;
@@ -1562,6 +1570,8 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
   if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
   const size_t N = cfg->N;
@@ -1652,7 +1662,7 @@ int smc_shard_attach(smc_engine* e, int32_t rank, int32_t world, const uint8_t i
   if (world < 2 || world > SMC_MAX_RANKS || rank < 0 || rank >= world) return fail(SMC_ERR_ARG, "rank/world out of range (2..8 ranks)");
   if (e->rows_ready || e->inited) return fail(SMC_ERR_STATE, "attach the shard before uploading rows");
   if (e->P.world > 1) return fail(SMC_ERR_STATE, "engine is already sharded");
-  if (e->P.sm.P > 1) return fail(SMC_ERR_STATE, "structured populations cannot be combined with particle sharding yet");
+  if (e->P.sm.P > 1 && e->BS == 32) return fail(SMC_ERR_ARG, "a sharded structured engine needs blocks of 64 or 128 particles");
   if (e->cfg.parity_scan) return fail(SMC_ERR_ARG, "parity_scan is a single-rank mode");
   if ((long long)e->cfg.N * world > 0x7fffffffLL) return fail(SMC_ERR_ARG, "more than 2^31 particles in total");
   int rc = nccl_load();
@@ -1694,7 +1704,7 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
   if (!e || !inv2N || !leaf_pop) return fail(SMC_ERR_ARG, "null argument");
   if (npop < 2 || npop > SMC_MAX_POPULATIONS) return fail(SMC_ERR_ARG, "populations must be in 2..4");
   Params& P = e->P;
-  if (P.world > 1) return fail(SMC_ERR_STATE, "structured populations cannot be combined with particle sharding yet");
+  if (P.world > 1 && e->BS == 32) return fail(SMC_ERR_ARG, "a sharded structured engine needs blocks of 64 or 128 particles");
   const bool update = P.sm.P > 1;
   if (update && P.sm.P != npop) return fail(SMC_ERR_STATE, "the number of populations cannot change");
   if (!update && e->rows_ready) return fail(SMC_ERR_STATE, "set the populations before uploading rows");
@@ -1744,13 +1754,8 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
         (rc = dev_alloc(e, &d_tot, h_tot.size(), false)) || (rc = dev_alloc(e, &d_single, h_single.size(), false)) ||
         (rc = dev_alloc(e, &d_fixed, (size_t)E, false)) || (rc = dev_alloc(e, &d_leaf, (size_t)n, false)))
       return rc;
-    const size_t N = e->cfg.N;
-    for (int b = 0; b < 2; b++) {
-      if ((rc = dev_alloc(e, &P.buf[b].pop, (size_t)nn * N)) || (rc = dev_alloc(e, &P.buf[b].mtime, (size_t)K * N)) ||
-          (rc = dev_alloc(e, &P.buf[b].mbranch, (size_t)K * N)) || (rc = dev_alloc(e, &P.buf[b].mpop, (size_t)K * N)) ||
-          (rc = dev_alloc(e, &P.buf[b].nmarks, N)))
-        return rc;
-    }
+    // the per-particle populations and migration marks are laid out with the tallies (smc_upload_rows): one slab that
+    // the peers of a sharded population map
     if ((rc = dev_alloc(e, &P.tallies, 2 * (size_t)Q * E))) return rc;
     P.sm.K = K; P.sm.Q = Q;
     P.sm.inv2N = d_inv; P.sm.mig = d_mig; P.sm.migtot = d_tot; P.sm.single_mig = d_single; P.sm.fixed = d_fixed;
@@ -1942,14 +1947,27 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
     const size_t QQ = (size_t)e->Q;
     const size_t s_open = up((size_t)E * NN * QQ * sizeof(double)), s_map = up((size_t)E * B * NN * sizeof(int)),
                  s_frozen = up((size_t)E * B * NN * QQ * sizeof(double));
+    // structured populations: pop[nn][N], mark times / branches / populations [K][N], marks in use [N], twice
+    const bool st = P.sm.P > 1;
+    const size_t KK = st ? (size_t)P.sm.K : 0, nnn = (size_t)P.m.nn;
+    const size_t s_pop = st ? up(nnn * NN) : 0, s_mt = st ? up(KK * NN * sizeof(double)) : 0, s_mb = st ? up(KK * NN) : 0,
+                 s_nm = st ? up(NN) : 0;
     char* slab = nullptr;
-    if ((rc = dev_alloc(e, &slab, 2 * s_open + 2 * s_map + s_frozen))) return rc;
+    if ((rc = dev_alloc(e, &slab, 2 * s_open + 2 * s_map + s_frozen + 2 * (s_pop + s_mt + 2 * s_mb + s_nm)))) return rc;
     e->ring_slab = slab;
     e->open_bytes = s_open;
     char* q = slab;
     for (int b = 0; b < 2; b++) { P.buf[b].open = (double*)q; q += s_open; }
     for (int b = 0; b < 2; b++) { P.buf[b].map = (int*)q; q += s_map; }
-    P.frozen = (double*)q;
+    P.frozen = (double*)q; q += s_frozen;
+    if (st)
+      for (int b = 0; b < 2; b++) {
+        P.buf[b].mtime = (double*)q; q += s_mt;
+        P.buf[b].pop = (signed char*)q; q += s_pop;
+        P.buf[b].mbranch = (signed char*)q; q += s_mb;
+        P.buf[b].mpop = (signed char*)q; q += s_mb;
+        P.buf[b].nmarks = (signed char*)q; q += s_nm;
+      }
     if (P.world > 1 && (rc = exchange_slab(e, slab, P.peer_tally))) return rc;
   }
   P.rs_cap = R;

@@ -547,3 +547,18 @@ def golden_configs1_medium(seeds=range(1, 11)):
 
 def golden_configs2_medium(seeds=range(1, 11)):
     _golden_medium("configs2_medium_reference.json", C2_BASE, "bench_data/split_mig_n8_10Mb_seed3.seg.gz", 5000000, seeds)
+
+
+def golden_smc2_frontend():
+    """result.out of the reference's own frontend driving the reference binary (tests/smc2_helper.py; the same arguments
+    the GPU test passes with -smcsmcpath smcsmc_b200/bin/smcsmc)"""
+    import shutil
+    import subprocess
+    import tempfile
+    root = os.path.dirname(os.path.dirname(HERE))
+    seg = os.path.join(os.path.dirname(HERE), "data", "const_n4_2Mb_seed7.seg")
+    with tempfile.TemporaryDirectory() as tmp:
+        out = os.path.join(tmp, "run")
+        subprocess.run([sys.executable, os.path.join(root, "tests", "smc2_helper.py"), ref_binary(), out, seg], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        shutil.copy(os.path.join(out, "result.out"), os.path.join(HERE, "smc2_frontend_reference.out"))

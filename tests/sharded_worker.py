@@ -38,6 +38,18 @@ CASES = {
 # the first case once more: the new engine finds its slabs in the block pool and the peers' mappings in the cache, the
 # communicator is the one of the first engine (same id), and it sweeps twice (smc_reset in between)
 CASES["n4_small_again"] = CASES["n4_small"]
+# two populations of 4 haplotypes, migration 2 -> 1 backwards in time, joined in the last epoch (BASELINE configs[2] in
+# small): the populations and migration marks of a parent on another rank travel over NVLink as well
+CASES["struct_2pop"] = (8, 2048, 100, 100000.0, [0.0, 4000.0, 20000.0], [1 / 2e4] * 3, [9000.0, 3000.0, 1000.0], 5e-8, 2e-8)
+
+
+def struct_model(E=3, P=2):
+    inv = np.full((E, P), 1 / 2e4)
+    mig = np.zeros((E, P, P))
+    mig[:2, 1, 0] = 2.5e-5
+    single = np.zeros((E, P, P))
+    single[2, 1, 0] = 1.0
+    return dict(inv2N=inv, mig=mig, single_mig=single, leaf_pop=[0, 0, 0, 0, 1, 1, 1, 1], max_marks=24)
 
 
 def main():
@@ -50,8 +62,9 @@ def main():
         x_end, al, is_site = rows(n, R, seqlen, seed=len(name.replace("_again", "")))
         uid = broadcast_unique_id(device="cuda")
         N = Ntot // world
+        pops = struct_model() if name.startswith("struct") else None
         pf = S.ParticleFilter(n, N, t_start, inv2N, mu, rho, seqlen, lags, seed=77, chunk=5, device=local,
-                              shard=(rank, world, uid))
+                              shard=(rank, world, uid), populations=pops)
         pf.upload_rows(x_end, al, is_site)
         pf.init_particles()
         pf.sweep(0, R // 2)
@@ -71,7 +84,8 @@ def main():
         pf.close()
         if rank != 0:
             continue
-        one = S.ParticleFilter(n, Ntot, t_start, inv2N, mu, rho, seqlen, lags, seed=77, chunk=5, device=local)
+        one = S.ParticleFilter(n, Ntot, t_start, inv2N, mu, rho, seqlen, lags, seed=77, chunk=5, device=local,
+                               populations=pops)
         one.upload_rows(x_end, al, is_site)
         one.init_particles()
         one.sweep()
