@@ -156,6 +156,13 @@ int smc_finish(smc_engine* e);
 /* out[6*E]: coal_count, coal_opportunity, coal_weight, recomb_count, recomb_opportunity, recomb_weight per epoch,
  * WITHOUT CountModel's initial pseudo-counts (count.cpp:161-193).  *_weight is sum(w^2 * opportunity). */
 int smc_get_tallies(smc_engine* e, double* out);
+/* out[R]: per .seg row the posterior-mean recombination opportunity sum_i w_i * integral over the row of the local tree
+ * length of particle i (generations x bp), weighted with the particles' weights right after the row -- the
+ * opportunity column of the local recombination map (CountModel::record_local_recomb_events, count.cpp:559-592; the
+ * reference weights every stretch with the pooled weight of its descendants a lag later: same expectation per locus up to
+ * the difference between the filtering and the fixed-lag smoothing posterior).  The driver spreads it over 100-bp bins
+ * into <prefix>.recomb.gz (CountModel::dump_local_recomb_logs, count.cpp:616-654).  Rows not swept yet read 0. */
+int smc_get_row_opportunity(smc_engine* e, double* out);
 int smc_get_lnZ(smc_engine* e, double* lnZ);                       /* ParticleContainer::ln_normalization_factor */
 /* counters[0] rows swept, [1] resampling events, [2] recombinations sampled, [3] numeric-error flag */
 int smc_get_counters(smc_engine* e, int64_t counters[4]);
@@ -197,6 +204,15 @@ int smc_calibrate_survival_struct(int device, int32_t n, int32_t E, const double
                                   const double* inv2N, const double* mig, const double* single_mig,
                                   const int32_t* leaf_pop, double rho, double seqlen, uint64_t seed, int64_t n_args,
                                   double* median_survival, int64_t* n_events);
+/* Terminal branch length quantiles of prior trees (calculate_terminal_branch_length_quantiles, smcsmc.cpp:128-167; the
+ * reference computes them at the start of every pfARG_core for the auxiliary particle filter's look-ahead): n_trees
+ * prior trees on the device (the reference draws 10^6), per sample the height of its parent coalescence ignoring
+ * migrations, lengths[n][nq] = the sorted values at index (size_t)(quantiles[k] * n_trees), and the mean tree length.
+ * npop < 2: single population (inv2N[E]); else the tables of smc_set_populations. */
+int smc_terminal_branch_quantiles(int device, int32_t n, int32_t E, const double* t_start, int32_t npop,
+                                  const double* inv2N, const double* mig, const double* single_mig,
+                                  const int32_t* leaf_pop, uint64_t seed, int64_t n_trees, int32_t nq,
+                                  const double* quantiles, double* lengths, double* mean_total_length);
 /* fastexp (particle.cpp:30-40) evaluated on the device, for the 1e-12 no-mutation-factor parity test */
 int smc_fastexp(int device, const double* x, int64_t count, double* out);
 

@@ -30,6 +30,12 @@ typedef struct {
   const double* lags;     /* [E] */
 } orc_pf_config;
 
+/* Optional side output: out[R], per row sum_i w_i * (local tree length x bp covered in the row) with the weights right
+ * after the row -- the opportunity the reference spreads over its local recombination map (count.cpp:559-587), here under
+ * the filtering weights.  NULL switches it off.  Only meaningful with nothing masked (rec_mask 3, max_rec NULL). */
+static double* g_row_opp_out = 0;
+void orc_set_row_opportunity_buffer(double* out) { g_row_opp_out = out; }
+
 /* returns 0, or 1 on overflow of the event buffer / zero total weight.
  * data[R][n] alleles; rs_pos/rs_ess sized R (may be NULL); last_anc[N] ancestry of the last APPLIED resampling. */
 int orc_particle_filter(const orc_model* m, const orc_pf_config* c, int R, const double* row_end, const int* data,
@@ -55,9 +61,11 @@ int orc_particle_filter(const orc_model* m, const orc_pf_config* c, int R, const
     parts[i].logw = -log((double)N);
     if (last_anc) last_anc[i] = -1;
   }
+  double* area = (double*)calloc((size_t)N, sizeof(double));
   for (int row = 0; row < R; row++) {
     for (int i = 0; i < N; i++) {
       orc_events t = { rowbuf, 0, 16384, 0 };
+      area[i] = 0.0;
       orc_rng_init(&r, c->seed, c->slot_offset + (uint32_t)i, (uint32_t)row, c->chunk, PURPOSE_EXTEND);
       orc_extend_row(m, &parts[i], &r, row_end[row], data + (size_t)row * n, is_site[row], c->ancestral_aware,
                      max_rec ? max_rec[row] : E - 1, &t);
@@ -69,6 +77,7 @@ int orc_particle_filter(const orc_model* m, const orc_pf_config* c, int R, const
       for (int k = 0; k < t.count; k++) {
         evs[nev].row = row; evs[nev].slot = i; evs[nev].ev = t.ev[k]; nev++;
         if (t.ev[k].type == ORC_EV_REC) n_recomb++;
+        if (t.ev[k].type == ORC_EV_RECOPP) area[i] += t.ev[k].opp * (t.ev[k].x1 - t.ev[k].x0);
       }
     }
     for (int i = 0; i < N; i++) lw[i] = parts[i].logw;
@@ -76,6 +85,11 @@ int orc_particle_filter(const orc_model* m, const orc_pf_config* c, int R, const
     if (!isfinite(lse)) { rc = 1; goto done; }
     lnZ += lse;
     for (int i = 0; i < N; i++) { parts[i].logw = lw[i]; weights[(size_t)row * N + i] = exp(lw[i]); }
+    if (g_row_opp_out) {
+      double acc = 0.0;
+      for (int i = 0; i < N; i++) acc += weights[(size_t)row * N + i] * area[i];
+      g_row_opp_out[row] = acc;
+    }
     double ess = orc_ess_partial_sums(weights + (size_t)row * N, N, ps);
     anc[(size_t)row * N] = -1;
     if (ess < N * c->ess_fraction - 1e-6) {
@@ -109,6 +123,6 @@ done:
   *lnZ_out = lnZ;
   if (n_resample_out) *n_resample_out = n_resample;
   if (n_recomb_out) *n_recomb_out = n_recomb;
-  free(next); free(weights); free(anc); free(lw); free(ps); free(counts); free(evs);
+  free(next); free(weights); free(anc); free(lw); free(ps); free(counts); free(evs); free(area);
   return rc;
 }

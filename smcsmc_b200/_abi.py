@@ -55,6 +55,9 @@ SYMBOLS = {
     "smc_branch_lengths": (_I, [_I, ctypes.c_int32, _I64, _V, _V, _V, _V, _V]),
     "smc_systematic_offspring": (_I, [_I, _V, _I64, _D, _V]),
     "smc_resample_counts": (_I, [_I, _V, _I64, _D, ctypes.c_int32, c_dp, _V]),
+    "smc_get_row_opportunity": (_I, [_V, _V]),
+    "smc_terminal_branch_quantiles": (_I, [_I, ctypes.c_int32, ctypes.c_int32, _V, ctypes.c_int32, _V, _V, _V, _V,
+                                            ctypes.c_uint64, _I64, ctypes.c_int32, _V, _V, c_dp]),
     "smc_resample_counts_noalloc": (_I, [_I, _V, _I64, _D, ctypes.c_int32, _V, _V, _V]),
     "smc_normalize_log": (_I, [_I, _V, _I64, c_dp, c_dp]),
     "smc_fastexp": (_I, [_I, _V, _I64, _V]),

@@ -470,22 +470,31 @@ __device__ inline int extend_row(const ModelDev& m, const TV& T, Rng& r, double 
 // barrier without issuing.  Per particle the draws, the operations and their order are those of extend_row (the oracle
 // stays the checker draw for draw); what a particle carries from round to round lives in shared memory (MoveSmem).
 // ------------------------------------------------------------------------------------------------------------------
+#ifdef SMC_CLOCKS
+// build variant for profiles/: thread 0 of every block adds the cycles of its phases to g_clk (smc_debug_clocks)
+__device__ unsigned long long g_clk[16];
+#define SMC_CLK(slot, t0) do { if (threadIdx.x == 0) { long long now_ = clock64(); atomicAdd(&g_clk[slot], (unsigned long long)(now_ - (t0))); (t0) = now_; } } while (0)
+#else
+#define SMC_CLK(slot, t0) do { } while (0)
+#endif
+
 struct MoveSmem {
   double* X;              // [BS] position of the particle's next recombination (>= x1: no move owed)
   double* LOGW;           // [BS]
   double* TL;             // [BS] tree length of the current tree
   double* SPARE;          // [BS] second uniform of the last Philox call
+  double* AREA;           // [BS] tree length x bp summed over the row's stretches (the row's recombination opportunity)
   uint32_t* CTR;          // [BS] Philox call counter of the (particle, row) stream
   unsigned char* HAVE;    // [BS] spare is valid
   unsigned char* LIST;    // [2][BS] columns that owe a move, by round parity
 };
-__host__ __device__ inline size_t move_bytes_per_thread() { return 4 * 8 + 4 + 1 + 2 + 1; }   // 40
+__host__ __device__ inline size_t move_bytes_per_thread() { return 5 * 8 + 4 + 1 + 2 + 1; }   // 48
 template <int BS>
 __device__ __forceinline__ MoveSmem make_move_smem(unsigned char* base) {
   MoveSmem ms;
   double* d = reinterpret_cast<double*>(base);
-  ms.X = d; ms.LOGW = d + BS; ms.TL = d + 2 * BS; ms.SPARE = d + 3 * BS;
-  ms.CTR = reinterpret_cast<uint32_t*>(d + 4 * BS);
+  ms.X = d; ms.LOGW = d + BS; ms.TL = d + 2 * BS; ms.SPARE = d + 3 * BS; ms.AREA = d + 4 * BS;
+  ms.CTR = reinterpret_cast<uint32_t*>(d + 5 * BS);
   ms.HAVE = reinterpret_cast<unsigned char*>(ms.CTR + BS);
   ms.LIST = ms.HAVE + BS;
   return ms;
@@ -494,7 +503,8 @@ __device__ __forceinline__ MoveSmem make_move_smem(unsigned char* base) {
 template <int BS, class TV, class Sink>
 __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, double x0, double x1,
                                        const signed char* data, int is_site, int max_rec_epoch, Sink& sink, double& logw,
-                                       double& next_base, bool live, const MoveSmem& ms, int* wcnt /* shared [2][BS/32] */) {
+                                       double& next_base, bool live, const MoveSmem& ms, int* wcnt /* shared [2][BS/32] */,
+                                       double& row_area) {
   const int n = m.n, t = threadIdx.x, lane = t & 31, warp = t >> 5;
   constexpr int nwarp = BS >> 5;
   int nmiss = 0;
@@ -502,17 +512,22 @@ __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, d
   const int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);   // particleContainer.cpp:103-111
   int nrec = 0;
   bool pending = false;
+#ifdef SMC_CLOCKS
+  long long clk = clock64();
+#endif
   if (live) {
     sink.row_begin(x1);
     const double tl = tree_length(m, T);
     const double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
     const double new_to = x1 < next_base ? x1 : next_base;
+    double area = 0.0;
     if (x0 < x1) {
       logw += dlog(fastexp(-m.mu * L_obs * (new_to - x0)));     // particle.cpp:770
       record_recomb_opportunity(m, T, sink, x0, new_to, max_rec_epoch);
+      area = tl * (new_to - x0);
     }
     pending = new_to < x1;
-    ms.X[t] = next_base; ms.LOGW[t] = logw; ms.TL[t] = tl;
+    ms.X[t] = next_base; ms.LOGW[t] = logw; ms.TL[t] = tl; ms.AREA[t] = area;
     ms.CTR[t] = r.c0; ms.SPARE[t] = r.spare; ms.HAVE[t] = (unsigned char)r.have;
   }
   unsigned bal = __ballot_sync(0xffffffffu, pending);
@@ -522,8 +537,12 @@ __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, d
   for (int w = 0; w < nwarp; w++) { const int c = wcnt[w]; if (w < warp) off += c; total += c; }
   if (pending) ms.LIST[off + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)t;
   int cur = 0;
+  SMC_CLK(3, clk);                     // first stretch
   while (total > 0) {                  // uniform over the block
     __syncthreads();                   // the list of this round is complete
+#ifdef SMC_CLOCKS
+    if (threadIdx.x == 0) { atomicAdd(&g_clk[8], 1ull); atomicAdd(&g_clk[9], (unsigned long long)total); }
+#endif
     bool again = false;
     int tp = 0;
     if (t < total) {
@@ -543,7 +562,7 @@ __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, d
       lw += dlog(fastexp(-m.mu * L_obs * (new_to - x)));
       record_recomb_opportunity(m, Tp, sp, x, new_to, max_rec_epoch);
       again = new_to < x1;
-      ms.X[tp] = nb; ms.LOGW[tp] = lw; ms.TL[tp] = tl;
+      ms.X[tp] = nb; ms.LOGW[tp] = lw; ms.TL[tp] = tl; ms.AREA[tp] += tl * (new_to - x);
       ms.CTR[tp] = rp.c0; ms.SPARE[tp] = rp.spare; ms.HAVE[tp] = (unsigned char)rp.have;
     }
     bal = __ballot_sync(0xffffffffu, again);
@@ -553,13 +572,15 @@ __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, d
     for (int w = 0; w < nwarp; w++) { const int c = wcnt[(cur ^ 1) * nwarp + w]; if (w < warp) off += c; total += c; }
     if (again) ms.LIST[(cur ^ 1) * BS + off + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)tp;
     cur ^= 1;
+    SMC_CLK(4, clk);                   // move rounds
   }
   __syncthreads();                     // the last round's results are visible to their owners
   if (live) {
-    logw = ms.LOGW[t]; next_base = ms.X[t];
+    logw = ms.LOGW[t]; next_base = ms.X[t]; row_area = ms.AREA[t];
     sink.row_end();
     if (is_site) logw += dlog(site_likelihood(m, T, data));
   }
+  SMC_CLK(5, clk);                     // row-end flush + site likelihood (thread 0's own)
   return nrec;
 }
 

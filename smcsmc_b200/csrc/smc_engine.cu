@@ -118,6 +118,8 @@ struct Params {
   double* bmax[2];
   double* bsum[2];
   double* bsq[2];
+  double* barea[2];        // [nblocks] block sums of exp(logw - block max) * (tree length x bp of the row)
+  double* row_opp;         // [R] posterior-mean recombination opportunity of each row (sum_i w_i int_row L_i dx)
   double* boff[2];         // [nblocks+1] exclusive prefix of normalised block totals
   double* bscale[2];
   double* psum;            // [N+1] parity-mode sequential partial sums
@@ -470,12 +472,16 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   const int n = m.n, nn = m.nn, E = m.E;
   auto T = tree_view_of<BS>(P, smem_raw, t, std::integral_constant<bool, ST>());
   const int QC = ST ? P.sm.Q : 4;      // tally cells per epoch
-  __shared__ double red[3][4];
+  __shared__ double red[4][4];
   __shared__ bool is_last;
 
   Ctrl* c = P.ctrl;
   const long long row = c->row;
   if (mode == 0 && row >= P.R) return;
+#ifdef SMC_CLOCKS
+  long long clk = clock64();
+  if (threadIdx.x == 0) atomicAdd(&g_clk[10], 1ull);
+#endif
   const int cur = c->cur;
   const int resampled = c->resampled;
   const double lse = c->lse;
@@ -546,6 +552,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     __syncthreads();
   }
 
+  SMC_CLK(0, clk);
   // ---- phase 1: load own state, or pull the parent's after a resampling ---------------------------------------
   // After a resampling every particle copies its parent's ancestor slot of every pending closed bucket (~150 of them
   // at the bench shape).  The (epoch, ring slot) pairs are the same for all particles of the launch: they are listed
@@ -758,8 +765,10 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   }
   __syncthreads();   // also: the slot list shares its storage with the accumulators phase 2 is about to zero
 
+  SMC_CLK(1, clk);
   // ---- phase 2: the row (every thread takes part: the moves are compacted over the block) ------------------------
   int nrec = 0;
+  double row_area = 0.0;
   if (mode == 0) {
     __shared__ int s_wcnt[2 * (BS >> 5)];
     const double x0 = row > 0 ? P.x_end[row - 1] : P.start_pos;
@@ -772,9 +781,10 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     const size_t tree_bytes = ST ? stree_bytes_per_thread(nn, E, P.sm.K) : tree_bytes_per_thread(nn, E);
     const MoveSmem ms = make_move_smem<BS>(smem_raw + (((size_t)BS * tree_bytes + 15) & ~(size_t)15));
     nrec = extend_row_block<BS>(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base, live, ms,
-                                s_wcnt);
+                                s_wcnt, row_area);
   }
 
+  SMC_CLK(2, clk);      // phase 2 as a whole (slots 3-5 split it)
   // ---- phase 3: store, weight partials, last block finalises ----------------------------------------------------
   if (live) {
     dst.logw[i] = logw;
@@ -810,15 +820,17 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     if (lane >= o) incl += y;
   }
   double sq = warp_sum(ex * ex);
+  double ar = warp_sum(live ? ex * row_area : 0.0);
   __syncthreads();
   if (lane == 31) red[1][warp] = incl;
-  if (lane == 0) red[2][warp] = sq;
+  if (lane == 0) { red[2][warp] = sq; red[3][warp] = ar; }
   __syncthreads();
-  double woff = 0.0, btot = 0.0, bsq = 0.0;
+  double woff = 0.0, btot = 0.0, bsq = 0.0, barea = 0.0;
   for (int w = 0; w < nwarp; w++) {
     if (w < warp) woff += red[1][w];
     btot += red[1][w];
     bsq += red[2][w];
+    barea += red[3][w];
   }
   if (live) P.local_cum[pnow][i] = woff + incl;
   int nr = warp_sum((double)nrec) + 0.5;
@@ -827,9 +839,11 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     P.bmax[pnow][blockIdx.x] = mx;
     P.bsum[pnow][blockIdx.x] = btot;
     P.bsq[pnow][blockIdx.x] = bsq;
+    P.barea[pnow][blockIdx.x] = barea;
   }
   __threadfence();
   __syncthreads();
+  SMC_CLK(6, clk);      // store + partials
   if (t == 0) {
     unsigned int tk = atomicAdd(&c->ticket, 1u);
     is_last = (tk == gridDim.x - 1);
@@ -848,18 +862,19 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   __syncthreads();
   gm = red[0][0];
   for (int w = 1; w < nwarp; w++) gm = fmax(gm, red[0][w]);
-  double S = 0.0, Q = 0.0;
+  double S = 0.0, Q = 0.0, A = 0.0;
   for (int b = t; b < nb; b += BS) {
     double f = dexp(__ldcg(P.bmax[pnow] + b) - gm);
     S += __ldcg(P.bsum[pnow] + b) * f;
     Q += __ldcg(P.bsq[pnow] + b) * f * f;
+    A += __ldcg(P.barea[pnow] + b) * f;
   }
-  S = warp_sum(S); Q = warp_sum(Q);
+  S = warp_sum(S); Q = warp_sum(Q); A = warp_sum(A);
   __syncthreads();
-  if (lane == 0) { red[1][warp] = S; red[2][warp] = Q; }
+  if (lane == 0) { red[1][warp] = S; red[2][warp] = Q; red[3][warp] = A; }
   __syncthreads();
-  S = 0.0; Q = 0.0;
-  for (int w = 0; w < nwarp; w++) { S += red[1][w]; Q += red[2][w]; }
+  S = 0.0; Q = 0.0; A = 0.0;
+  for (int w = 0; w < nwarp; w++) { S += red[1][w]; Q += red[2][w]; A += red[3][w]; }
   constexpr bool sharded = SH;
   const double new_lse = gm + log(S);
   const double ess = S * S / Q;
@@ -904,7 +919,7 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     const size_t mine = (size_t)(par * SMC_MAX_RANKS + P.rank) * 8;
     for (int r = 0; r < G; r++) {
       double* mb = at_peer(P.mbox, P.peer_state[r]) + mine;
-      mb[0] = gm; mb[1] = S; mb[2] = Q; mb[3] = sh[BS];
+      mb[0] = gm; mb[1] = S; mb[2] = Q; mb[3] = sh[BS]; mb[5] = A;
     }
     __threadfence_system();
     for (int r = 0; r < G; r++)
@@ -919,9 +934,20 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       const volatile double* v = P.mbox + (size_t)(par * SMC_MAX_RANKS + r) * 8;
       for (int k = 0; k < 4; k++) all[r * 4 + k] = v[k];
     }
+    {   // the row's posterior-mean recombination opportunity over all ranks (weights relative to the global maximum)
+      double gmax = -DBL_MAX, sa = 0.0, ss = 0.0;
+      for (int r = 0; r < G; r++) gmax = fmax(gmax, all[r * 4]);
+      for (int r = 0; r < G; r++) {
+        const double f = exp(all[r * 4] - gmax);
+        ss += all[r * 4 + 1] * f;
+        sa += reinterpret_cast<const volatile double*>(P.mbox + (size_t)(par * SMC_MAX_RANKS + r) * 8)[5] * f;
+      }
+      P.row_opp[row] = sa / ss;
+    }
     shard_commit(P, c, row, all);
     return;
   }
+  P.row_opp[row] = A / S;
   double norm = sh[BS];
   if (P.parity_scan) {
     // order-faithful partial sums (particleContainer.cpp:256-262): left to right, one thread
@@ -1124,6 +1150,31 @@ __global__ void __launch_bounds__(128) k_survival(const __grid_constant__ ModelD
       if (!present) { dist[i * (n - 1) + j] = pos; T.l1(n + j) = 0.0; alive--; break; }
     }
   }
+  if constexpr (ST) { if (T.FLAG[t]) atomicOr(flags, (int)T.FLAG[t]); }
+}
+
+// Terminal branch lengths of prior trees (calculate_terminal_branch_length_quantiles, smcsmc.cpp:128-167): one thread draws
+// one prior tree and reports, per sample, the height of its parent coalescence (migrations are marks here, never nodes,
+// so parent_height_ignoring_migrations is the parent slot's height) and the tree length.  dist[(leaf * count) + i].
+template <bool ST>
+__global__ void __launch_bounds__(128) k_terminal(const __grid_constant__ ModelDev m, const __grid_constant__ SModelDev sm,
+                                                  long long count, uint64_t seed, double* dist, double* tlen, int* flags) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int BS = AUX_BS;
+  const int t = threadIdx.x;
+  const int n = m.n, nn = m.nn;
+  auto T = [&]() {
+    if constexpr (ST) return make_stree_view<BS>(smem_raw, m.n, nn, m.E, t, &sm);
+    else return make_tree_view<BS>(smem_raw, m.n, nn, m.E, t);
+  }();
+  const long long i = (long long)blockIdx.x * BS + t;
+  if (i >= count) return;
+  Rng r;
+  rng_init(r, seed, (uint32_t)i, 0, 0x7B1, RNG_INIT);
+  if constexpr (ST) T.FLAG[t] = 0;
+  init_tree(m, T, r);
+  for (int v = 0; v < n; v++) { const int p = T.par(v); dist[(size_t)v * count + i] = p >= 0 ? T.hw(p) : 0.0; }
+  tlen[i] = tree_length(m, T);
   if constexpr (ST) { if (T.FLAG[t]) atomicOr(flags, (int)T.FLAG[t]); }
 }
 
@@ -1460,6 +1511,9 @@ int launch_row(smc_engine* e, int mode) {
     }
   }
   e->launches++;
+  // a launch that cannot be queued (bad configuration, captured stream invalidated) is reported where it happens
+  const cudaError_t le = cudaPeekAtLastError();
+  if (le != cudaSuccess) return fail(SMC_ERR_CUDA, std::string("row kernel launch: ") + cudaGetErrorString(le));
   return 0;
 }
 
@@ -1472,13 +1526,16 @@ int launch_rows(smc_engine* e, int64_t count) {
   (void)tuned;
   if (!no_graph && count >= GRAPH_ROWS) {
     if (!e->row_graph || e->graph_dirty) {
-      if (e->row_graph) { cudaGraphExecDestroy(e->row_graph); e->row_graph = nullptr; }
+      if (e->row_graph) { CUDA_TRY(cudaGraphExecDestroy(e->row_graph)); e->row_graph = nullptr; }
       cudaGraph_t g = nullptr;
       const long long before = e->launches;
       CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-      for (int k = 0; k < GRAPH_ROWS; k++) launch_row(e, 0);
-      CUDA_TRY(cudaStreamEndCapture(e->stream, &g));
+      int lrc = 0;
+      for (int k = 0; k < GRAPH_ROWS && !lrc; k++) lrc = launch_row(e, 0);
+      const cudaError_t ce_end = cudaStreamEndCapture(e->stream, &g);      // always end the capture, also after a failure
       e->launches = before;
+      if (lrc) { if (g) cudaGraphDestroy(g); return lrc; }
+      if (ce_end != cudaSuccess) return fail(SMC_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce_end));
       cudaError_t ce = cudaGraphInstantiate(&e->row_graph, g, 0);
       cudaGraphDestroy(g);
       if (ce != cudaSuccess) { e->row_graph = nullptr; return fail(SMC_ERR_CUDA, cudaGetErrorString(ce)); }
@@ -1489,12 +1546,16 @@ int launch_rows(smc_engine* e, int64_t count) {
       e->launches += GRAPH_ROWS;
     }
   }
-  for (; count > 0; count--) launch_row(e, 0);
+  for (; count > 0; count--) {
+    int rc = launch_row(e, 0);
+    if (rc) return rc;
+  }
   return 0;
 }
 
 int materialise(smc_engine* e) {
-  launch_row(e, 1);
+  int rc = launch_row(e, 1);
+  if (rc) return rc;
   smc_commit_kernel<<<1, 1, 0, e->stream>>>(e->P.ctrl);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
@@ -1603,6 +1664,7 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
     if ((rc = dev_alloc(e, &P.bmax[b], P.nblocks))) { smc_destroy(e); return rc; }
     if ((rc = dev_alloc(e, &P.bsum[b], P.nblocks))) { smc_destroy(e); return rc; }
     if ((rc = dev_alloc(e, &P.bsq[b], P.nblocks))) { smc_destroy(e); return rc; }
+    if ((rc = dev_alloc(e, &P.barea[b], P.nblocks))) { smc_destroy(e); return rc; }
   }
   P.rank = 0; P.world = 1; P.Ntot = (long long)N; P.base = 0;
   if ((rc = dev_alloc(e, &P.psum, cfg->parity_scan ? N + 1 : 1))) { smc_destroy(e); return rc; }
@@ -1971,7 +2033,7 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
     if (P.world > 1 && (rc = exchange_slab(e, slab, P.peer_tally))) return rc;
   }
   P.rs_cap = R;
-  if ((rc = dev_alloc(e, &P.rs_pos, R)) || (rc = dev_alloc(e, &P.rs_ess, R))) return rc;
+  if ((rc = dev_alloc(e, &P.rs_pos, R)) || (rc = dev_alloc(e, &P.rs_ess, R)) || (rc = dev_alloc(e, &P.row_opp, R))) return rc;
   CUDA_TRY(cudaStreamSynchronize(e->stream));   // host vectors go out of scope
   e->rows_ready = true;
   return 0;
@@ -2000,13 +2062,13 @@ int smc_sweep(smc_engine* e, int64_t row_begin, int64_t row_end) {
   if (row_begin != e->swept) return fail(SMC_ERR_STATE, "rows must be swept in order, starting where the last sweep ended");
   if (row_end < row_begin || row_end > e->P.R) return fail(SMC_ERR_ARG, "row range out of bounds");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
-  cudaEventRecord(e->ev0, e->stream);
+  CUDA_TRY(cudaEventRecord(e->ev0, e->stream));
   {
     // sharded engines take the same path: the ranks' per-row exchange happens inside the row kernel (peer mailbox)
     int rc = launch_rows(e, row_end - row_begin);
     if (rc) return rc;
   }
-  cudaEventRecord(e->ev1, e->stream);
+  CUDA_TRY(cudaEventRecord(e->ev1, e->stream));
   CUDA_TRY(cudaGetLastError());
   // timing is collected lazily: the events are read at the next synchronising call
   e->swept = row_end;
@@ -2030,7 +2092,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
   }
   // every engine has its own stream: launches of different chunks interleave and run concurrently on the device
   CUDA_TRY(cudaSetDevice(engines[0]->cfg.device));
-  cudaEventRecord(engines[0]->ev0, engines[0]->stream);
+  CUDA_TRY(cudaEventRecord(engines[0]->ev0, engines[0]->stream));
   for (int k = 1; k < count; k++) {
     CUDA_TRY(cudaSetDevice(engines[k]->cfg.device));
     if (engines[k]->cfg.device == engines[0]->cfg.device) cudaStreamWaitEvent(engines[k]->stream, engines[0]->ev0, 0);
@@ -2056,7 +2118,7 @@ int smc_sweep_many(smc_engine** engines, int32_t count, int64_t rows_per_turn) {
   for (int k = 0; k < count; k++) {
     smc_engine* e = engines[k];
     CUDA_TRY(cudaSetDevice(e->cfg.device));
-    cudaEventRecord(e->ev1, e->stream);
+    CUDA_TRY(cudaEventRecord(e->ev1, e->stream));
   }
   for (int k = 0; k < count; k++) {
     smc_engine* e = engines[k];
@@ -2120,7 +2182,7 @@ int smc_finish(smc_engine* e) {
     for (int q = 0; q < upto; q++) fp[cs[q].x] = cs[q].y + 1;
   }
   CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, fp.data(), fp.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
-  cudaEventRecord(e->ev0, e->stream);
+  CUDA_TRY(cudaEventRecord(e->ev0, e->stream));
   if (e->P.sm.P > 1) smc_flush_struct_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
   else smc_flush_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
   e->launches++;
@@ -2129,7 +2191,7 @@ int smc_finish(smc_engine* e) {
     NCCL_TRY(g_nccl.AllReduce(e->P.tallies, e->P.tallies, (size_t)e->tally_rows * e->cfg.E, ncclDouble, ncclSum, e->comm, e->stream));
     NCCL_TRY(g_nccl.AllReduce(&e->P.ctrl->n_recomb, &e->P.ctrl->n_recomb, 1, ncclUint64, ncclSum, e->comm, e->stream));
   }
-  cudaEventRecord(e->ev1, e->stream);
+  CUDA_TRY(cudaEventRecord(e->ev1, e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   float ms = 0;
   cudaEventElapsedTime(&ms, e->ev0, e->ev1);
@@ -2151,6 +2213,16 @@ static int read_ctrl(smc_engine* e, Ctrl* c) {
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   CUDA_TRY(cudaMemcpy(c, e->P.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int smc_get_row_opportunity(smc_engine* e, double* out) {
+  if (!e || !out) return fail(SMC_ERR_ARG, "null argument");
+  if (!e->rows_ready) return fail(SMC_ERR_STATE, "upload rows first");
+  CUDA_TRY(cudaSetDevice(e->cfg.device));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  CUDA_TRY(cudaMemcpy(out, e->P.row_opp, (size_t)e->P.R * sizeof(double), cudaMemcpyDeviceToHost));
+  for (long long r = e->swept; r < e->P.R; r++) out[r] = 0.0;       // rows not swept yet
   return 0;
 }
 
@@ -2381,8 +2453,10 @@ int smc_normalize_log(int device, double* logw, int64_t N, double* lnZ, double* 
 // shared by the two calibration entry points; npop <= 1: single population (inv2N[E]), else structured tables
 static int calibrate_impl(int device, int32_t n, int32_t E, const double* t_start, int32_t npop, const double* inv2N,
                           const double* mig, const double* single_mig, const int32_t* leaf_pop, double rho, double seqlen,
-                          uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events) {
-  if (!t_start || !inv2N || !median_survival) return fail(SMC_ERR_ARG, "null argument");
+                          uint64_t seed, int64_t n_args, double* median_survival, int64_t* n_events,
+                          int32_t nq = 0, const double* quantiles = nullptr, double* tbl = nullptr, double* mean_tl = nullptr) {
+  const bool terminal = quantiles != nullptr;      // terminal branch length quantiles instead of survival distances
+  if (!t_start || !inv2N || (!terminal && !median_survival) || (terminal && (!tbl || nq < 1))) return fail(SMC_ERR_ARG, "null argument");
   if (n_args < 1) return fail(SMC_ERR_ARG, "n_args must be >= 1");
   int rc = use_device(device);
   if (rc) return rc;
@@ -2392,9 +2466,9 @@ static int calibrate_impl(int device, int32_t n, int32_t E, const double* t_star
   std::vector<double> inv0(E);
   for (int e = 0; e < E; e++) inv0[e] = st ? inv2N[(size_t)e * npop] : inv2N[e];
   if ((rc = fill_model(m, n, E, 0.0, rho, seqlen, 0, t_start, inv0.data(), nullptr, nullptr))) return rc;
-  const int BS = AUX_BS, per = n - 1;
+  const int BS = AUX_BS, per = terminal ? n : n - 1;
   DevBuf dd, de, df, t_inv, t_mig, t_tot, t_single, t_fixed, t_leaf;
-  if ((rc = dd.alloc(n_args * per * sizeof(double))) || (rc = de.alloc(n_args * per * sizeof(int))) || (rc = df.alloc(sizeof(int))))
+  if ((rc = dd.alloc(n_args * per * sizeof(double))) || (rc = de.alloc(n_args * (terminal ? 2 : per) * sizeof(int))) || (rc = df.alloc(sizeof(int))))
     return rc;
   CUDA_TRY(cudaMemset(df.p, 0, sizeof(int)));
   SModelDev sm;
@@ -2446,12 +2520,35 @@ static int calibrate_impl(int device, int32_t n, int32_t E, const double* t_star
     if (smem > 230400) { sm.K = 2 * n + 8; smem = stree_smem(m.nn, E, sm.K, BS); }
     if (smem > 230400) return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has");
     CUDA_TRY(cudaFuncSetAttribute(k_survival<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
-    k_survival<true><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
+    CUDA_TRY(cudaFuncSetAttribute(k_terminal<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+    if (terminal) k_terminal<true><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (double*)de.p, (int*)df.p);
+    else k_survival<true><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
   } else {
     CUDA_TRY(cudaFuncSetAttribute(k_survival<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
-    k_survival<false><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
+    CUDA_TRY(cudaFuncSetAttribute(k_terminal<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+    if (terminal) k_terminal<false><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (double*)de.p, (int*)df.p);
+    else k_survival<false><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
   }
   CUDA_TRY(cudaGetLastError());
+  if (terminal) {
+    std::vector<double> d(n_args * per), tl(n_args);
+    int fl = 0;
+    CUDA_TRY(cudaMemcpy(d.data(), dd.p, d.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(tl.data(), de.p, tl.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(&fl, df.p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (fl & SFLAG_NOCOAL) return fail(SMC_ERR_NUMERIC, "Lines did not coalescence: the populations of the model never join and do not exchange migrants");
+    for (int v = 0; v < n; v++) {
+      std::sort(d.begin() + (size_t)v * n_args, d.begin() + (size_t)(v + 1) * n_args);
+      for (int k = 0; k < nq; k++) {
+        if (!(quantiles[k] >= 0.0 && quantiles[k] < 1.0)) return fail(SMC_ERR_ARG, "quantiles must be in [0,1)");
+        tbl[(size_t)v * nq + k] = d[(size_t)v * n_args + (size_t)(quantiles[k] * (double)n_args)];   // smcsmc.cpp:158
+      }
+    }
+    double sum = 0.0;
+    for (double x : tl) sum += x;
+    if (mean_tl) *mean_tl = sum / (double)n_args;
+    return 0;
+  }
   std::vector<double> dist(n_args * per);
   std::vector<int> ep(n_args * per);
   int flags = 0;
@@ -2564,3 +2661,20 @@ extern "C" int smc_resample_counts_noalloc(int device, const double* d_w, int64_
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
+
+extern "C" int smc_terminal_branch_quantiles(int device, int32_t n, int32_t E, const double* t_start, int32_t npop,
+                                             const double* inv2N, const double* mig, const double* single_mig,
+                                             const int32_t* leaf_pop, uint64_t seed, int64_t n_trees, int32_t nq,
+                                             const double* quantiles, double* lengths, double* mean_total_length) {
+  if (!quantiles || !lengths) return fail(SMC_ERR_ARG, "null argument");
+  return calibrate_impl(device, n, E, t_start, npop < 2 ? 1 : npop, inv2N, mig, single_mig, leaf_pop, 1e-8, 1.0, seed, n_trees,
+                        nullptr, nullptr, nq, quantiles, lengths, mean_total_length);
+}
+
+#ifdef SMC_CLOCKS
+extern "C" int smc_debug_clocks(unsigned long long out[16], int reset) {
+  CUDA_TRY(cudaMemcpyFromSymbol(out, smc::g_clk, sizeof(unsigned long long) * 16));
+  if (reset) { unsigned long long z[16] = {0}; CUDA_TRY(cudaMemcpyToSymbol(smc::g_clk, z, sizeof(z))); }
+  return 0;
+}
+#endif

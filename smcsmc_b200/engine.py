@@ -157,6 +157,12 @@ class ParticleFilter:
         check(lib().smc_get_counters(self._h, _P(c)))
         return dict(rows=int(c[0]), resamples=int(c[1]), recombinations=int(c[2]), err=int(c[3]))
 
+    def row_opportunity(self):
+        """per row: sum_i w_i * (local tree length x bp over the row), the local recombination map's opportunity"""
+        out = np.zeros(self.R)
+        check(lib().smc_get_row_opportunity(self._h, _P(out)))
+        return out
+
     def resample_log(self):
         pos, ess = np.zeros(max(self.R, 1)), np.zeros(max(self.R, 1))
         k = ctypes.c_int64()
@@ -258,4 +264,22 @@ def calibrate_survival_struct(n, t_start, inv2N, mig, single_mig, leaf_pop, rho,
                                               None if sg is None else _P(sg), _P(lp), rho, seqlen, seed, n_args,
                                               _P(med), _P(cnt)))
     return med, cnt
+
+
+def terminal_branch_quantiles(n, t_start, inv2N, quantiles=(0.001, 0.003, 0.01, 0.03, 0.1, 0.5, 0.95), n_trees=1000000, seed=1,
+                              mig=None, single_mig=None, leaf_pop=None, device=0):
+    """calculate_terminal_branch_length_quantiles (smcsmc.cpp:128): (lengths[n][len(quantiles)], mean tree length) from
+    n_trees prior trees drawn on the device; inv2N[E] for one population, [E][P] with leaf_pop for several"""
+    ts, iv, q = _f64(t_start), _f64(inv2N), _f64(quantiles)
+    E = len(ts)
+    npop = 1 if iv.ndim == 1 else iv.shape[1]
+    out = np.zeros((n, len(q)))
+    mean = ctypes.c_double()
+    mg = None if mig is None else _f64(mig)
+    sg = None if single_mig is None else _f64(single_mig)
+    lp = None if leaf_pop is None else np.ascontiguousarray(leaf_pop, dtype=np.int32)
+    check(lib().smc_terminal_branch_quantiles(device, n, E, _P(ts), npop, _P(iv), None if mg is None else _P(mg),
+                                              None if sg is None else _P(sg), None if lp is None else _P(lp), seed,
+                                              n_trees, len(q), _P(q), _P(out), ctypes.byref(mean)))
+    return out, mean.value
 

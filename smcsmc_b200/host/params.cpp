@@ -1,6 +1,7 @@
 // Command-line parser: PfParam::parse (pfparam.cpp:51-169) + the subset of scrm's Param::parse (param.cc:37-520) that
 // the piecewise-constant engine supports: sizes per epoch and population, migration matrices, joins (-ej / -eps).
 #include "params.hpp"
+#include <iostream>
 #include <algorithm>
 #include <cstdio>
 
@@ -53,7 +54,7 @@ Epoch& epoch_at(Params& P, double t) {
 // model.cc:672-686).  Tables are sized for the final number from the start; an option that addresses "all populations"
 // touches the ones declared so far and leaves the later ones as "not given" (NaN), which is what scrm's
 // addPopToVectorList / addPopToMatrixList produce.
-int g_cur_pops = 1;
+thread_local int g_cur_pops = 1;   // populations in existence while the scrm flags are read (-I, then -es adds one)
 
 void check_pop(const Params& P, int pop, const std::string& flag) {
   if (pop < 0 || pop >= g_cur_pops) throw std::invalid_argument("Invalid population in option " + flag);
@@ -163,8 +164,15 @@ void parse(int argc, char** argv, Params& P) {
       P.calibrate_lag = true; P.lag_fraction = a.next_double(f);
       if (P.lag_fraction < 0.0) throw std::invalid_argument("Out of range: -calibrate_lag " + a.cur());
     }
-    else if (f == "-delay") { (void)a.next_double(f); }        // only used with -bias_* / -guide (not supported): no effect
-    else if (f == "-delay_coal" || f == "-delay_migr") {}
+    else if (f == "-delay") {
+      // the delay of an importance weight only exists with -bias_* / -guide, which the engine rejects: accepted, no effect
+      (void)a.next_double(f);
+      std::cerr << "Note: -delay has no effect (importance-weight delays belong to -bias_heights / -guide, which the B200 "
+                   "engine does not support yet)" << std::endl;
+    }
+    else if (f == "-delay_coal" || f == "-delay_migr")
+      std::cerr << "Note: " << f << " has no effect (importance-weight delays belong to -bias_heights / -guide, which the "
+                   "B200 engine does not support yet)" << std::endl;
     else if (f == "-ancestral_aware") P.ancestral_aware = true;
     else if (f == "-dephase") P.dephase = true;
     else if (f == "-apf") { if ((int)a.next_double(f) != 0) unsupported(f, "auxiliary particle filter"); }

@@ -416,16 +416,61 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
   }
   const double resample_count = (double)counters[1], delayed_opp = P.loci_length;
 
-  {   // <prefix>.recomb.gz: header of CountModel::dump_local_recomb_logs (count.cpp:616-628); the per-100-bp table is
-      // row f2 of the scope table and is left empty
+  {   // <prefix>.recomb.gz (CountModel::dump_local_recomb_logs, count.cpp:616-654): per 100-bp bin the posterior-mean
+      // recombination opportunity per nucleotide.  Each .seg row's opportunity (smc_get_row_opportunity) is spread
+      // evenly over the row with the reference's differential book-keeping (record_local_recomb_events,
+      // count.cpp:559-587).  The per-sample / time / log_time columns (recombination events attributed to their
+      // descendants) are row f2 of the scope table and read 0.
+    const double bin = 100.0;
+    bool any_rec = false, all_rec = true;
+    for (int e = 0; e < E; e++) {
+      const bool on = e < (int)P.record_event_in_epoch.size() ? (P.record_event_in_epoch[e] & 1) : true;
+      any_rec = any_rec || on; all_rec = all_rec && on;
+    }
+    if (any_rec && !all_rec && em == 0)
+      clog << " Note: " << out.recomb_name << " reports the opportunity of all epochs, including those excluded with -xr" << endl;
+    const size_t nbins = any_rec ? (size_t)(P.loci_length / bin) : 0;     // no recorded recombinations: header only
+    vector<double> diff(nbins + 3, 0.0);
+    for (size_t k = 0; k < C && nbins; k++) {
+      const host::SegRows& rows = chunks[k];
+      vector<double> ro(rows.rows());
+      check(smc_get_row_opportunity(eng[k], ro.data()));
+      const double off = chunk_start[k] - P.start_position;
+      for (size_t r = 0; r < rows.rows(); r++) {
+        const double xs = off + (r ? rows.x_end[r - 1] : 0.0), xe = off + rows.x_end[r];
+        if (!(xs < xe)) continue;
+        const size_t first = (size_t)(xs / bin), last = (size_t)(1 + xe / bin);
+        if (last + 1 > diff.size()) diff.resize(last + 1, 0.0);
+        const double fi = min((first + 1) * bin, xe) - xs, li = xe - max((last - 1) * bin, xs), dens = ro[r] / (xe - xs);
+        if (first == last - 1) { diff[first] += fi * dens; diff[first + 1] -= fi * dens; }
+        else {
+          diff[first] += fi * dens; diff[first + 1] += (bin - fi) * dens;
+          diff[last - 1] += (li - bin) * dens; diff[last] -= li * dens;
+        }
+      }
+    }
     gzFile g = gzopen(out.recomb_name.c_str(), "ab");
-    if (g && em == 0) {
+    if (!g) throw runtime_error("cannot open " + out.recomb_name);
+    if (em == 0) {
       string h = "iter\tlocus\tsize\topp_per_nt";
       for (int s = 0; s < n; s++) h += "\t" + to_string(s + 1);
       h += "\ttime\tlog_time\n";
       gzwrite(g, h.data(), (unsigned)h.size());
     }
-    if (g) gzclose(g);
+    string zeros;
+    for (int s = 0; s < n + 2; s++) zeros += "\t0.00000e+00";
+    zeros += "\n";
+    string buf;
+    char line[96];
+    double cur = 0.0;
+    for (size_t i = 0; i < nbins; i++) {
+      cur += diff[i];
+      snprintf(line, sizeof line, "%d\t%.0f\t%.0f\t%.5e", em, i * bin + P.start_position, bin, cur / bin);
+      buf += line; buf += zeros;
+      if (buf.size() > (1u << 20)) { gzwrite(g, buf.data(), (unsigned)buf.size()); buf.clear(); }
+    }
+    if (!buf.empty()) gzwrite(g, buf.data(), (unsigned)buf.size());
+    gzclose(g);
   }
 
   // reset_model_parameters(force_update = true): the in-binary M-step (count.cpp:44-63,267-352)

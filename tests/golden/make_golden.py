@@ -562,3 +562,66 @@ def golden_smc2_frontend():
         subprocess.run([sys.executable, os.path.join(root, "tests", "smc2_helper.py"), ref_binary(), out, seg], check=True,
                        stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         shutil.copy(os.path.join(out, "result.out"), os.path.join(HERE, "smc2_frontend_reference.out"))
+
+
+def golden_tbl_quantiles(count=200000):
+    """Terminal branch lengths of the reference's own prior trees (Forest::buildInitialTree through libsmcref), sorted and
+    read at the reference's quantile indices (calculate_terminal_branch_length_quantiles, smcsmc.cpp:128-167), for the
+    zigzag model with 8 samples; tests/test_gpu_parity.py compares smc_terminal_branch_quantiles with it in law."""
+    import json
+    q = [0.001, 0.003, 0.01, 0.03, 0.1, 0.5, 0.95]
+    cmd = ("-nsam 8 -Np 10 -N0 10000 -t 1000 -r 400 1000000 " +
+           " ".join("-eN %r %r" % (t, s) for t, s in zip(C1_TIMES, [1, .2, 1, .2, 1, .2, 1, .2, 1, .2, 1])) + " -seed 5")
+    h = _libs.ref_open("smcsmc " + cmd)
+    L = _libs.ref()
+    n, nn = 8, 15
+    parent = np.zeros((count, nn), dtype=np.int32)
+    height = np.zeros((count, nn))
+    tl = np.zeros(count)
+    assert L.ref_prior_trees(h, count, _libs.P(parent), _libs.P(height), _libs.P(tl)) == 0
+    tbl = np.take_along_axis(height, parent[:, :n], axis=1)          # parent height of every leaf
+    lengths = [[float(np.sort(tbl[:, v])[int(x * count)]) for x in q] for v in range(n)]
+    json.dump({"cmd": cmd, "quantiles": q, "count": count, "lengths": lengths, "mean_total_length": float(tl.mean())},
+              open(os.path.join(HERE, "tbl_quantiles.json"), "w"), indent=1)
+
+
+def read_recomb_map(path, iteration=0):
+    """<prefix>.recomb.gz -> (locus, opp_per_nt, rest) of one iteration (CountModel::dump_local_recomb_logs)"""
+    import gzip
+    loc, opp, rest = [], [], []
+    with gzip.open(path, "rt") as f:
+        header = f.readline().rstrip("\n").split("\t")
+        for line in f:
+            c = line.rstrip("\n").split("\t")
+            if int(c[0]) != iteration:
+                continue
+            loc.append(float(c[1])); opp.append(float(c[3])); rest.append([float(v) for v in c[4:]])
+    return header, np.array(loc), np.array(opp), np.array(rest)
+
+
+def golden_recomb_map(seeds=range(1, 13), window=50000):
+    """The opportunity column of the reference's local recombination map (<prefix>.recomb.gz) on
+    tests/data/const_n4_2Mb_seed7.seg, one sweep per seed with the corrected binary, averaged over 50-kb windows;
+    tests/test_gpu_parity.py compares the B200 driver's table with it window by window."""
+    import json
+    import subprocess
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+    seg = os.path.join(os.path.dirname(HERE), "data", "const_n4_2Mb_seed7.seg")
+    out = {"base": EM_BASE, "extra": "-EM 0", "seeds": list(seeds), "window": window, "binary": "smcsmc_fixed"}
+    with tempfile.TemporaryDirectory() as tmp:
+        def run(seed):
+            o = os.path.join(tmp, "m_s%d" % seed)
+            subprocess.run([ref_binary()] + EM_BASE.format(extra="-EM 0", seed=seed, seg=seg, out=o).split(), check=True,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            header, loc, opp, rest = read_recomb_map(o + ".recomb.gz")
+            rows = parse_out(o + ".out")
+            total = [r for r in rows if r["Type"] == "Recomb"]
+            k = int(window // 100)
+            nw = len(opp) // k
+            return {"header": header, "bins": int(len(opp)), "first_locus": float(loc[0]), "last_locus": float(loc[-1]),
+                    "windows": opp[:nw * k].reshape(nw, k).mean(axis=1).tolist(), "sum_opp": float(opp.sum() * 100.0),
+                    "out_recomb_opp": float(sum(float(r["Opp"]) for r in total))}
+        with ThreadPoolExecutor(8) as ex:
+            out["runs"] = list(ex.map(run, seeds))
+    json.dump(out, open(os.path.join(HERE, "recomb_map_reference.json"), "w"))

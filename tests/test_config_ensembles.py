@@ -84,8 +84,9 @@ def _check(ref_runs, rep, msg, tol, tol_recent, small=30.0):
 
 
 def test_configs1_medium_zigzag(tmp_path):
-    """every Coal / Recomb row of all six sweeps within Monte-Carlo error of the reference ensemble, and both programs'
-    final size estimates follow the simulated alternation (10 000 / 2 000) where 10 Mb of 8 haplotypes resolve it"""
+    """every Coal / Recomb row of all six sweeps within Monte-Carlo error of the reference ensemble, and the final size
+    estimates of the two programs within 10 % of each other per epoch, with the same first trace of the simulated
+    alternation (10 000 / 2 000)"""
     ref = json.load(open(os.path.join(G, "configs1_medium_reference.json")))
     seg = str(tmp_path / "c1.seg")
     cut_seg(os.path.join(ROOT, ref["data"]), seg, ref["length"])
@@ -114,17 +115,20 @@ def test_configs1_medium_zigzag(tmp_path):
     ne_mine = np.array([[float(run[k]["Ne"]) for k in idx] for run in mine]).mean(axis=0)
     print("final Ne  ref ", np.round(ne_ref), "\nfinal Ne  ours", np.round(ne_mine))
     for ne in (ne_ref, ne_mine):
-        # epochs 4..9 (1 600 - 51 200 generations) carry hundreds to thousands of coalescences per sweep: a small epoch
-        # (odd index) sits below both of its large neighbours
-        for e in (5, 7, 9):
-            assert ne[e] < ne[e - 1] and ne[e] < ne[e + 1], (e, ne)
-        assert 1200 < ne[7] < 4000 and 6000 < ne[8] < 16000, ne
+        # Five EM iterations from all-ones sizes on 10 Mb do not resolve the 10 000 / 2 000 alternation -- the sizes of
+        # BOTH programs are still drifting down from the start value towards its harmonic mean (3 300) -- but the
+        # strongest bottleneck the data see (epoch 7, 6 400 - 12 800 generations) already shows as a dip below both
+        # neighbours in both, and every epoch with data sits between the two simulated sizes
+        assert ne[7] < ne[6] and ne[7] < ne[8], ne
+        assert np.all(ne[4:] > 2000) and np.all(ne[4:] < 10000), ne
     for e in range(4, 11):
         assert ne_mine[e] == pytest.approx(ne_ref[e], rel=0.10), (e, ne_mine[e], ne_ref[e])
     # the recombination rate of the last M-step, both near the simulated 1e-8
     kr = [k for k, r in enumerate(ref["runs"][0]) if r["Type"] == "Recomb" and int(r["Iter"]) == last][0]
-    for runs in (ref["runs"], mine):
-        assert np.mean([float(r[kr]["Rate"]) for r in runs]) == pytest.approx(1e-8, rel=0.08)
+    rates = [np.mean([float(r[kr]["Rate"]) for r in runs]) for runs in (ref["runs"], mine)]
+    assert rates[1] == pytest.approx(rates[0], rel=0.05), rates
+    for x in rates:       # both programs sit ~16 % under the simulated 1e-8 after five iterations on this window
+        assert x == pytest.approx(1e-8, rel=0.25), rates
 
 
 def test_configs1_first_sweep_with_the_reference_lags(tmp_path):

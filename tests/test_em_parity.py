@@ -69,7 +69,9 @@ def test_out_file_format(runs):
         assert len(line) == len(raw[0])
     assert os.path.exists(out + ".log") and "smcsmc log" in open(out + ".log").read()
     import gzip
-    assert gzip.open(out + ".recomb.gz", "rt").readline().startswith("iter\tlocus\tsize\topp_per_nt\t1\t2\t3\t4\ttime")
+    lines = gzip.open(out + ".recomb.gz", "rt").read().splitlines()
+    # -xr 0-3: no recombination recorded anywhere, the table is its header (count.cpp:619: no bins were ever touched)
+    assert lines == ["iter\tlocus\tsize\topp_per_nt\t1\t2\t3\t4\ttime\tlog_time"]
     assert "Lags set to:" in r.stderr and "survival distance" in r.stderr and "resampled" in r.stderr
 
 
@@ -181,6 +183,60 @@ def test_calibration_matches_reference_survival_distances():
     ratio = med[7:] / np.array(ref[7:])
     assert np.all(ratio > 0.65) and np.all(ratio < 1.05), ratio
     assert med[0] == pytest.approx(ref[0], rel=0.35)            # epoch 0: few nodes are that young
+
+
+def _read_recomb_map(path):
+    import gzip
+    with gzip.open(path, "rt") as f:
+        header = f.readline().rstrip("\n")
+        rows = [line.rstrip("\n").split("\t") for line in f]
+    return header, rows
+
+
+def test_local_recombination_map_opportunity(runs, tmp_path):
+    """<prefix>.recomb.gz (CountModel::dump_local_recomb_logs, count.cpp:616-654): same header, same bins (100 bp from
+    the start position), same number formats as the reference's table; the opportunity column -- the posterior-mean
+    local tree length -- follows the reference's 50-kb window means (fixture from the corrected binary, 12 seeds) along
+    the 2 Mb, sums to the Recomb row's opportunity of the .out file, and -chunks writes the same table."""
+    ref, mine = runs
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "recomb_map_reference.json")))
+    g0 = gold["runs"][0]
+    k = gold["window"] // 100
+    wins = []
+    for out, r in mine["sweep"][:len(gold["seeds"])]:
+        header, rows = _read_recomb_map(out + ".recomb.gz")
+        assert header.split("\t") == g0["header"]
+        assert len(rows) == g0["bins"]
+        assert (float(rows[0][1]), float(rows[-1][1])) == (g0["first_locus"], g0["last_locus"])
+        assert rows[0][:3] == ["0", "1", "100"] and rows[-1][:3] == ["0", "1999901", "100"]
+        for c in rows[0][3:] + rows[-1][3:]:
+            assert re.match(r"^\d\.\d{5}e[+-]\d\d$", c), c
+        opp = np.array([float(x[3]) for x in rows])
+        assert all(float(v) == 0.0 for x in rows[::997] for v in x[4:])      # event columns: scope row f2
+        # the table integrates to the sweep's recombination opportunity (filtering vs lagged weights: 2 %)
+        total = sum(float(x["Opp"]) for x in parse_out(out + ".out")[1] if x["Type"] == "Recomb")
+        assert opp.sum() * 100.0 == pytest.approx(total, rel=0.02)
+        wins.append(opp[:len(opp) // k * k].reshape(-1, k).mean(axis=1))
+    wins = np.array(wins)
+    refw = np.array([x["windows"] for x in gold["runs"]])
+    assert all(x["sum_opp"] == pytest.approx(x["out_recomb_opp"], rel=1e-4) for x in gold["runs"])
+    m, rm = wins.mean(axis=0), refw.mean(axis=0)
+    print("ours", m.round(0), "ref", rm.round(0), "ratio", (m / rm).round(3), sep="\n")
+    assert np.corrcoef(m, rm)[0, 1] > 0.99
+    assert m.sum() == pytest.approx(rm.sum(), rel=0.02)
+    se = np.sqrt(wins.var(axis=0, ddof=1) / len(wins) + refw.var(axis=0, ddof=1) / len(refw))
+    z = (m - rm) / np.sqrt(se ** 2 + (0.05 * rm) ** 2)      # 5 %: filtering (ours) vs fixed-lag smoothing (reference) weights
+    assert np.abs(z[1:]).max() < 4.0, z                     # window 0: the sweeps start from different prior draws
+    # multi-window sweep: the table has the same bins and, away from window starts, the same opportunity
+    out = str(tmp_path / "c4")
+    cmd = [BIN] + ref["base"].format(extra="-EM 0", seed=5, seg=SEG, out=out).split() + ["-chunks", "4"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    header, rows = _read_recomb_map(out + ".recomb.gz")
+    assert len(rows) == g0["bins"] and rows[-1][1] == "1999901"
+    c4 = np.array([float(x[3]) for x in rows])
+    c4 = c4[:len(c4) // k * k].reshape(-1, k).mean(axis=1)
+    assert np.corrcoef(c4, rm)[0, 1] > 0.95
 
 
 def test_chunks_extension_adds_up(tmp_path):

@@ -227,6 +227,10 @@ def test_full_filter_vs_oracle(S, name):
     for q in (0, 1, 3, 4):       # counts and opportunities (linear in the weights)
         np.testing.assert_allclose(t[q], ref["tallies"][q], rtol=1e-10, atol=1e-13)
     assert t[4].sum() > 0 and (name == "R1_single_row" or (t[1].sum() > 0 and t[3].sum() > 0))
+    if max_rec is None:          # per-row opportunity of the local recombination map (filtering weights)
+        ro = pf.row_opportunity()
+        np.testing.assert_allclose(ro, ref["row_opp"], rtol=1e-10, atol=0)
+        assert ro.sum() == pytest.approx(t[4].sum(), rel=0.2) and np.all(ro[np.diff(x_end, prepend=0.0) > 0] > 0)
     # weight^2 tallies: copies do not share records, so sum(w^2 opp) is a lower bound of the reference's value
     assert np.all(t[2] <= ref["tallies"][2] * (1 + 1e-9) + 1e-300)
     assert np.all(t[5] <= ref["tallies"][5] * (1 + 1e-9) + 1e-300)
@@ -467,3 +471,27 @@ def test_errors(S):
     with pytest.raises(S.SmcError):
         S.systematic_offspring(np.array([0.0, 1.0]), 1.5)
     pf.close()
+
+
+def test_terminal_branch_quantiles_vs_reference_prior_trees(S):
+    """calculate_terminal_branch_length_quantiles (smcsmc.cpp:128-167) on the device against the same statistic of the
+    reference's own prior trees (tests/golden/tbl_quantiles.json, 2e5 trees through libsmcref): zigzag model, n = 8.
+    In law: the quantile of an order statistic has relative error ~ 1 / sqrt(q * count)."""
+    import json
+    g = json.load(open(os.path.join(G, "tbl_quantiles.json")))
+    t = [4e4 * x for x in (0, .0025, .005, .01, .02, .04, .08, .16, .32, .64, 1.28)]
+    inv = [1 / (2e4 * s) for s in (1, .2, 1, .2, 1, .2, 1, .2, 1, .2, 1)]
+    q = g["quantiles"]
+    lengths, mean_tl = S.terminal_branch_quantiles(8, t, inv, quantiles=q, n_trees=1000000, seed=3)
+    ref = np.array(g["lengths"])
+    assert lengths.shape == ref.shape == (8, len(q))
+    assert mean_tl == pytest.approx(g["mean_total_length"], rel=0.01)
+    pooled, pooled_ref = lengths.mean(axis=0), ref.mean(axis=0)           # samples are exchangeable
+    for k, x in enumerate(q):
+        tol = 4.0 / np.sqrt(min(x, 1 - x) * g["count"]) + 0.01
+        assert pooled[k] == pytest.approx(pooled_ref[k], rel=tol), (x, pooled[k], pooled_ref[k])
+        np.testing.assert_allclose(lengths[:, k], ref[:, k], rtol=3 * tol)
+    assert np.all(np.diff(lengths, axis=1) > 0)
+    with pytest.raises(S.SmcError):
+        S.terminal_branch_quantiles(8, t, inv, quantiles=[1.5], n_trees=1000)
+
