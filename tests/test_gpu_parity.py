@@ -230,7 +230,7 @@ def test_full_filter_vs_oracle(S, name):
     if max_rec is None:          # per-row opportunity of the local recombination map (filtering weights)
         ro = pf.row_opportunity()
         np.testing.assert_allclose(ro, ref["row_opp"], rtol=1e-10, atol=0)
-        assert ro.sum() == pytest.approx(t[4].sum(), rel=0.2) and np.all(ro[np.diff(x_end, prepend=0.0) > 0] > 0)
+        assert np.all(ro[np.diff(x_end, prepend=0.0) > 0] > 0) and np.all(ro[np.diff(x_end, prepend=0.0) == 0] == 0)
     # weight^2 tallies: copies do not share records, so sum(w^2 opp) is a lower bound of the reference's value
     assert np.all(t[2] <= ref["tallies"][2] * (1 + 1e-9) + 1e-300)
     assert np.all(t[5] <= ref["tallies"][5] * (1 + 1e-9) + 1e-300)
