@@ -213,6 +213,9 @@ int smc_terminal_branch_quantiles(int device, int32_t n, int32_t E, const double
                                   const double* inv2N, const double* mig, const double* single_mig,
                                   const int32_t* leaf_pop, uint64_t seed, int64_t n_trees, int32_t nq,
                                   const double* quantiles, double* lengths, double* mean_total_length);
+/* Measurement helper (no reference counterpart): the device's sustained fp64 FMA rate in TFLOP/s from a register-only
+ * probe kernel; bench.py quotes the row kernel's fp64 work against it beside the HBM roofline. */
+int smc_measure_fp64_fma(int device, double* tflops);
 /* fastexp (particle.cpp:30-40) evaluated on the device, for the 1e-12 no-mutation-factor parity test */
 int smc_fastexp(int device, const double* x, int64_t count, double* out);
 

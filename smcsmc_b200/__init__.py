@@ -6,7 +6,7 @@ compute and has NO fallback: loading fails loudly when the CUDA library has not 
 """
 from ._abi import lib, lib_path, SmcError, SmcConfig  # noqa: F401
 from .engine import (ParticleFilter, shard_unique_id, sweep_many, site_likelihood, branch_lengths, systematic_offspring, resample_counts,  # noqa: F401
-                     normalize_log, fastexp, calibrate_survival, terminal_branch_quantiles)
+                     normalize_log, fastexp, calibrate_survival, terminal_branch_quantiles, measure_fp64_fma)
 from .segdata import read_seg, SegRows  # noqa: F401
 
 __version__ = "0.1"

@@ -56,6 +56,7 @@ SYMBOLS = {
     "smc_systematic_offspring": (_I, [_I, _V, _I64, _D, _V]),
     "smc_resample_counts": (_I, [_I, _V, _I64, _D, ctypes.c_int32, c_dp, _V]),
     "smc_get_row_opportunity": (_I, [_V, _V]),
+    "smc_measure_fp64_fma": (_I, [_I, _V]),
     "smc_terminal_branch_quantiles": (_I, [_I, ctypes.c_int32, ctypes.c_int32, _V, ctypes.c_int32, _V, _V, _V, _V,
                                             ctypes.c_uint64, _I64, ctypes.c_int32, _V, _V, c_dp]),
     "smc_resample_counts_noalloc": (_I, [_I, _V, _I64, _D, ctypes.c_int32, _V, _V, _V]),

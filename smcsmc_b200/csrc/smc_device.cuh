@@ -126,6 +126,7 @@ struct TreeViewT {
   double* L0;         // [n-1][BS] scratch for the internal nodes, addressed by node id (base shifted by -n rows)
   double* L1;         // [n-1][BS]
   double* ACC;        // [E][BS]  recombination opportunity summed over the current row
+  double* ACC2;       // [E][BS]  the same beyond the first bucket bound inside the row; shares the storage of L0 / L1
   int t, n;
   __device__ __forceinline__ double h(int v) const { return v < n ? 0.0 : H[v * BS + t]; }
   __device__ __forceinline__ double& hw(int v) const { return H[v * BS + t]; }        // internal nodes only
@@ -135,8 +136,10 @@ struct TreeViewT {
 };
 
 // Carve a block's dynamic shared memory into the per-thread columns of a TreeView.
+// scratch rows shared by L0 / L1 (2 (n-1) rows, used by the pruning passes) and ACC2 (E rows, used between them)
+__host__ __device__ inline size_t tree_scratch_rows(int nn, int E) { return (size_t)(nn - 1) > (size_t)E ? (size_t)(nn - 1) : (size_t)E; }
 __host__ __device__ inline size_t tree_bytes_per_thread(int nn, int E) {
-  return (size_t)(nn - 1) / 2 * 8 + (size_t)nn + (size_t)(nn - 1) * 8 + (size_t)E * 8;
+  return (size_t)(nn - 1) / 2 * 8 + (size_t)nn + tree_scratch_rows(nn, E) * 8 + (size_t)E * 8;
 }
 template <int BS>
 __device__ __forceinline__ TreeViewT<BS> make_tree_view(unsigned char* smem, int n, int nn, int E, int t) {
@@ -147,7 +150,8 @@ __device__ __forceinline__ TreeViewT<BS> make_tree_view(unsigned char* smem, int
   T.H = base - (size_t)n * BS;
   T.L0 = base + in - (size_t)n * BS;
   T.L1 = base + 2 * in - (size_t)n * BS;
-  T.ACC = base + 3 * in;
+  T.ACC2 = base + in;
+  T.ACC = base + in + tree_scratch_rows(nn, E) * BS;
   T.PAR = reinterpret_cast<signed char*>(T.ACC + (size_t)E * BS);
   return T;
 }
@@ -252,24 +256,32 @@ __device__ inline double site_likelihood(const ModelDev& m, const TV& T, const s
 // (record_recomb_extension, particle.cpp:305-357: sum over time slices of #lineages * slice length).  Internal slots are
 // sorted by height and all leaves sit at 0, so the slice between consecutive internal nodes carries n, n-1, ...
 // lineages; one ascending sweep completes the epochs in order and hands each one to the sink as soon as it is known.
+// Recombination opportunity per bp of the current tree inside each epoch (= the tree's branch length in the epoch),
+// handed to the sink for the stretch [xa, xb).  One merged walk over the height-sorted internal slots and the epoch
+// bounds: every iteration consumes whichever comes first, so the lanes of a warp stay in step (a loop over the nodes
+// with an inner loop over the bounds diverged on every tree: 25 % of a block's life at 11 epochs).
 template <class TV, class Sink>
 __device__ inline void record_recomb_opportunity(const ModelDev& m, const TV& T, Sink& sink, double xa, double xb,
                                                  int max_rec_epoch) {
-  const int n = m.n, E = m.E;
-  int e = 0, k = n;
+  const int n = m.n, nn = m.nn, E = m.E;
+  int e = 0, k = n, j = n;
   double lo = 0.0, len = 0.0;
-  for (int j = n; j < m.nn; j++) {
-    double hi = T.hw(j);
-    while (e + 1 < E && m.t_start[e + 1] < hi) {
-      double b = m.t_start[e + 1];
+  double hi = T.hw(j);
+  double b = e + 1 < E ? m.t_start[e + 1] : DBL_MAX;
+  for (;;) {
+    if (b < hi) {                        // the epoch ends below the next node
       if (b > lo) { len += k * (b - lo); lo = b; }
       if (len > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, xa, xb, len);
       len = 0.0;
       e++;
+      b = e + 1 < E ? m.t_start[e + 1] : DBL_MAX;
+    } else {                             // the next node
+      if (hi > lo) len += k * (hi - lo);
+      lo = hi;
+      k--;
+      if (++j == nn) break;
+      hi = T.hw(j);
     }
-    if (hi > lo) len += k * (hi - lo);
-    lo = hi;
-    k--;
   }
   if (len > 0.0 && (m.rec_mask[e] & 1) && e <= max_rec_epoch) sink.rec_opp(e, xa, xb, len);
 }
@@ -392,9 +404,9 @@ __device__ inline void smc_move(const ModelDev& m, const TV& T, Rng& r, double x
     int idx = (int)(rng_uniform(r) * k);
     if (idx >= k) idx = k - 1;
     int Tg = -1;
-    for (int v = 0; v < nn; v++) {
-      int p = T.par(v);
-      if (p >= 0 && T.h(v) <= tt && tt < T.hw(p)) { if (idx == 0) { Tg = v; break; } idx--; }
+    // slots are height-sorted and c is the first one above tt: the branches alive at tt are the v < c with parent >= c
+    for (int v = 0; v < c; v++) {
+      if (T.par(v) >= c) { if (idx == 0) { Tg = v; break; } idx--; }
     }
     if (Tg == b) {
       // back-coalescence into the stub: tree unchanged (SMC')
@@ -553,14 +565,21 @@ __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, d
       rp.c1 = r.c1 - (uint32_t)t + (uint32_t)tp; rp.c0 = ms.CTR[tp]; rp.spare = ms.SPARE[tp]; rp.have = ms.HAVE[tp];
       double lw = ms.LOGW[tp];
       const double x = ms.X[tp];
+#ifdef SMC_CLOCKS
+      long long clk2 = clock64();
+#endif
       smc_move(m, Tp, rp, x, max_rec_epoch, sp, lw, ms.TL[tp]);
+      SMC_CLK(11, clk2);               // the move
       nrec++;
       const double tl = tree_length(m, Tp);
       const double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, Tp, data);
+      SMC_CLK(12, clk2);               // tree length, observed length
       const double nb = draw_next_base(m, tl, rp, x);
       const double new_to = x1 < nb ? x1 : nb;
       lw += dlog(fastexp(-m.mu * L_obs * (new_to - x)));
+      SMC_CLK(13, clk2);               // next base, no-mutation factor
       record_recomb_opportunity(m, Tp, sp, x, new_to, max_rec_epoch);
+      SMC_CLK(14, clk2);               // recombination opportunity of the stretch
       again = new_to < x1;
       ms.X[tp] = nb; ms.LOGW[tp] = lw; ms.TL[tp] = tl; ms.AREA[tp] += tl * (new_to - x);
       ms.CTR[tp] = rp.c0; ms.SPARE[tp] = rp.spare; ms.HAVE[tp] = (unsigned char)rp.have;

@@ -174,11 +174,17 @@ struct RingSink {
   int t;
   const double* ubf;          // [E] shared: upper bound of the bucket open at the row's left end
   unsigned long long split;   // bit e: a bound of epoch e lies inside this row
+  const double* ubf2;         // [E] shared: the bound after ubf (the bucket born at ubf ends there)
+  double* ACC2;               // [E][BS] shared: recombination opportunity of the row in [ubf, ubf2), or NULL (row with
+                              // partly missing data: the scratch it aliases is in use, the cells are written through)
   // cells per epoch and where the recombination cells sit (single population: coal cnt, coal opp, rec cnt, rec opp)
   __device__ __forceinline__ int Q() const { return ST ? P->sm.Q : 4; }
   static constexpr int REC_CNT = ST ? 0 : 2, REC_OPP = ST ? 1 : 3;
   __device__ __forceinline__ int bucket(int e, double x) const {
     int k = ks[e];
+    if (x < ubf[e]) return k;
+    if (x < ubf2[e]) return k + 1;
+    k += 2;
     const double* ub = P->ub + P->ub_off[e];
     while (ub[k] <= x) k++;          // last bound is +inf
     return k;
@@ -193,7 +199,7 @@ struct RingSink {
     split = 0ull;
     for (int e = 0; e < P->m.E; e++) {
       ACC[e * BS + t] = 0.0;
-      if (ubf[e] < x1) split |= 1ull << e;
+      if (ubf[e] < x1) { split |= 1ull << e; if (ACC2) ACC2[e * BS + t] = 0.0; }
     }
   }
   __device__ void row_end() const {
@@ -212,12 +218,29 @@ struct RingSink {
 #pragma unroll
       for (int j = 0; j < 4; j++) if (a[j] != 0.0) *cp[j] = v[j] + a[j];
     }
+    if (ACC2 && split) {               // the buckets born at the first bound inside the row
+      for (int e0 = 0; e0 < E; e0 += 4) {
+        double a[4], v[4];
+        double* cp[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const int e = e0 + j;
+          const bool on = e < E && ((split >> e) & 1ull);
+          a[j] = on ? ACC2[e * BS + t] : 0.0;
+          cp[j] = cell(on ? e : 0, ks[on ? e : 0] + (on ? 1 : 0), REC_OPP);
+          v[j] = a[j] != 0.0 ? *cp[j] : 0.0;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) if (a[j] != 0.0) *cp[j] = v[j] + a[j];
+      }
+    }
   }
   __device__ void coal(int e, double x, int cnt, double opp) const {
     int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
     // count and opportunity sit side by side (16-byte aligned): one read-modify-write instead of two dependent ones.
-    // (Reductions -- atomicAdd without a return value -- were tried for these records and for the split path of rec_opp:
-    // 9 % slower here and 1.9 x slower there, the loop around an atomic no longer reconverges; profiles/r2_kernel_notes.md)
+    // (Tried and slower, profiles/r2_kernel_notes.md: reductions -- atomicAdd without a return value -- for these records
+    // (9 %) and for the split path of rec_opp (1.9 x: the loop around an atomic no longer reconverges); queueing a move's
+    // records and committing them together with all loads in flight (20 %: the queue lives in local memory).)
     double2* c2 = reinterpret_cast<double2*>(cell(e, k, 0));
     double2 v = *c2;
     v.x += cnt ? 1.0 : 0.0;
@@ -233,8 +256,27 @@ struct RingSink {
   }
   __device__ void smig(int e, int p, double x, int to, double dt) const {
     int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
-    *cell(e, k, cell_mig_opp(p)) += dt;
-    if (to >= 0) *cell(e, k, cell_mig_cnt(P->sm.P, p, to)) += 1.0;
+    double* base = cell(e, k, 0);
+    double* po = base + cell_mig_opp(p);
+    double* pm = base + cell_mig_cnt(P->sm.P, p, to >= 0 ? to : 0);
+    const double vo = *po, vm = to >= 0 ? *pm : 0.0;      // both loads in flight before the first store
+    *po = vo + dt;
+    if (to >= 0) *pm = vm + 1.0;
+  }
+  // One interval of the floating lineage in population p: coalescence opportunity (and event), migration opportunity
+  // (and event p -> to).  The three cells of a population are neighbours; everything is loaded before anything is stored,
+  // so the interval costs one round trip to L2 instead of three or four dependent ones (the same additions to the same
+  // cells as scoal + smig).
+  __device__ void srec(int e, int p, double x, int cnt, double opp, int to, double dt) const {
+    int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
+    double* base = cell(e, k, 0);
+    double* pc = base + cell_coal_cnt(p);                  // count, opportunity, migration opportunity
+    double* pm = base + cell_mig_cnt(P->sm.P, p, to >= 0 ? to : 0);
+    const double v0 = pc[0], v1 = pc[1], v2 = pc[2], vm = to >= 0 ? *pm : 0.0;
+    if (cnt) pc[0] = v0 + 1.0;
+    if (opp != 0.0) pc[1] = v1 + opp;
+    pc[2] = v2 + dt;
+    if (to >= 0) *pm = vm + 1.0;
   }
   __device__ void rec_event(int e, double x) const {
     int k = (split >> e) & 1ull ? bucket(e, x) : ks[e];
@@ -245,6 +287,12 @@ struct RingSink {
     // cell row_end() adds the accumulator to -- only what lies beyond that bound is written through
     if (!((split >> e) & 1ull) || xb <= ubf[e]) { ACC[e * BS + t] += rate * (xb - xa); return; }
     if (xa < ubf[e]) { ACC[e * BS + t] += rate * (ubf[e] - xa); xa = ubf[e]; }
+    if (ACC2 && xa < ubf2[e]) {        // the common case: one bound inside the row
+      const double end = xb < ubf2[e] ? xb : ubf2[e];
+      ACC2[e * BS + t] += rate * (end - xa);
+      xa = end;
+      if (!(xa < xb)) return;
+    }
     int k = bucket(e, xa);
     const double* ub = P->ub + P->ub_off[e];
     while (xa < xb) {
@@ -468,7 +516,17 @@ __global__ void SMC_ROW_BOUNDS
 smc_row_kernel(const __grid_constant__ Params P, int mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int t = threadIdx.x;
-  const ModelDev& m = P.m;
+  // The model tables are read with a per-lane epoch index all through the row.  In the parameter bank such a load is
+  // replayed once per distinct address in the warp (constant-cache broadcast); a copy in shared memory is not.
+  __shared__ ModelDev s_model;
+  {
+    static_assert(sizeof(ModelDev) % 8 == 0, "ModelDev is copied as 8-byte words");
+    const unsigned long long* srcw = reinterpret_cast<const unsigned long long*>(&P.m);
+    unsigned long long* dstw = reinterpret_cast<unsigned long long*>(&s_model);
+    for (int w = t; w < (int)(sizeof(ModelDev) / 8); w += BS) dstw[w] = srcw[w];
+  }
+  __syncthreads();
+  const ModelDev& m = s_model;
   const int n = m.n, nn = m.nn, E = m.E;
   auto T = tree_view_of<BS>(P, smem_raw, t, std::integral_constant<bool, ST>());
   const int QC = ST ? P.sm.Q : 4;      // tally cells per epoch
@@ -755,12 +813,13 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
 
   // the row's tally schedule is the same for every particle: one copy per block in shared memory
   __shared__ int s_ks[SMC_MAX_EPOCHS], s_ksl[SMC_MAX_EPOCHS], s_kn[SMC_MAX_EPOCHS];
-  __shared__ double s_ubf[SMC_MAX_EPOCHS];
+  __shared__ double s_ubf[SMC_MAX_EPOCHS], s_ubf2[SMC_MAX_EPOCHS];
   if (mode == 0) {
     for (int e = t; e < E; e += BS) {
       const int k0 = P.kstart[row * E + e];
       s_ks[e] = k0; s_ksl[e] = P.kslot[row * E + e]; s_kn[e] = P.kstart[(row + 1) * E + e];
       s_ubf[e] = P.ub[P.ub_off[e] + k0];
+      s_ubf2[e] = s_ubf[e] < DBL_MAX ? P.ub[P.ub_off[e] + k0 + 1] : s_ubf[e];      // the last bound of an epoch is +inf
     }
   }
   __syncthreads();   // also: the slot list shares its storage with the accumulators phase 2 is about to zero
@@ -777,7 +836,11 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     for (int k = 0; k < n; k++) data[k] = P.alleles[row * n + k];
     Rng r;
     rng_init(r, P.seed, P.slot_offset + (uint32_t)i, (uint32_t)row, P.chunk, RNG_EXTEND);
-    RingSink<BS, ST> sink{&P, dst.open, (int)i, s_ks, s_ksl, s_kn, T.ACC, t, s_ubf, 0ull};
+    int nmiss_row = 0;
+    for (int k = 0; k < n; k++) nmiss_row += data[k] == -1;
+    // ACC2 shares the pruning scratch: free during the row unless branch_length_with_data runs (partly missing data)
+    RingSink<BS, ST> sink{&P, dst.open, (int)i, s_ks, s_ksl, s_kn, T.ACC, t, s_ubf, 0ull, s_ubf2,
+                          (nmiss_row == 0 || nmiss_row == n) ? T.ACC2 : nullptr};
     const size_t tree_bytes = ST ? stree_bytes_per_thread(nn, E, P.sm.K) : tree_bytes_per_thread(nn, E);
     const MoveSmem ms = make_move_smem<BS>(smem_raw + (((size_t)BS * tree_bytes + 15) & ~(size_t)15));
     nrec = extend_row_block<BS>(m, T, r, x0, x1, data, P.is_site[row], P.max_rec[row], sink, logw, next_base, live, ms,
@@ -1407,6 +1470,8 @@ int use_device(int device) {
 size_t tree_smem(int nn, int E, int BS) { return (size_t)BS * smc::tree_bytes_per_thread(nn, E) + 16; }
 size_t stree_smem(int nn, int E, int K, int BS) { return (size_t)BS * smc::stree_bytes_per_thread(nn, E, K) + 16; }
 // the row kernel: the tree columns plus what a particle carries between the rounds of a row (MoveSmem)
+// dynamic shared memory a row kernel may ask for: the 227 KB a block can have minus its static arrays (4 KB bound)
+#define SMC_MAX_DYN_SMEM 228352
 size_t row_smem(int nn, int E, int BS) { return tree_smem(nn, E, BS) + (size_t)BS * smc::move_bytes_per_thread() + 16; }
 size_t srow_smem(int nn, int E, int K, int BS) { return stree_smem(nn, E, K, BS) + (size_t)BS * smc::move_bytes_per_thread() + 16; }
 
@@ -1615,25 +1680,25 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   if (ce != cudaSuccess) { delete e; return fail(SMC_ERR_CUDA, cudaGetErrorString(ce)); }
   cudaEventCreate(&e->ev0); cudaEventCreate(&e->ev1);
   // opt in to the full 227 KB once (the attribute is per function, not per engine)
-  if (e->smem > 230400) { smc_destroy(e); return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has"); }
-  ce = cudaFuncSetAttribute(smc_row_kernel<32, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (e->smem > SMC_MAX_DYN_SMEM) { smc_destroy(e); return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has"); }
+  ce = cudaFuncSetAttribute(smc_row_kernel<32, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
   if (const char* cv = getenv("SMC_CARVEOUT")) {   // tuning knob: shared-memory share of the 256 KB L1/shared array, in percent
     const int pct = atoi(cv);
     if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
     if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   }
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
-  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<32, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<64, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_row_kernel<128, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(smc_init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM);
   if (ce != cudaSuccess) { std::string msg = cudaGetErrorString(ce); smc_destroy(e); return fail(SMC_ERR_CUDA, "shared memory opt-in: " + msg); }
   const size_t N = cfg->N;
   const int n = cfg->n, nn = 2 * n - 1;
@@ -1806,7 +1871,7 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
     const int Q = 2 + 3 * Pp + Pp * Pp;
     size_t smem = srow_smem(nn, E, K, e->BS);
     smem = std::max(smem, (size_t)E * 2 * Q * (e->BS / 32) * sizeof(double) + 16);   // hand-over staging of phase 0
-    if (smem > 230400 || stree_smem(nn, E, K, AUX_BS) > 230400)
+    if (smem > SMC_MAX_DYN_SMEM || stree_smem(nn, E, K, AUX_BS) > SMC_MAX_DYN_SMEM)
       return fail(SMC_ERR_ARG, "n, E and max_marks need more shared memory than one SM has (fewer particles per block: SMC_BLOCK=32)");
     double *d_inv, *d_mig, *d_tot, *d_single, *d_vbc, *d_vbm; unsigned char* d_fixed; signed char* d_leaf;
     if ((rc = dev_alloc(e, &d_vbc, h_inv.size(), false)) || (rc = dev_alloc(e, &d_vbm, h_mig.size(), false))) return rc;
@@ -2163,10 +2228,17 @@ int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_l
   return 0;
 }
 
+#ifdef SMC_CLOCKS
+static void clocks_print();
+#endif
 int smc_finish(smc_engine* e) {
   if (!e) return fail(SMC_ERR_ARG, "null engine");
   if (!e->inited) return fail(SMC_ERR_STATE, "particles not initialised");
   if (e->finished) return 0;
+#ifdef SMC_CLOCKS
+  cudaDeviceSynchronize();
+  clocks_print();
+#endif
   if (e->swept != e->P.R) return fail(SMC_ERR_STATE, "finish before the last row was swept");
   CUDA_TRY(cudaSetDevice(e->cfg.device));
   // buckets the regular schedule still owes for the last row are folded into the flush: both use the final weights
@@ -2369,7 +2441,7 @@ int tree_fn(int device, int n, int64_t count, const int32_t* parent, const doubl
   CUDA_TRY(cudaMemcpy(dh.p, height, count * nn * sizeof(double), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(da.p, alleles, count * n, cudaMemcpyHostToDevice));
   size_t smem = tree_smem(nn, 1, BS);
-  CUDA_TRY(cudaFuncSetAttribute(k_tree_functions, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+  CUDA_TRY(cudaFuncSetAttribute(k_tree_functions, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM));
   k_tree_functions<<<(unsigned)((count + BS - 1) / BS), BS, smem>>>(m, count, (const int*)dp.p, (const double*)dh.p,
                                                                    (const signed char*)da.p, what, (double*)d0.p, (double*)d1.p);
   CUDA_TRY(cudaGetLastError());
@@ -2517,15 +2589,15 @@ static int calibrate_impl(int device, int32_t n, int32_t E, const double* t_star
     sm.leaf_pop = (const signed char*)t_leaf.p;
     sm.vb_coal = nullptr; sm.vb_mig = nullptr;
     smem = stree_smem(m.nn, E, sm.K, BS);
-    if (smem > 230400) { sm.K = 2 * n + 8; smem = stree_smem(m.nn, E, sm.K, BS); }
-    if (smem > 230400) return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has");
-    CUDA_TRY(cudaFuncSetAttribute(k_survival<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
-    CUDA_TRY(cudaFuncSetAttribute(k_terminal<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+    if (smem > SMC_MAX_DYN_SMEM) { sm.K = 2 * n + 8; smem = stree_smem(m.nn, E, sm.K, BS); }
+    if (smem > SMC_MAX_DYN_SMEM) return fail(SMC_ERR_ARG, "n and E need more shared memory than one SM has");
+    CUDA_TRY(cudaFuncSetAttribute(k_survival<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM));
+    CUDA_TRY(cudaFuncSetAttribute(k_terminal<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM));
     if (terminal) k_terminal<true><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (double*)de.p, (int*)df.p);
     else k_survival<true><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
   } else {
-    CUDA_TRY(cudaFuncSetAttribute(k_survival<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
-    CUDA_TRY(cudaFuncSetAttribute(k_terminal<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 230400));
+    CUDA_TRY(cudaFuncSetAttribute(k_survival<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM));
+    CUDA_TRY(cudaFuncSetAttribute(k_terminal<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMC_MAX_DYN_SMEM));
     if (terminal) k_terminal<false><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (double*)de.p, (int*)df.p);
     else k_survival<false><<<(unsigned)((n_args + BS - 1) / BS), BS, smem>>>(m, sm, n_args, seed, (double*)dd.p, (int*)de.p, (int*)df.p);
   }
@@ -2671,7 +2743,57 @@ extern "C" int smc_terminal_branch_quantiles(int device, int32_t n, int32_t E, c
                         nullptr, nullptr, nq, quantiles, lengths, mean_total_length);
 }
 
+// ---- measurement helper: the fp64 FMA rate of the device (bench.py reports the row kernel against it) -------------------
+namespace {
+__global__ void __launch_bounds__(256) k_dfma_probe(double* out, int iters, double a, double b) {
+  // eight independent chains per thread: enough to cover the DFMA latency at 8 resident warps per scheduler
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+    x0 = __fma_rn(x0, a, b); x1 = __fma_rn(x1, a, b); x2 = __fma_rn(x2, a, b); x3 = __fma_rn(x3, a, b);
+    x4 = __fma_rn(x4, a, b); x5 = __fma_rn(x5, a, b); x6 = __fma_rn(x6, a, b); x7 = __fma_rn(x7, a, b);
+  }
+  const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (s == 12345.678) out[0] = s;      // never true: keeps the chains alive
+}
+}  // namespace
+
+extern "C" int smc_measure_fp64_fma(int device, double* tflops) {
+  if (!tflops) return fail(SMC_ERR_ARG, "null argument");
+  int rc = use_device(device);
+  if (rc) return rc;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  double* d = nullptr;
+  CUDA_TRY(cudaMalloc(&d, sizeof(double)));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int blocks = prop.multiProcessorCount * 8, iters = 1 << 15;
+  k_dfma_probe<<<blocks, 256>>>(d, 1 << 10, 0.999999, 1e-9);           // warm-up
+  cudaEventRecord(e0);
+  k_dfma_probe<<<blocks, 256>>>(d, iters, 0.999999, 1e-9);
+  cudaEventRecord(e1);
+  cudaError_t ce = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  if (ce != cudaSuccess) return fail(SMC_ERR_CUDA, cudaGetErrorString(ce));
+  *tflops = 2.0 * 8.0 * (double)iters * 256.0 * (double)blocks / ((double)ms * 1e-3) * 1e-12;
+  return 0;
+}
+
 #ifdef SMC_CLOCKS
+// SMC_CLOCKS_PRINT=1: every smc_finish prints the accumulated per-phase cycles (tools/struct_time.sh with the clk build)
+static void clocks_print() {
+  if (!getenv("SMC_CLOCKS_PRINT")) return;
+  unsigned long long v[16];
+  if (cudaMemcpyFromSymbol(v, smc::g_clk, sizeof(v)) != cudaSuccess) return;
+  const double blocks = (double)v[10], tot = (double)(v[0] + v[1] + v[2] + v[6]);
+  fprintf(stderr, "[clk] blocks %.0f cycles/block %.0f rounds/block %.2f tasks/round %.1f cycles/round %.0f\n", blocks, tot / blocks,
+          v[8] / blocks, (double)v[9] / (double)(v[8] ? v[8] : 1), (double)v[4] / (double)(v[8] ? v[8] : 1));
+  const char* nm[16] = {"phase0 due tallies", "phase1 load/pull", "phase2 total", " first stretch", " move rounds", " flush+site lik",
+                        "phase3 store+partials", "", "", "", "", "  move", "  tree length", "  next base+factor", "  rec opp", ""};
+  for (int k : {0, 1, 2, 3, 4, 11, 12, 13, 14, 5, 6}) fprintf(stderr, "[clk] %-24s %10.0f cycles/block %5.1f %%\n", nm[k], v[k] / blocks, 100.0 * v[k] / tot);
+}
 extern "C" int smc_debug_clocks(unsigned long long out[16], int reset) {
   CUDA_TRY(cudaMemcpyFromSymbol(out, smc::g_clk, sizeof(unsigned long long) * 16));
   if (reset) { unsigned long long z[16] = {0}; CUDA_TRY(cudaMemcpyToSymbol(smc::g_clk, z, sizeof(z))); }

@@ -82,7 +82,8 @@ __device__ __forceinline__ STreeViewT<BS> make_stree_view(unsigned char* smem, i
   T.H = base - (size_t)n * BS;
   T.L0 = base + in - (size_t)n * BS;
   T.L1 = base + 2 * in - (size_t)n * BS;
-  T.ACC = base + 3 * in;
+  T.ACC2 = base + in;
+  T.ACC = base + in + tree_scratch_rows(nn, E) * BS;
   T.MT = T.ACC + (size_t)E * BS;
   T.PAR = reinterpret_cast<signed char*>(T.MT + (size_t)K * BS);
   T.POP = T.PAR + (size_t)nn * BS;
@@ -159,6 +160,7 @@ __device__ inline void s_fixed_time_events(const ModelDev& m, const TV& T, int e
 struct SNullSink {
   __device__ void scoal(int, int, double, int, double) const {}
   __device__ void smig(int, int, double, int, double) const {}
+  __device__ void srec(int, int, double, int, double, int, double) const {}
 };
 
 // The sweep of a floating lineage that starts at (t0, pop0) over the tree made of the nodes in `present`
@@ -181,18 +183,24 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
     const int nm0 = T.nm();
     for (int q = 0; q < nm0; q++) { const int mb = T.mb(q); if (mb >= 0) marked |= 1ull << mb; }
   }
+  // The internal slots in use are height-sorted and contiguous from n (s_rotate keeps them so while the prior tree
+  // grows): c = first slot above tt.  A branch v -> p is alive at tt exactly when v is a present leaf or a slot below c
+  // and p >= c, and the next node above tt is slot c -- no height is compared inside the scans.
+  int used = n;
+  while (used < nn && ((present >> used) & 1ull)) used++;
+  const unsigned long long leaves = present & ((1ull << n) - 1ull);
+  int c = n;
   for (;;) {
     const bool above = !(tt < hroot);
     int k = 0;
     double tend = e + 1 < m.E ? m.t_start[e + 1] : DBL_MAX;
     const double tep = tend;
     if (!above) {
-      for (int v = 0; v < nn; v++) {
-        if (!((present >> v) & 1ull)) continue;
-        double hv = T.h(v);
-        if (v >= n && hv > tt && hv < tend) tend = hv;
-        int p = T.par(v);
-        if (p >= 0 && hv <= tt && tt < T.h(p) && (((marked >> v) & 1ull) ? s_pop_at(T, v, tt) : (int)T.pop(v)) == pf) k++;
+      while (c < used && T.h(c) <= tt) c++;
+      if (c < used) { const double hc = T.h(c); if (hc < tend) tend = hc; }
+      for (int v = 0; v < c; v++) {
+        if (v < n && !((leaves >> v) & 1ull)) continue;
+        if (T.par(v) >= c && (((marked >> v) & 1ull) ? s_pop_at(T, v, tt) : (int)T.pop(v)) == pf) k++;
       }
       const int nm = T.nm();
       for (int q = 0; q < nm; q++) { double mt = T.mt(q); if (mt > tt && mt < tend) tend = mt; }
@@ -227,8 +235,7 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
     if ((m.rec_mask[e] & 2) && e <= max_rec_epoch) {     // particle.cpp:251-300
       const double dt = tev - tt;
       const int weight = k + (pw > 0.0 ? 1 : 0);
-      sink.scoal(e, pf, x, ev_f == 1, weight * dt);
-      sink.smig(e, pf, x, ev_f == 2 ? to_f : -1, dt);
+      sink.srec(e, pf, x, ev_f == 1, weight * dt, ev_f == 2 ? to_f : -1, dt);
       if (above) sink.smig(e, pr, x, ev_r == 2 ? to_r : -1, dt);
     }
     const double ts = tt;                                // start of the interval: where the contemporaries were counted
@@ -239,11 +246,9 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
         if (above) { target = -1; return tt; }
         int idx = (int)(rng_uniform(r) * k);
         if (idx >= k) idx = k - 1;
-        for (int v = 0; v < nn; v++) {
-          if (!((present >> v) & 1ull)) continue;
-          int p = T.par(v);
-          if (p < 0) continue;
-          if (T.h(v) <= ts && ts < T.h(p) && (((marked >> v) & 1ull) ? s_pop_at(T, v, ts) : (int)T.pop(v)) == pf) { if (idx == 0) { target = v; return tt; } idx--; }
+        for (int v = 0; v < c; v++) {                     // c still is the first slot above ts
+          if (v < n && !((leaves >> v) & 1ull)) continue;
+          if (T.par(v) >= c && (((marked >> v) & 1ull) ? s_pop_at(T, v, ts) : (int)T.pop(v)) == pf) { if (idx == 0) { target = v; return tt; } idx--; }
         }
         target = -2;                                     // cannot happen
         return tt;

@@ -266,6 +266,13 @@ def calibrate_survival_struct(n, t_start, inv2N, mig, single_mig, leaf_pop, rho,
     return med, cnt
 
 
+def measure_fp64_fma(device=0):
+    """sustained fp64 FMA rate of the device in TFLOP/s (register-only probe kernel)"""
+    v = ctypes.c_double()
+    check(lib().smc_measure_fp64_fma(device, ctypes.byref(v)))
+    return v.value
+
+
 def terminal_branch_quantiles(n, t_start, inv2N, quantiles=(0.001, 0.003, 0.01, 0.03, 0.1, 0.5, 0.95), n_trees=1000000, seed=1,
                               mig=None, single_mig=None, leaf_pop=None, device=0):
     """calculate_terminal_branch_length_quantiles (smcsmc.cpp:128): (lengths[n][len(quantiles)], mean tree length) from

@@ -78,7 +78,8 @@ def main():
             pf.finish()
         parent, height, logw, nb = pf.particles()
         mine = dict(parent=parent, height=height, logw=logw, nb=nb, lnZ=pf.ln_normalization_factor(),
-                    tallies=pf.tallies(), counters=pf.counters(), rs=pf.resample_log(), anc=pf.last_ancestry())
+                    tallies=pf.tallies(), counters=pf.counters(), rs=pf.resample_log(), anc=pf.last_ancestry(),
+                    row_opp=pf.row_opportunity())
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
         pf.close()
@@ -104,6 +105,7 @@ def main():
                 assert g["counters"]["err"] == 0
                 assert abs(g["lnZ"] - one.ln_normalization_factor()) <= 1e-9 * abs(one.ln_normalization_factor())
                 np.testing.assert_allclose(g["tallies"], one.tallies(), rtol=1e-8, atol=1e-12)
+                np.testing.assert_allclose(g["row_opp"], one.row_opportunity(), rtol=1e-9, atol=0)
                 assert np.array_equal(g["rs"][0], one.resample_log()[0])
                 np.testing.assert_allclose(g["rs"][1], one.resample_log()[1], rtol=1e-9)
             assert np.array_equal(np.concatenate([g["parent"] for g in gathered]), p1)
