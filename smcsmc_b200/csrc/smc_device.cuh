@@ -523,75 +523,68 @@ __device__ inline int extend_row_block(const ModelDev& m, const TV& T, Rng& r, d
   for (int i = 0; i < n; i++) nmiss += data[i] == -1;
   const int leaf_status = nmiss == 0 ? 1 : (nmiss == n ? -1 : 0);   // particleContainer.cpp:103-111
   int nrec = 0;
-  bool pending = false;
 #ifdef SMC_CLOCKS
   long long clk = clock64();
 #endif
   if (live) {
     sink.row_begin(x1);
-    const double tl = tree_length(m, T);
-    const double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, T, data);
-    const double new_to = x1 < next_base ? x1 : next_base;
-    double area = 0.0;
-    if (x0 < x1) {
-      logw += dlog(fastexp(-m.mu * L_obs * (new_to - x0)));     // particle.cpp:770
-      record_recomb_opportunity(m, T, sink, x0, new_to, max_rec_epoch);
-      area = tl * (new_to - x0);
-    }
-    pending = new_to < x1;
-    ms.X[t] = next_base; ms.LOGW[t] = logw; ms.TL[t] = tl; ms.AREA[t] = area;
+    ms.X[t] = next_base; ms.LOGW[t] = logw; ms.TL[t] = 0.0; ms.AREA[t] = 0.0;
     ms.CTR[t] = r.c0; ms.SPARE[t] = r.spare; ms.HAVE[t] = (unsigned char)r.have;
   }
-  unsigned bal = __ballot_sync(0xffffffffu, pending);
-  if (lane == 0) wcnt[warp] = __popc(bal);
-  __syncthreads();
-  int total = 0, off = 0;
-  for (int w = 0; w < nwarp; w++) { const int c = wcnt[w]; if (w < warp) off += c; total += c; }
-  if (pending) ms.LIST[off + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)t;
-  int cur = 0;
-  SMC_CLK(3, clk);                     // first stretch
+  // Round 0 is the stretch up to the particle's first recombination (every thread its own particle, no move); the
+  // rounds after it run the compacted list of particles that owe a move.  One body serves both: the kernel is bound by
+  // instruction fetch, a second copy of the stretch code costs more than the `first` tests.
+  bool first = true;
+  int total = BS, cur = 0;
   while (total > 0) {                  // uniform over the block
-    __syncthreads();                   // the list of this round is complete
+    __syncthreads();                   // the list of this round is complete (round 0: the columns above are written)
 #ifdef SMC_CLOCKS
-    if (threadIdx.x == 0) { atomicAdd(&g_clk[8], 1ull); atomicAdd(&g_clk[9], (unsigned long long)total); }
+    if (threadIdx.x == 0 && !first) { atomicAdd(&g_clk[8], 1ull); atomicAdd(&g_clk[9], (unsigned long long)total); }
 #endif
     bool again = false;
-    int tp = 0;
-    if (t < total) {
-      tp = ms.LIST[cur * BS + t];
+    int tp = t;
+    if (first ? live : t < total) {
+      if (!first) tp = ms.LIST[cur * BS + t];
       TV Tp = T; Tp.t = tp;
       Sink sp = sink; sp.t = tp; sp.i = sink.i - t + tp;
       Rng rp = r;
       rp.c1 = r.c1 - (uint32_t)t + (uint32_t)tp; rp.c0 = ms.CTR[tp]; rp.spare = ms.SPARE[tp]; rp.have = ms.HAVE[tp];
       double lw = ms.LOGW[tp];
-      const double x = ms.X[tp];
+      const double x = first ? x0 : ms.X[tp];          // where the stretch starts
 #ifdef SMC_CLOCKS
       long long clk2 = clock64();
 #endif
-      smc_move(m, Tp, rp, x, max_rec_epoch, sp, lw, ms.TL[tp]);
+      if (!first) {
+        smc_move(m, Tp, rp, x, max_rec_epoch, sp, lw, ms.TL[tp]);
+        nrec++;
+      }
       SMC_CLK(11, clk2);               // the move
-      nrec++;
       const double tl = tree_length(m, Tp);
       const double L_obs = leaf_status == -1 ? 0.0 : leaf_status == 1 ? tl : branch_length_with_data(m, Tp, data);
       SMC_CLK(12, clk2);               // tree length, observed length
-      const double nb = draw_next_base(m, tl, rp, x);
+      const double nb = first ? ms.X[tp] : draw_next_base(m, tl, rp, x);
       const double new_to = x1 < nb ? x1 : nb;
-      lw += dlog(fastexp(-m.mu * L_obs * (new_to - x)));
-      SMC_CLK(13, clk2);               // next base, no-mutation factor
-      record_recomb_opportunity(m, Tp, sp, x, new_to, max_rec_epoch);
-      SMC_CLK(14, clk2);               // recombination opportunity of the stretch
+      if (x < x1) {                    // a row of zero length (two typed sites at one position) has no stretch
+        lw += dlog(fastexp(-m.mu * L_obs * (new_to - x)));     // particle.cpp:770
+        SMC_CLK(13, clk2);             // next base, no-mutation factor
+        record_recomb_opportunity(m, Tp, sp, x, new_to, max_rec_epoch);
+        SMC_CLK(14, clk2);             // recombination opportunity of the stretch
+        ms.AREA[tp] += tl * (new_to - x);
+      }
       again = new_to < x1;
-      ms.X[tp] = nb; ms.LOGW[tp] = lw; ms.TL[tp] = tl; ms.AREA[tp] += tl * (new_to - x);
+      ms.X[tp] = nb; ms.LOGW[tp] = lw; ms.TL[tp] = tl;
       ms.CTR[tp] = rp.c0; ms.SPARE[tp] = rp.spare; ms.HAVE[tp] = (unsigned char)rp.have;
     }
-    bal = __ballot_sync(0xffffffffu, again);
+    const unsigned bal = __ballot_sync(0xffffffffu, again);
     if (lane == 0) wcnt[(cur ^ 1) * nwarp + warp] = __popc(bal);
     __syncthreads();                   // counts of the next round are visible, every read of this round's list is done
-    total = 0; off = 0;
+    total = 0;
+    int off = 0;
     for (int w = 0; w < nwarp; w++) { const int c = wcnt[(cur ^ 1) * nwarp + w]; if (w < warp) off += c; total += c; }
     if (again) ms.LIST[(cur ^ 1) * BS + off + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)tp;
     cur ^= 1;
-    SMC_CLK(4, clk);                   // move rounds
+    if (first) SMC_CLK(3, clk); else SMC_CLK(4, clk);   // first stretch / move rounds
+    first = false;
   }
   __syncthreads();                     // the last round's results are visible to their owners
   if (live) {

@@ -2792,6 +2792,8 @@ static void clocks_print() {
           v[8] / blocks, (double)v[9] / (double)(v[8] ? v[8] : 1), (double)v[4] / (double)(v[8] ? v[8] : 1));
   const char* nm[16] = {"phase0 due tallies", "phase1 load/pull", "phase2 total", " first stretch", " move rounds", " flush+site lik",
                         "phase3 store+partials", "", "", "", "", "  move", "  tree length", "  next base+factor", "  rec opp", ""};
+  fprintf(stderr, "[clk] structured: float %.0f cycles/block (%.1f %%), %.2f intervals per round-0-thread float, %.0f cycles per interval\n",
+          v[7] / blocks, 100.0 * v[7] / tot, (double)v[15] / (double)(v[8] ? v[8] : 1), (double)v[7] / (double)(v[15] ? v[15] : 1));
   for (int k : {0, 1, 2, 3, 4, 11, 12, 13, 14, 5, 6}) fprintf(stderr, "[clk] %-24s %10.0f cycles/block %5.1f %%\n", nm[k], v[k] / blocks, 100.0 * v[k] / tot);
 }
 extern "C" int smc_debug_clocks(unsigned long long out[16], int reset) {

@@ -186,6 +186,7 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
   // The internal slots in use are height-sorted and contiguous from n (s_rotate keeps them so while the prior tree
   // grows): c = first slot above tt.  A branch v -> p is alive at tt exactly when v is a present leaf or a slot below c
   // and p >= c, and the next node above tt is slot c -- no height is compared inside the scans.
+  double a_opp = 0.0, a_dt = 0.0, r_dt = 0.0;          // records not yet written: floating lineage (e, pf), root lineage (e, pr)
   int used = n;
   while (used < nn && ((present >> used) & 1ull)) used++;
   const unsigned long long leaves = present & ((1ull << n) - 1ull);
@@ -205,6 +206,9 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
       const int nm = T.nm();
       for (int q = 0; q < nm; q++) { double mt = T.mt(q); if (mt > tt && mt < tend) tend = mt; }
     }
+#ifdef SMC_CLOCKS
+    if (threadIdx.x == 0 && vb_logw) atomicAdd(&g_clk[15], 1ull);      // intervals of thread 0's floats
+#endif
     const double inv = s.inv2N[e * P + pf];
     const double coal_rate = above ? 0.0 : k * inv;
     const double mig_f = s.migtot[e * P + pf];
@@ -233,10 +237,19 @@ __device__ inline double s_float(const ModelDev& m, const TV& T, unsigned long l
       if (ev_r == 2) *vb_logw += s.vb_mig[(e * P + pr) * P + to_r];
     }
     if ((m.rec_mask[e] & 2) && e <= max_rec_epoch) {     // particle.cpp:251-300
+      // Consecutive intervals of one lineage in one (epoch, population) add to the same cells: they are summed in
+      // registers and written when an event has to be recorded with them or the epoch changes -- a float that crosses
+      // ten nodes makes one round trip to its cells, not ten.
       const double dt = tev - tt;
       const int weight = k + (pw > 0.0 ? 1 : 0);
-      sink.srec(e, pf, x, ev_f == 1, weight * dt, ev_f == 2 ? to_f : -1, dt);
-      if (above) sink.smig(e, pr, x, ev_r == 2 ? to_r : -1, dt);
+      a_opp += weight * dt;
+      a_dt += dt;
+      if (above) r_dt += dt;
+      if (hit || tend == tep) {
+        sink.srec(e, pf, x, ev_f == 1, a_opp, ev_f == 2 ? to_f : -1, a_dt);
+        if (r_dt > 0.0 || ev_r == 2) sink.smig(e, pr, x, ev_r == 2 ? to_r : -1, r_dt);
+        a_opp = 0.0; a_dt = 0.0; r_dt = 0.0;
+      }
     }
     const double ts = tt;                                // start of the interval: where the contemporaries were counted
     tt = tev;
@@ -357,7 +370,11 @@ __device__ inline void smc_move(const ModelDev& m, const STreeViewT<BS>& T, Rng&
   // 2. float
   int target = -1, cpop = 0;
   const unsigned long long all = nn >= 64 ? ~0ull : ((1ull << nn) - 1ull);
+#ifdef SMC_CLOCKS
+  long long clk3 = clock64();
+#endif
   const double tc = s_float(m, T, all, root, r, hh, s_pop_at(T, b, hh), target, cpop, sink, x, max_rec_epoch, &logw);
+  SMC_CLK(7, clk3);                                    // the float alone
   if (target <= -2) return;
   // 3. surgery.  The stub of b above the cut disappears unless the lineage coalesces back into it.
   if (target == b) {
