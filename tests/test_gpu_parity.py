@@ -495,3 +495,10 @@ def test_terminal_branch_quantiles_vs_reference_prior_trees(S):
     with pytest.raises(S.SmcError):
         S.terminal_branch_quantiles(8, t, inv, quantiles=[1.5], n_trees=1000)
 
+
+
+def test_fp64_fma_probe(S):
+    """smc_measure_fp64_fma (bench.py's fp64 denominator): a B200 sustains 30-40 TFLOP/s of DFMA; a value far outside
+    means the probe kernel was optimised away or the clocks are capped"""
+    v = S.measure_fp64_fma()
+    assert 5.0 < v < 100.0, v
