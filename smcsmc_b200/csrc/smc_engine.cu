@@ -65,6 +65,8 @@ struct Ctrl {
   double resample_pos;      // row end at which the resampling was decided (offspring re-draw from here)
   long long resample_row;
   long long cons_done;      // row whose leading tally consumption has already been done (by a materialise pass)
+  int pool_c0, pool_c1;     // range of P.cons whose descendants' weights sit pooled in P.pool[pool_par] and still owe their
+  int pool_par;             // second-moment tallies (the launch after the one that pooled them adds those)
   unsigned int ticket;
   int err;
   int sflags;               // SFLAG_* raised by any particle (structured populations)
@@ -124,6 +126,10 @@ struct Params {
   double* bscale[2];
   double* psum;            // [N+1] parity-mode sequential partial sums
   double* tallies;         // [6][E]; structured: [2][Q][E] (sum of w * cell, sum of w^2 * cell)
+  double* pool;            // [2][E][N] weight of the current particles pooled per ancestor slot (see phase 0), by parity
+  int pool_on;             // 0: per-particle w^2 (tuning knob SMC_NO_POOL; sharded populations)
+  double* pool2;           // [E][QW][N] per slot: sum of pool^2 * cell over the buckets whose record the slot owned (QW = 2
+                           // opportunity cells, or all Q cells with populations); smc_finish adds it up into the tallies
   int* anc;                // [N] ancestry of the last resampling (global particle index when sharded)
   double* rs_pos; double* rs_ess; long long rs_cap;
   // particle sharding over ranks: this engine owns particles [base, base + N) of Ntot.  What a
@@ -146,7 +152,7 @@ __device__ __forceinline__ Tp* at_peer(Tp* p, long long delta) {
 
 // the frozen record (4 doubles) of closed bucket (e, slot s) that belongs to particle i's ancestor
 template <bool SH>
-__device__ __forceinline__ void load_frozen(const Params& P, const int* map, int e, int s, long long i, double out[4]) {
+__device__ __forceinline__ int load_frozen(const Params& P, const int* map, int e, int s, long long i, double out[4]) {
   const size_t es = (size_t)(e * P.B + s);
   const int m = map[es * P.N + i];
   const double* f = P.frozen;
@@ -155,6 +161,7 @@ __device__ __forceinline__ void load_frozen(const Params& P, const int* map, int
   const double2* c2 = reinterpret_cast<const double2*>(f + (es * P.N + l) * 4);
   double2 a = c2[0], b = c2[1];
   out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
+  return m;
 }
 
 // Tally sink.  Records of the bucket that stays open beyond this row go to the particle's `open` cells, records of
@@ -312,7 +319,33 @@ __device__ __forceinline__ double warp_max(double v) {
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
-
+// pool[key] += w, once per run of equal keys in the warp (segmented inclusive scan; the run's last lane adds).  Keys are
+// ancestor slots: systematic resampling keeps the particles' order, so the descendants of one slot are neighbours and a
+// slot with thousands of descendants costs a few atomics per warp instead of thousands on one address.  key < 0: no part.
+__device__ __noinline__ void pool_add_runs(double* pool, int key, double w) {
+  const int lane = threadIdx.x & 31;
+  for (int d = 1; d < 32; d <<= 1) {
+    const double ow = __shfl_up_sync(0xffffffffu, w, d);
+    const int ok = __shfl_up_sync(0xffffffffu, key, d);
+    if (lane >= d && ok == key) w += ow;
+  }
+  const int nk = __shfl_down_sync(0xffffffffu, key, 1);
+  if (key >= 0 && (lane == 31 || nk != key) && w != 0.0) atomicAdd(pool + key, w);
+}
+__device__ __forceinline__ void pool_add(double* pool, int key, double w) {
+  const int key0 = __shfl_sync(0xffffffffu, key, 0);
+  if (__all_sync(0xffffffffu, key == key0)) {          // the whole warp descends from one slot (the usual case at depth)
+    w = warp_sum(w);
+    if ((threadIdx.x & 31) == 0 && key >= 0 && w != 0.0) atomicAdd(pool + key, w);
+    return;
+  }
+  const int pk = __shfl_up_sync(0xffffffffu, key, 1);
+  if (__all_sync(0xffffffffu, (threadIdx.x & 31) == 0 || pk != key)) {   // no two neighbours share a slot (shallow buckets)
+    if (key >= 0 && w != 0.0) atomicAdd(pool + key, w);
+    return;
+  }
+  pool_add_runs(pool, key, w);                         // out of line: the row kernel is bound by instruction fetch
+}
 // normalised cumulative weight c_i = P_{i+1} (un-divided) of particle i after row parity p
 __device__ __forceinline__ double cum_at(const Params& P, int p, long long i, int bs) {
   if (P.parity_scan) return P.psum[i + 1];
@@ -559,12 +592,77 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
   const bool tail = mode == 1 && row >= P.R;
   int c0 = 0, c1 = 0;
   if (row > 0 && c->cons_done != row && !tail) { c0 = P.cons_off[row - 1]; c1 = P.cons_off[row]; }
+  // Second moments (the *_weight tallies behind the ESS column of .out, count.cpp:519-526): the reference squares the
+  // weight POOLED over the particles that share a record.  Particles share a closed bucket's record exactly when their
+  // map entries are equal, so the launch that consumes a bucket pools the weights per ancestor slot (pool_add) and the
+  // NEXT launch -- when every block's contribution has landed -- lets the owner of each slot add pool^2 * opportunity
+  // to its own running sums (pool2: plain read-modify-writes, no shuffles or atomics; a warp reduction and an atomic per
+  // bucket cost 5 % of the sweep) and clear the pool; smc_finish adds the running sums into the tallies.
+  // Two pools by parity, the ring keeps a consumed bucket one launch longer (smc_upload_rows).
+  // Not pooled: what siblings born while the bucket was still open share of it (they carry it by value), the bucket
+  // open at the end of the data, and sharded populations (per-particle w^2, a lower bound).
+  const int pc0 = c->pool_c0, pc1 = c->pool_c1, ppar = c->pool_par;
+  const bool pooling = !SH && P.pool_on;
+  if (pooling && pc1 > pc0) {
+    const int QW = ST ? QC : 2;
+    for (int q0 = pc0; q0 < pc1; q0 += 4) {
+      // the pool values of four buckets are loaded together (each wait would otherwise be a round trip to L2)
+      double pw4[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        pw4[j] = (live && q0 + j < pc1) ? P.pool[((size_t)ppar * E + P.cons[q0 + j].x) * P.N + i] : 0.0;
+      if constexpr (ST) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const double pw = pw4[j];
+          if (pw == 0.0) continue;         // few slots have descendants left by the time a bucket falls due
+          const int2 ek = P.cons[q0 + j];
+          P.pool[((size_t)ppar * E + ek.x) * P.N + i] = 0.0;
+          const double* fr = P.frozen + ((size_t)(ek.x * P.B + ek.y % P.B) * P.N + i) * QC;
+          double* s2 = P.pool2 + (size_t)ek.x * QW * P.N + i;
+          for (int a = 0; a < QW; a++) s2[(size_t)a * P.N] += pw * pw * fr[a];
+        }
+      } else {
+        // one population: cells 1 and 3 (the opportunities).  All loads of the four buckets first, then the stores: done
+        // one bucket after the other, each read-modify-write waited out its own round trip (4 % of the sweep)
+        double f1[4], f3[4], a1[4], a3[4];
+        double* s2[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          f1[j] = f3[j] = a1[j] = a3[j] = 0.0;
+          s2[j] = nullptr;
+          if (pw4[j] != 0.0) {
+            const int2 ek = P.cons[q0 + j];
+            const double2* fr = reinterpret_cast<const double2*>(P.frozen + ((size_t)(ek.x * P.B + ek.y % P.B) * P.N + i) * 4);
+            s2[j] = P.pool2 + (size_t)ek.x * 2 * P.N + i;
+            f1[j] = fr[0].y; f3[j] = fr[1].y;
+            a1[j] = s2[j][0]; a3[j] = s2[j][P.N];
+            P.pool[((size_t)ppar * E + ek.x) * P.N + i] = 0.0;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          if (pw4[j] != 0.0) {
+            s2[j][0] = a1[j] + pw4[j] * pw4[j] * f1[j];
+            s2[j][P.N] = a3[j] + pw4[j] * pw4[j] * f3[j];
+          }
+      }
+    }
+  }
   if (c1 > c0) {
     // at most one bucket per epoch falls due per row; the per-warp sums of all of them are staged in the (still
     // unused) tree area and handed to the global tallies with one pass
     double* scr = reinterpret_cast<double*>(smem_raw);           // [c1 - c0][6][nwarp]  (structured: [..][2Q][nwarp])
     const double w = live ? dexp(src.logw[i] - lse) : 0.0;
-    const double w2 = w * w;
+    const double w2 = pooling ? 0.0 : w * w;
+    double* pl = P.pool + (size_t)(ppar ^ 1) * E * P.N;
+    if (pooling && ST) {
+      for (int q = c0; q < c1; q++) {
+        const int2 ek = P.cons[q];
+        const int key = live ? src.map[(size_t)(ek.x * P.B + ek.y % P.B) * P.N + i] : -1;
+        pool_add(pl + (size_t)ek.x * P.N, key, w);
+      }
+    }
     if constexpr (ST) {
       // every cell is summed with w and with w^2: rows [0, QC) and [QC, 2Q) of the tallies
       for (int q = c0; q < c1; q++) {
@@ -589,11 +687,13 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
       for (int q = c0; q < c1; q++) {
         int2 ek = P.cons[q];
         double v[6] = {0, 0, 0, 0, 0, 0};
+        int key = -1;
         if (live) {
           double f[4];
-          load_frozen<SH>(P, src.map, ek.x, ek.y % P.B, i, f);
+          key = load_frozen<SH>(P, src.map, ek.x, ek.y % P.B, i, f);
           v[0] = w * f[0]; v[1] = w * f[1]; v[2] = w2 * f[1]; v[3] = w * f[2]; v[4] = w * f[3]; v[5] = w2 * f[3];
         }
+        if (pooling) pool_add(pl + (size_t)ek.x * P.N, key, w);
 #pragma unroll
         for (int a = 0; a < 6; a++) {
           v[a] = warp_sum(v[a]);
@@ -1019,11 +1119,22 @@ smc_row_kernel(const __grid_constant__ Params P, int mode) {
     P.psum[P.N] = acc;
     norm = acc;
   }
+  if (pooling) {        // what this launch pooled waits for the next one; what it found pooled is booked
+    c->pool_c0 = c0; c->pool_c1 = c1;
+    if (c1 > c0) c->pool_par = ppar ^ 1;
+  }
   commit_row(P, c, row, new_lse, ess, S > 0.0, norm, (long long)P.N);
 }
 
-// commit of a materialise-only pass
-__global__ void smc_commit_kernel(Ctrl* c) {
+// commit of a materialise-only pass (its phase 0 did what a row launch's does: see the pool hand-over there)
+__global__ void smc_commit_kernel(const __grid_constant__ Params P, Ctrl* c) {
+  if (P.world == 1 && P.pool_on) {
+    const long long row = c->row;
+    int c0 = 0, c1 = 0;
+    if (row > 0 && row < P.R && c->cons_done != row) { c0 = P.cons_off[row - 1]; c1 = P.cons_off[row]; }
+    c->pool_c0 = c0; c->pool_c1 = c1;
+    if (c1 > c0) c->pool_par ^= 1;
+  }
   c->cons_done = c->row;
   if (c->resampled) c->cur ^= 1;
   c->resampled = 0;
@@ -1054,7 +1165,9 @@ __global__ void __launch_bounds__(128) smc_flush_kernel(const __grid_constant__ 
           double2 a = o2[0], b = o2[1];
           f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
         }
-        v[0] += w * f[0]; v[1] += w * f[1]; v[2] += w * w * f[1]; v[3] += w * f[2]; v[4] += w * f[3]; v[5] += w * w * f[3];
+        // second moments of closed buckets are pooled per ancestor slot by smc_flush_pool_kernel (one population of one GPU)
+        const double w2 = (P.world > 1 || !P.pool_on || k == nbk - 1) ? w * w : 0.0;
+        v[0] += w * f[0]; v[1] += w * f[1]; v[2] += w2 * f[1]; v[3] += w * f[2]; v[4] += w * f[3]; v[5] += w2 * f[3];
       }
     }
     for (int a = 0; a < 6; a++) { v[a] = warp_sum(v[a]); if (lane == 0) tal[a][warp] = v[a]; }
@@ -1081,13 +1194,15 @@ __global__ void __launch_bounds__(128) smc_flush_struct_kernel(const __grid_cons
   for (int e = 0; e < E; e++) {
     const int nbk = P.ub_off[e + 1] - P.ub_off[e];
     for (int a = 0; a < Q; a++) {
-      double f = 0.0;
-      if (live)
-        for (int k = first_pending[e]; k < nbk; k++)
-          f += k < nbk - 1 ? (P.world > 1 ? frozen_record<true>(P, src.map, e, k % P.B, i, Q)[a]
-                                          : frozen_record<false>(P, src.map, e, k % P.B, i, Q)[a])
-                           : src.open[((size_t)e * P.N + i) * Q + a];
-      const double v0 = warp_sum(w * f), v1 = warp_sum(w * w * f);
+      double f = 0.0, fo = 0.0;
+      if (live) {
+        for (int k = first_pending[e]; k < nbk - 1; k++)
+          f += P.world > 1 ? frozen_record<true>(P, src.map, e, k % P.B, i, Q)[a]
+                           : frozen_record<false>(P, src.map, e, k % P.B, i, Q)[a];
+        fo = src.open[((size_t)e * P.N + i) * Q + a];
+      }
+      // second moments of closed buckets are pooled per ancestor slot by smc_flush_pool_kernel (one GPU)
+      const double v0 = warp_sum(w * (f + fo)), v1 = warp_sum(w * w * ((P.world > 1 || !P.pool_on) ? f + fo : fo));
       if (lane == 0) { tal[0][warp] = v0; tal[1][warp] = v1; }
       __syncthreads();
       if (t < 2) {
@@ -1098,6 +1213,60 @@ __global__ void __launch_bounds__(128) smc_flush_struct_kernel(const __grid_cons
       __syncthreads();
     }
   }
+}
+
+// End of data, second moments of the closed buckets (see phase 0 of the row kernel): pass 0 books what the last row launch
+// left pooled; pass 1 pools the final weights per ancestor slot for bucket first_pending[e] + j of every epoch, pass 2
+// books it (owner of the slot: pool^2 * cell) and clears the pool.  One launch per pass: the launch boundary is the
+// grid-wide barrier between pooling and booking.
+__global__ void __launch_bounds__(128) smc_flush_pool_kernel(const __grid_constant__ Params P, const int* first_pending, int j,
+                                                             int pass) {
+  Ctrl* c = P.ctrl;
+  const int BS = blockDim.x, t = threadIdx.x;
+  const long long i = (long long)blockIdx.x * BS + t;
+  const bool live = i < P.N;
+  const StateBuf& src = P.buf[c->cur];
+  const int E = P.m.E;
+  const bool st = P.sm.P > 1;
+  const int Q = st ? P.sm.Q : 4, QW = st ? Q : 2;
+  const int items = pass == 0 ? c->pool_c1 - c->pool_c0 : E;
+  const double* pool = P.pool + (pass == 0 ? (size_t)c->pool_par * E * P.N : 0);
+  const double w = live && pass == 1 ? exp(src.logw[i] - c->lse) : 0.0;
+  for (int it = 0; it < items; it++) {
+    int e, k;
+    if (pass == 0) { const int2 ek = P.cons[c->pool_c0 + it]; e = ek.x; k = ek.y; }
+    else { e = it; k = first_pending[e] + j; if (k >= P.ub_off[e + 1] - P.ub_off[e] - 1) continue; }
+    const size_t es = (size_t)(e * P.B + k % P.B);
+    double* pp = const_cast<double*>(pool) + (size_t)e * P.N;
+    if (pass == 1) {
+      pool_add(pp, live ? src.map[es * P.N + i] : -1, w);
+      continue;
+    }
+    const double pw = live ? pp[i] : 0.0;
+    if (pw == 0.0) continue;
+    pp[i] = 0.0;
+    const double* fr = P.frozen + (es * P.N + i) * Q;
+    double* s2 = P.pool2 + (size_t)e * QW * P.N + i;
+    for (int a = 0; a < QW; a++) s2[(size_t)a * P.N] += pw * pw * fr[st ? a : 2 * a + 1];
+  }
+}
+
+// the slots' running second-moment sums into the tallies (end of data)
+__global__ void __launch_bounds__(128) smc_pool_reduce_kernel(const __grid_constant__ Params P) {
+  const int BS = blockDim.x, t = threadIdx.x, lane = t & 31;
+  const long long i = (long long)blockIdx.x * BS + t;
+  const bool live = i < P.N;
+  const int E = P.m.E;
+  const bool st = P.sm.P > 1;
+  const int Q = st ? P.sm.Q : 4, QW = st ? Q : 2;
+  for (int e = 0; e < E; e++)
+    for (int a = 0; a < QW; a++) {
+      double* s2 = P.pool2 + ((size_t)e * QW + a) * P.N;
+      double v = live ? s2[i] : 0.0;
+      if (live && v != 0.0) s2[i] = 0.0;
+      v = warp_sum(v);
+      if (lane == 0 && v != 0.0) atomicAdd(P.tallies + (size_t)(st ? Q + a : (a == 0 ? 2 : 5)) * E + e, v);
+    }
 }
 
 // prior trees + first recombination position + weight 1/N (particleContainer.cpp:33-65)
@@ -1353,6 +1522,7 @@ struct smc_engine {
   cudaGraphExec_t row_graph = nullptr;
   bool graph_dirty = true;
   std::vector<int> first_pending_h;     // per epoch: number of buckets the regular schedule consumes
+  size_t pool2_count = 0;               // doubles in P.pool2
   int* first_pending_d = nullptr;
   // particle sharding
   void* state_slab = nullptr;
@@ -1621,7 +1791,7 @@ int launch_rows(smc_engine* e, int64_t count) {
 int materialise(smc_engine* e) {
   int rc = launch_row(e, 1);
   if (rc) return rc;
-  smc_commit_kernel<<<1, 1, 0, e->stream>>>(e->P.ctrl);
+  smc_commit_kernel<<<1, 1, 0, e->stream>>>(e->P, e->P.ctrl);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -1674,6 +1844,7 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   if (const char* s = getenv("SMC_BLOCK")) { int b = atoi(s); if (b == 32 || b == 64 || b == 128) e->BS = b; }   // tuning knob
   P.nblocks = (cfg->N + e->BS - 1) / e->BS;
   e->smem = row_smem(P.m.nn, P.m.E, e->BS);
+  P.pool_on = getenv("SMC_NO_POOL") ? 0 : 1;   // knob: per-particle w^2 in the *_weight tallies (ESS column too high), 4 % faster
   if (getenv("SMC_FLAT_SEARCH")) P.flat_search = 1;   // tests: the one-level parent search the two-level one must reproduce
   if (const char* s = getenv("SMC_EXTRA_SMEM")) e->smem += (size_t)atoi(s);                                       // occupancy experiments
   cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
@@ -1734,6 +1905,9 @@ int smc_create(const smc_config* cfg, smc_engine** out) {
   P.rank = 0; P.world = 1; P.Ntot = (long long)N; P.base = 0;
   if ((rc = dev_alloc(e, &P.psum, cfg->parity_scan ? N + 1 : 1))) { smc_destroy(e); return rc; }
   if ((rc = dev_alloc(e, &P.tallies, 6 * (size_t)cfg->E))) { smc_destroy(e); return rc; }
+  if ((rc = dev_alloc(e, &P.pool, 2 * (size_t)cfg->E * N))) { smc_destroy(e); return rc; }
+  if ((rc = dev_alloc(e, &P.pool2, 2 * (size_t)cfg->E * N))) { smc_destroy(e); return rc; }
+  e->pool2_count = 2 * (size_t)cfg->E * N;
   if ((rc = dev_alloc(e, &P.anc, N))) { smc_destroy(e); return rc; }
   if ((rc = dev_alloc(e, &P.ctrl, 1))) { smc_destroy(e); return rc; }
   cudaMemsetAsync(P.anc, 0xff, N * sizeof(int), e->stream);
@@ -1884,6 +2058,8 @@ int smc_set_populations(smc_engine* e, int32_t npop, const double* inv2N, const 
     // the per-particle populations and migration marks are laid out with the tallies (smc_upload_rows): one slab that
     // the peers of a sharded population map
     if ((rc = dev_alloc(e, &P.tallies, 2 * (size_t)Q * E))) return rc;
+    if ((rc = dev_alloc(e, &P.pool2, (size_t)Q * E * P.N))) return rc;
+    e->pool2_count = (size_t)Q * E * P.N;
     P.sm.K = K; P.sm.Q = Q;
     P.sm.inv2N = d_inv; P.sm.mig = d_mig; P.sm.migtot = d_tot; P.sm.single_mig = d_single; P.sm.fixed = d_fixed;
     P.sm.leaf_pop = d_leaf;
@@ -2036,6 +2212,7 @@ int smc_upload_rows(smc_engine* e, const double* x_end, const int8_t* alleles, c
       const int oldest = r > 0 ? kfirst[(size_t)(r - 1) * E + ep] : 0;
       B = std::max(B, kn - oldest + 1);
     }
+  B += 1;      // a consumed bucket's records are read once more by the next launch (pooled second moments, phase 0)
   Params& P = e->P;
   P.B = B;
   P.R = R;
@@ -2217,6 +2394,8 @@ int smc_reset(smc_engine* e, const double* inv2N, double rho, const double* vb_l
   // frozen records and maps are (re)initialised when their bucket is born; only the open cells start from zero
   for (int b = 0; b < 2; b++) CUDA_TRY(cudaMemsetAsync(P.buf[b].open, 0, e->open_bytes, e->stream));
   CUDA_TRY(cudaMemsetAsync(P.tallies, 0, (size_t)e->tally_rows * E * sizeof(double), e->stream));
+  CUDA_TRY(cudaMemsetAsync(P.pool, 0, 2 * (size_t)E * P.N * sizeof(double), e->stream));
+  CUDA_TRY(cudaMemsetAsync(P.pool2, 0, e->pool2_count * sizeof(double), e->stream));
   CUDA_TRY(cudaMemsetAsync(P.anc, 0xff, (size_t)P.N * sizeof(int), e->stream));
   Ctrl init;
   memset(&init, 0, sizeof(init));
@@ -2255,6 +2434,19 @@ int smc_finish(smc_engine* e) {
   }
   CUDA_TRY(cudaMemcpyAsync(e->first_pending_d, fp.data(), fp.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   CUDA_TRY(cudaEventRecord(e->ev0, e->stream));
+  if (e->P.world == 1 && e->P.pool_on) {       // pooled second moments: first what the last row launch left, then bucket by bucket
+    smc_flush_pool_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d, 0, 0);
+    e->launches++;
+    int deepest = 0;
+    for (int ep = 0; ep < e->cfg.E; ep++) deepest = std::max(deepest, e->first_pending_h[ep] - fp[ep]);
+    for (int j = 0; j < deepest; j++) {
+      smc_flush_pool_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d, j, 1);
+      smc_flush_pool_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d, j, 2);
+      e->launches += 2;
+    }
+    smc_pool_reduce_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P);
+    e->launches++;
+  }
   if (e->P.sm.P > 1) smc_flush_struct_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
   else smc_flush_kernel<<<e->P.nblocks, e->BS, 0, e->stream>>>(e->P, e->first_pending_d);
   e->launches++;

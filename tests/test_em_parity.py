@@ -120,6 +120,27 @@ def test_single_sweep_within_monte_carlo_error(runs):
     assert opp.mean() == pytest.approx(n_seg / 2.5e-8, rel=0.05)         # Watterson: total length = S / mu
 
 
+def test_post_lag_ess_column(runs):
+    """the ESS column of .out (pfparam.cpp:524: opportunity / weight-squared tally, the number of independent ancestors
+    the counted records hang from): the reference pools the weights of the particles that share a record before
+    squaring (count.cpp:519-526); the engine pools per ancestor slot of every closed lag bucket.  Ensemble means per
+    row within [0.8, 1.8] of the reference's (24 seeds each; measured 1.08-1.56, the engine's is the higher: sharing
+    that arose while a bucket was still open is not pooled) -- it was 10-80 x too high with per-particle squares."""
+    ref, mine = runs
+    ref_runs = ref["runs"]["sweep"]
+    mine_rows = [parse_out(out + ".out")[1] for out, _ in mine["sweep"]]
+    checked = 0
+    for k, row in enumerate(ref_runs[0]):
+        if row["Type"] not in ("Coal", "Recomb"):
+            continue
+        a = np.mean([float(r[k]["ESS"]) for r in mine_rows])
+        b = np.mean([float(r[k]["ESS"]) for r in ref_runs])
+        print(row["Type"], row["Epoch"], "ESS ours %.2f ref %.2f ratio %.2f" % (a, b, a / b))
+        assert 0.8 < a / b < 1.8, (row["Type"], row["Epoch"], a, b)
+        checked += 1
+    assert checked == 5
+
+
 def test_em_iterations_within_monte_carlo_error(runs):
     """three in-binary EM iterations on the population sizes (M-step: CountModel::reset_Ne, count.cpp:267-294)"""
     ref, mine = runs

@@ -234,6 +234,11 @@ def test_full_filter_vs_oracle(S, name):
     # weight^2 tallies: copies do not share records, so sum(w^2 opp) is a lower bound of the reference's value
     assert np.all(t[2] <= ref["tallies"][2] * (1 + 1e-9) + 1e-300)
     assert np.all(t[5] <= ref["tallies"][5] * (1 + 1e-9) + 1e-300)
+    # ... and close to it since the weights are pooled per ancestor slot of every closed bucket (what is missed: sharing
+    # among siblings born while a bucket was open, and the bucket open at the end -- large on these short sequences)
+    for q in (2, 5):
+        if c["resamples"] > 0 and ref["tallies"][q].sum() > 0:
+            assert t[q].sum() >= 0.3 * ref["tallies"][q].sum(), (q, t[q].sum(), ref["tallies"][q].sum())
     pf.close()
 
 
