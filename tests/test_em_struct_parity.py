@@ -83,6 +83,25 @@ def test_layout_matches_reference(runs):
             assert float(a["Count"]) == 0.0 and float(b["Count"]) == 0.0
 
 
+def test_structured_post_lag_ess_column(runs):
+    """the ESS column with populations (every cell has a weight-squared twin, count.cpp:519-526): pooled per ancestor
+    slot as in the single-population engine; ensemble means within [0.7, 1.8] of the reference's on every Coal, Recomb
+    and Migr row that holds more than the pseudo-count"""
+    ref, mine = runs
+    ref_runs = ref["runs"]["sweep"]
+    mine_rows = [parse_out(out + ".out")[1] for out, _ in mine["sweep"]]
+    checked = 0
+    for k, row in enumerate(ref_runs[0]):
+        if row["Type"] not in ("Coal", "Recomb", "Migr"):
+            continue
+        a = np.mean([float(r[k]["ESS"]) for r in mine_rows])
+        b = np.mean([float(r[k]["ESS"]) for r in ref_runs])
+        print(row["Type"], row["Epoch"], row["From"], row["To"], "ESS ours %.2f ref %.2f ratio %.2f" % (a, b, a / b))
+        assert 0.7 < a / b < 1.8, (row, a, b)
+        checked += 1
+    assert checked == 13
+
+
 def test_structured_sweep_within_monte_carlo_error(runs):
     ref, mine = runs
     ref_runs = ref["runs"]["sweep"]
