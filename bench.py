@@ -537,7 +537,7 @@ def issue_roofline(S, device, clocks, particle_rows_per_s_per_gpu, rs_frac, prof
     fp64 pipe 5 % busy; what it uses up is instruction issue: ~10 k SASS instructions of dependent, divergent fp64 /
     shared-memory code per particle and row.  achieved = warp instructions per second, from the per-launch instruction
     count of the ncu capture of this kernel (profiles/r2_final_row_kernel_N160k_ncu_full.csv, smsp__inst_executed.sum
-    / particles: 260 per particle-row on a plain row, 362 on a resampling row; n = 8, E = 11) x the particle-rows per
+    / particles: 273 per particle-row on a plain row, 369 on a resampling row; n = 8, E = 11) x the particle-rows per
     second measured here; peak = SMs x 4 schedulers x the SM clock sampled during the run (one warp instruction per
     scheduler and cycle).  The fp64 FMA peak is measured live by a register-only probe kernel (smc_measure_fp64_fma)."""
     import torch
@@ -545,10 +545,10 @@ def issue_roofline(S, device, clocks, particle_rows_per_s_per_gpu, rs_frac, prof
     mhz = float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)
     peak = sms * 4 * mhz * 1e6
     out = {"bound": "issue", "unit": "warp-inst/s", "peak": peak, "sms": sms, "sm_mhz": mhz,
-           "dfma_peak_tflops": S.measure_fp64_fma(device), "fp64_pipe_active_frac": 0.057,
+           "dfma_peak_tflops": S.measure_fp64_fma(device), "fp64_pipe_active_frac": 0.056,
            "source": "instruction counts and fp64 pipe utilisation: ncu capture under profiles/ (static); rate: this run"}
     if profiled_shape:
-        per = 260.0 * (1.0 - rs_frac) + 362.0 * rs_frac
+        per = 273.0 * (1.0 - rs_frac) + 369.0 * rs_frac
         out.update({"warp_inst_per_particle_row": per, "achieved": per * particle_rows_per_s_per_gpu,
                     "frac": per * particle_rows_per_s_per_gpu / peak})
     else:

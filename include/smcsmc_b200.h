@@ -154,7 +154,11 @@ int smc_finish(smc_engine* e);
 
 /* ---- results ------------------------------------------------------------------------------------------------ */
 /* out[6*E]: coal_count, coal_opportunity, coal_weight, recomb_count, recomb_opportunity, recomb_weight per epoch,
- * WITHOUT CountModel's initial pseudo-counts (count.cpp:161-193).  *_weight is sum(w^2 * opportunity). */
+ * WITHOUT CountModel's initial pseudo-counts (count.cpp:161-193).  *_weight is sum(W^2 * opportunity) with W the weight
+ * pooled over the particles that share the record (count.cpp:519-526): pooled per ancestor slot of every closed lag
+ * bucket, per particle for the bucket still open at the end of the data and for particle-sharded populations (an upper
+ * bound of the resulting ESS).  The *_weight rows are complete after smc_finish (the second moments of a
+ * row's buckets are booked one launch later and added up at the end).  Environment SMC_NO_POOL=1: per-particle squares. */
 int smc_get_tallies(smc_engine* e, double* out);
 /* out[R]: per .seg row the posterior-mean recombination opportunity sum_i w_i * integral over the row of the local tree
  * length of particle i (generations x bp), weighted with the particles' weights right after the row -- the

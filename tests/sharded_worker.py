@@ -85,8 +85,12 @@ def main():
         pf.close()
         if rank != 0:
             continue
+        # a sharded population keeps per-particle squares in the *_weight rows (include/smcsmc_b200.h, smc_get_tallies):
+        # the single-GPU engine it is compared with is created with the same rule (the knob is read by smc_create)
+        os.environ["SMC_NO_POOL"] = "1"
         one = S.ParticleFilter(n, Ntot, t_start, inv2N, mu, rho, seqlen, lags, seed=77, chunk=5, device=local,
                                populations=pops)
+        del os.environ["SMC_NO_POOL"]
         one.upload_rows(x_end, al, is_site)
         one.init_particles()
         one.sweep()
