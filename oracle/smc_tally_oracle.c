@@ -46,12 +46,24 @@ typedef struct { int row, slot; orc_event ev; } orc_rec_event;
  * out: [2][Q][E] = sum of w * amount, then sum of w^2 * amount (the latter feeds the ESS column for the opportunity
  * channels).  orc_lagged_tallies below is this function with the single-population channel map; the structured
  * filter (smc_struct_oracle.c) uses it with per-population coalescence / migration channels. */
+/* Optional side output [Q][E]: the second moments as the CUDA engine defines them -- the weight is pooled
+ * over the particles that share the record's LAG BUCKET, i.e. that have the same ancestor in the row in which the
+ * update window the record falls into was passed by the sweep (the engine freezes a bucket's cells there), not the same
+ * ancestor in the row that wrote the record as in the reference.  A lower bound of the reference's value (block 1 of
+ * `out`), equal to it when no resampling separates writing and closing.  The window counted at the end of the data
+ * never closes: per-particle squares.  NULL switches it off. */
+static double* g_pooled_at_close = 0;
+void orc_set_pooled_at_close_buffer(double* out) { g_pooled_at_close = out; }
+
 void orc_channel_tallies(int E, int Q, const double* lags, int R, int N, const double* row_end, const double* weights,
                          const int* anc, const double* w_final, double seq_end, const orc_chan_event* evs, long nev,
                          double* out) {
   double counted_to[ORC_MAXE], update_to[ORC_MAXE];
   for (int e = 0; e < E; e++) counted_to[e] = 0.0;
   memset(out, 0, sizeof(double) * 2 * (size_t)Q * E);
+  double* pooled = g_pooled_at_close;
+  double* V = pooled ? (double*)malloc(sizeof(double) * (size_t)(R + 1) * N) : 0;   /* V[r][s], see below */
+  if (pooled) memset(pooled, 0, sizeof(double) * (size_t)Q * E);
   double* W = (double*)malloc(sizeof(double) * (size_t)(R + 1) * N);   /* W[r][s] descendant weight */
   for (int step = 0; step <= R; step++) {
     int end_data = step == R;
@@ -68,6 +80,35 @@ void orc_channel_tallies(int E, int Q, const double* lags, int R, int N, const d
         if (anc[(size_t)r * N] < 0) { memcpy(dst, src, sizeof(double) * N); continue; }
         for (int i = 0; i < N; i++) dst[i] = 0.0;
         for (int i = 0; i < N; i++) dst[anc[(size_t)r * N + i]] += src[i];
+      }
+      /* engine-defined second moments: per epoch the row in which this step's window closed, and for every (row, slot)
+       * at or before it the sum of squared descendant weights over its descendants in that row */
+      for (int ep = first; pooled && ep < E; ep++) {
+        int rc = top;                                   /* end of data: the window never closes -> per particle */
+        if (!end_data) { rc = 0; while (rc < step && row_end[rc] < update_to[ep]) rc++; }
+        for (int i = 0; i < N; i++) { double w = W[(size_t)rc * N + i]; V[(size_t)rc * N + i] = w * w; }
+        for (int r = rc - 1; r >= 0; r--) {
+          double* dst = V + (size_t)r * N;
+          const double* src = V + (size_t)(r + 1) * N;
+          if (anc[(size_t)r * N] < 0) { memcpy(dst, src, sizeof(double) * N); continue; }
+          for (int i = 0; i < N; i++) dst[i] = 0.0;
+          for (int i = 0; i < N; i++) dst[anc[(size_t)r * N + i]] += src[i];
+        }
+        for (long k = 0; k < nev; k++) {
+          const orc_chan_event* re = &evs[k];
+          if (re->epoch != ep || re->row > top || (!end_data && re->row > step)) continue;
+          double xs = counted_to[ep], xe = update_to[ep], amount;
+          if (re->rect) {
+            double a = re->x0 > xs ? re->x0 : xs, b = re->x1 < xe ? re->x1 : xe;
+            if (!(b > a)) continue;
+            amount = re->val * (b - a);
+          } else {
+            if (!(xs <= re->x0 && re->x0 < xe)) continue;
+            amount = re->val;
+          }
+          int rw = re->row < rc ? re->row : rc;          /* a record written in the closing row itself: its own slot */
+          pooled[(size_t)re->chan * E + ep] += V[(size_t)rw * N + re->slot] * amount;
+        }
       }
       for (long k = 0; k < nev; k++) {
         const orc_chan_event* re = &evs[k];
@@ -93,6 +134,7 @@ void orc_channel_tallies(int E, int Q, const double* lags, int R, int N, const d
     for (int e = 0; e < E; e++) counted_to[e] = update_to[e];
   }
   free(W);
+  if (V) free(V);
 }
 
 /* out: [6][E] = coal_count, coal_opp, coal_weight(w^2), rec_count, rec_opp, rec_weight(w^2) -- WITHOUT the initial
@@ -120,7 +162,15 @@ void orc_lagged_tallies(int E, const double* lags, int R, int N, const double* r
     }
   }
   double* o = (double*)malloc(sizeof(double) * 2 * 4 * (size_t)E);
+  double* user = g_pooled_at_close;                       /* [2][E]: coalescence and recombination opportunity */
+  double* p4 = user ? (double*)malloc(sizeof(double) * 4 * (size_t)E) : 0;
+  g_pooled_at_close = p4;
   orc_channel_tallies(E, 4, lags, R, N, row_end, weights, anc, w_final, seq_end, g, ng, o);
+  g_pooled_at_close = user;
+  if (user) {
+    for (int e = 0; e < E; e++) { user[e] = p4[1 * E + e]; user[E + e] = p4[3 * E + e]; }
+    free(p4);
+  }
   for (int e = 0; e < E; e++) {
     out[0 * E + e] = o[(0 * 4 + 0) * E + e];
     out[1 * E + e] = o[(0 * 4 + 1) * E + e];

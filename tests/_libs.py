@@ -118,6 +118,8 @@ def oracle():
                                           ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_long)]
         L.orc_set_row_opportunity_buffer.argtypes = [ctypes.c_void_p]
         L.orc_set_row_opportunity_buffer.restype = None
+        L.orc_set_pooled_at_close_buffer.argtypes = [ctypes.c_void_p]
+        L.orc_set_pooled_at_close_buffer.restype = None
         _oracle = L
     return _oracle
 
@@ -145,10 +147,13 @@ def oracle_filter(model, N, seed, chunk, start_pos, ess_fraction, lags, row_end,
     last_anc = np.zeros(N, dtype=np.int32)
     row_opp = np.zeros(R)
     L.orc_set_row_opportunity_buffer(P(row_opp))
+    pooled = np.zeros(2 * E)
+    L.orc_set_pooled_at_close_buffer(P(pooled))
     rc = L.orc_particle_filter(ctypes.byref(model), ctypes.byref(cfg), R, P(row_end), P(data), P(is_site),
                                None if mr is None else P(mr), parts, ctypes.byref(lnZ), P(tallies),
                                ctypes.byref(nres), P(rs_pos), P(rs_ess), P(last_anc), ctypes.byref(nrec))
     L.orc_set_row_opportunity_buffer(None)
+    L.orc_set_pooled_at_close_buffer(None)
     if rc:
         raise RuntimeError("oracle filter failed (event buffer overflow or zero weight)")
     parent = np.zeros((N, nn), dtype=np.int32)
@@ -160,7 +165,7 @@ def oracle_filter(model, N, seed, chunk, start_pos, ess_fraction, lags, row_end,
         logw[i], nb[i] = parts[i].logw, parts[i].next_base
     return dict(parent=parent, height=height, logw=logw, next_base=nb, lnZ=lnZ.value, tallies=tallies.reshape(6, E),
                 n_resample=nres.value, rs_pos=rs_pos[:nres.value], rs_ess=rs_ess[:nres.value], last_anc=last_anc,
-                n_recomb=nrec.value, row_opp=row_opp)
+                n_recomb=nrec.value, row_opp=row_opp, w2_pooled_at_close=pooled.reshape(2, E))
 
 
 def make_model(n, t_start, inv2N, mu, rho, seqlen, vb_logfac=None, rec_mask=None):

@@ -239,6 +239,11 @@ def test_full_filter_vs_oracle(S, name):
     for q in (2, 5):
         if c["resamples"] > 0 and ref["tallies"][q].sum() > 0:
             assert t[q].sum() >= 0.3 * ref["tallies"][q].sum(), (q, t[q].sum(), ref["tallies"][q].sum())
+    # exactly what the engine defines (oracle/smc_tally_oracle.c, pooled at the row in which the record's update window
+    # was passed): the pooling kernels, the two-launch hand-over and the end-of-data passes add up to the same numbers
+    if max_rec is None:
+        np.testing.assert_allclose(t[2], ref["w2_pooled_at_close"][0], rtol=1e-9, atol=1e-300)
+        np.testing.assert_allclose(t[5], ref["w2_pooled_at_close"][1], rtol=1e-9, atol=1e-300)
     pf.close()
 
 
