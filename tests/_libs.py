@@ -335,11 +335,14 @@ def oracle_sfilter(smodel, N, seed, chunk, start_pos, ess_fraction, lags, row_en
     nres = ctypes.c_int()
     nrec = ctypes.c_long()
     last_anc = np.zeros(N, dtype=np.int32)
+    pooled = np.zeros(Q * E)
+    L.orc_set_pooled_at_close_buffer(P(pooled))
     rc = L.orc_sparticle_filter(ctypes.byref(smodel), N, ctypes.c_uint64(seed), ctypes.c_uint32(chunk),
                                 ctypes.c_uint32(slot_offset), ctypes.c_double(start_pos), ctypes.c_double(ess_fraction),
                                 ancestral_aware, P(lags), R, P(row_end), P(data), P(is_site),
                                 None if mr is None else P(mr), parts, ctypes.byref(lnZ), P(tallies), ctypes.byref(nres),
                                 P(last_anc), ctypes.byref(nrec))
+    L.orc_set_pooled_at_close_buffer(None)
     if rc:
         raise RuntimeError("structured oracle filter failed: %d" % rc)
     parent = np.zeros((N, nn), dtype=np.int32)
@@ -356,4 +359,5 @@ def oracle_sfilter(smodel, N, seed, chunk, start_pos, ess_fraction, lags, row_en
         marks.append(sorted((int(parts[i].mark_branch[q]), float(parts[i].mark_time[q]), int(parts[i].mark_pop[q]))
                             for q in range(k)))
     return dict(parent=parent, height=height, pop=pop, marks=marks, logw=logw, next_base=nb, lnZ=lnZ.value,
-                tallies=tallies.reshape(2, Q, E), n_resample=nres.value, last_anc=last_anc, n_recomb=nrec.value)
+                tallies=tallies.reshape(2, Q, E), n_resample=nres.value, last_anc=last_anc, n_recomb=nrec.value,
+                w2_pooled_at_close=pooled.reshape(Q, E))

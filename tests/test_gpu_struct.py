@@ -117,6 +117,8 @@ def test_structured_filter_vs_oracle(S, name):
     np.testing.assert_allclose(t[0], ref["tallies"][0], rtol=1e-10, atol=1e-13)
     # w^2 sums: copies do not share records, so the device value is a lower bound
     assert np.all(t[1] <= ref["tallies"][1] * (1 + 1e-9) + 1e-300)
+    # ... and exactly the engine's definition (pooled at the row in which the record's update window was passed)
+    np.testing.assert_allclose(t[1], ref["w2_pooled_at_close"], rtol=1e-9, atol=1e-300)
     # the tallies carry what the model implies: coalescences in every population that has samples or receives lineages,
     # migration counts only where the model has a rate
     mig = G[name + "_mig"]
