@@ -14,6 +14,7 @@
 #include <iomanip>
 #include <iostream>
 #include <sstream>
+#include <thread>
 #include "../../include/smcsmc_b200.h"
 #include "params.hpp"
 #include "segment.hpp"
@@ -189,6 +190,73 @@ void dump_model(const Params& P) {
 }
 
 // one EM iteration: pfARG_core (smcsmc.cpp:278-400)
+// ---- <prefix>.recomb.gz rows (CountModel::dump_local_recomb_logs, count.cpp:630-653) -----------------------------------
+// "%.5e" of a positive double, digits from integer arithmetic; anything near a rounding tie or out of the usual range goes
+// through snprintf, so the text is what the reference's iostream prints
+static int format_sci5(char* o, double v) {
+  if (v == 0.0) { memcpy(o, "0.00000e+00", 11); return 11; }
+  if (!(v > 1e-290 && v < 1e290)) return snprintf(o, 32, "%.5e", v);
+  int ex = (int)floor(log10(v));
+  double m = v / pow(10.0, ex);
+  if (m >= 10.0) { m /= 10.0; ex++; }
+  if (m < 1.0) { m *= 10.0; ex--; }
+  const double scaled = m * 1e5;
+  const double r = floor(scaled + 0.5);
+  if (fabs(scaled + 0.5 - floor(scaled + 0.5)) < 1e-6 || fabs(scaled + 0.5 - floor(scaled + 0.5)) > 1.0 - 1e-6 || r >= 1e6 || ex < -99 || ex > 99)
+    return snprintf(o, 32, "%.5e", v);
+  long long d = (long long)r;
+  o[0] = (char)('0' + d / 100000); o[1] = '.';
+  for (int k = 5; k >= 1; k--) { o[1 + k] = (char)('0' + d % 10); d /= 10; }
+  o[7] = 'e'; o[8] = ex < 0 ? '-' : '+';
+  const int ax = ex < 0 ? -ex : ex;
+  o[9] = (char)('0' + ax / 10); o[10] = (char)('0' + ax % 10);
+  return 11;
+}
+
+static thread g_recomb_writer;
+static string g_recomb_error;
+static void recomb_writer_join() {
+  if (g_recomb_writer.joinable()) g_recomb_writer.join();
+  if (!g_recomb_error.empty()) { string m = g_recomb_error; g_recomb_error.clear(); throw runtime_error(m); }
+}
+
+static void write_recomb_table(string name, int em, int n, double start_position, double bin, size_t nbins, vector<double> diff) {
+  gzFile g = gzopen(name.c_str(), "ab1");
+  if (!g) { g_recomb_error = "cannot open " + name; return; }
+  if (em == 0) {
+    string h = "iter\tlocus\tsize\topp_per_nt";
+    for (int s = 0; s < n; s++) h += "\t" + to_string(s + 1);
+    h += "\ttime\tlog_time\n";
+    gzwrite(g, h.data(), (unsigned)h.size());
+  }
+  string zeros;
+  for (int s = 0; s < n + 2; s++) zeros += "\t0.00000e+00";
+  zeros += "\n";
+  char head[48], binsz[32];
+  const int nh = snprintf(head, sizeof head, "%d\t", em), nb = snprintf(binsz, sizeof binsz, "\t%.0f\t", bin);
+  string buf;
+  buf.reserve((1u << 20) + 256);
+  char num[40];
+  double cur = 0.0;
+  for (size_t i = 0; i < nbins; i++) {
+    cur += diff[i];
+    buf.append(head, nh);
+    const double locus = i * bin + start_position;
+    if (locus >= 0 && locus < 9e15 && locus == floor(locus)) {
+      char* e_ = num + sizeof num; char* q = e_;
+      unsigned long long u = (unsigned long long)locus;
+      do { *--q = (char)('0' + u % 10); u /= 10; } while (u);
+      buf.append(q, e_ - q);
+    } else buf.append(num, snprintf(num, sizeof num, "%.0f", locus));
+    buf.append(binsz, nb);
+    buf.append(num, format_sci5(num, cur / bin));
+    buf += zeros;
+    if (buf.size() > (1u << 20)) { gzwrite(g, buf.data(), (unsigned)buf.size()); buf.clear(); }
+  }
+  if (!buf.empty()) gzwrite(g, buf.data(), (unsigned)buf.size());
+  gzclose(g);
+}
+
 void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<double>& chunk_start, double chunk_len,
                 const Out& out, int em, const vector<int>& devices) {
   const int device = devices[0];
@@ -449,28 +517,10 @@ void pfARG_core(Params& P, const vector<host::SegRows>& chunks, const vector<dou
         }
       }
     }
-    gzFile g = gzopen(out.recomb_name.c_str(), "ab");
-    if (!g) throw runtime_error("cannot open " + out.recomb_name);
-    if (em == 0) {
-      string h = "iter\tlocus\tsize\topp_per_nt";
-      for (int s = 0; s < n; s++) h += "\t" + to_string(s + 1);
-      h += "\ttime\tlog_time\n";
-      gzwrite(g, h.data(), (unsigned)h.size());
-    }
-    string zeros;
-    for (int s = 0; s < n + 2; s++) zeros += "\t0.00000e+00";
-    zeros += "\n";
-    string buf;
-    char line[96];
-    double cur = 0.0;
-    for (size_t i = 0; i < nbins; i++) {
-      cur += diff[i];
-      snprintf(line, sizeof line, "%d\t%.0f\t%.0f\t%.5e", em, i * bin + P.start_position, bin, cur / bin);
-      buf += line; buf += zeros;
-      if (buf.size() > (1u << 20)) { gzwrite(g, buf.data(), (unsigned)buf.size()); buf.clear(); }
-    }
-    if (!buf.empty()) gzwrite(g, buf.data(), (unsigned)buf.size());
-    gzclose(g);
+    // formatting and compressing 10 bins per kb takes longer than the sweep of a 100-Mb locus: a writer thread does it
+    // while the next EM iteration runs (joined before the next table and at exit)
+    recomb_writer_join();
+    g_recomb_writer = thread(write_recomb_table, out.recomb_name, em, n, (double)P.start_position, bin, nbins, std::move(diff));
   }
 
   // reset_model_parameters(force_update = true): the in-binary M-step (count.cpp:44-63,267-352)
@@ -595,8 +645,10 @@ int main(int argc, char* argv[]) {
       write_log(lf, P, out);
     }
     write_log(cout, P, out);
+    recomb_writer_join();
     return EXIT_SUCCESS;
   } catch (const exception& e) {
+    if (g_recomb_writer.joinable()) g_recomb_writer.join();
     cerr << "Error: " << e.what() << endl;
     return EXIT_FAILURE;
   }
