@@ -139,6 +139,36 @@ def test_lagged_tallies(L):
         np.testing.assert_allclose(out, want, rtol=1e-12, atol=1e-300)
 
 
+def test_second_moments_pooled_at_close_bracket_the_reference(L):
+    """the engine's definition of the *_weight tallies as the oracle states it (orc_set_pooled_at_close_buffer: weights
+    pooled over the particles with the same ancestor in the row in which the record's update window was passed) on the
+    reference-generated tally scripts: never above the reference's value (pooled at the row that wrote the record),
+    never below per-particle squares, and equal to both when the script has no resampling"""
+    g = np.load(os.path.join(G, "tallies.npz"))
+    L.orc_set_pooled_at_close_buffer.argtypes = [ctypes.c_void_p]
+    L.orc_set_pooled_at_close_buffer.restype = None
+    seen_gap = False
+    for k in range(int(g["ncases"])):
+        N, E = int(g[f"t{k}_N"]), int(g[f"t{k}_E"])
+        evs = [(int(r), int(s), int(ty), int(e), int(c), x0, x1, opp) for (r, s, ty, e, c, x0, x1, opp) in g[f"t{k}_evs"]]
+        arr = _cases.rec_events_array(evs)
+        row_end, weights, anc = g[f"t{k}_row_end"], np.ascontiguousarray(g[f"t{k}_weights"]), np.ascontiguousarray(g[f"t{k}_anc"])
+        out, pooled = np.zeros(6 * E), np.zeros(2 * E)
+        L.orc_set_pooled_at_close_buffer(P(pooled))
+        L.orc_lagged_tallies(E, P(g[f"t{k}_lags"]), len(row_end), N, P(row_end), P(weights), P(anc),
+                             P(g[f"t{k}_w_final"]), float(g[f"t{k}_seqlen"]), arr, len(evs), P(out))
+        L.orc_set_pooled_at_close_buffer(None)
+        exact = out.reshape(6, E)[[2, 5]]
+        pooled = pooled.reshape(2, E)
+        assert np.all(pooled <= exact * (1 + 1e-12) + 1e-300)
+        if np.all(anc.reshape(len(row_end), N)[:, 0] < 0):       # no resampling anywhere: nothing is shared
+            np.testing.assert_allclose(pooled, exact, rtol=1e-12, atol=1e-300)
+        elif exact.sum() > 0:
+            seen_gap = seen_gap or pooled.sum() < exact.sum() * (1 - 1e-9)
+            assert pooled.sum() > 0
+    assert seen_gap          # the scripts do contain sharing that arises between writing and closing
+
+
 def test_fastexp_branches(L):
     # rational branch vs libm branch (particle.cpp:30-40)
     for x in (-1e-9, -0.1, -0.7, -0.7184, -0.72, -5.0):
